@@ -1,0 +1,108 @@
+"""Seeded synthetic weights / inputs for the ViT-family configs BASELINE.json names.
+
+There is no network for checkpoints or ImageNet, so every test, fixture and
+bench run uses these.  The generator is deliberately independent of the
+reference's own init order: it emits a plain ``state_dict`` (reference key
+names, SURVEY.md section 5 "checkpoint") from a CPU ``torch.Generator``; the
+same dict is loaded into the reference model (in the build container, to make
+golden fixtures) and into ours (on the GPU box), so both sides see bit-identical
+weights.  De-degeneration follows SURVEY.md section 8(d): LN weight ~ U(0.5, 1.5),
+biases ~ N(0, 0.1), qkv weight x6 (peaked attention so Shiftmax is exercised).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import torch
+
+
+@dataclass(frozen=True)
+class VitConfig:
+    name: str
+    embed_dim: int
+    depth: int
+    num_heads: int
+    mlp_ratio: int = 4
+    img_size: int = 224
+    patch_size: int = 16
+    in_chans: int = 3
+    num_classes: int = 1000
+    # the 8 per-location bit-widths of vit_quant.VisionTransformer.__init__ (vit_quant.py:180-187)
+    bitwidths: tuple = (8, 8, 8, 8, 8, 8, 8, 8)
+    gelu_type: str = "ivit"
+    softmax_type: str = "ivit"
+    layernorm_type: str = "ivit"
+
+    @property
+    def num_patches(self) -> int:
+        return (self.img_size // self.patch_size) ** 2
+
+    @property
+    def tokens(self) -> int:
+        return self.num_patches + 1
+
+    def with_layers(self, gelu=None, softmax=None, layernorm=None, bitwidths=None) -> "VitConfig":
+        from dataclasses import replace
+        return replace(self,
+                       gelu_type=gelu or self.gelu_type,
+                       softmax_type=softmax or self.softmax_type,
+                       layernorm_type=layernorm or self.layernorm_type,
+                       bitwidths=tuple(bitwidths) if bitwidths is not None else self.bitwidths)
+
+
+CONFIGS = {
+    "deit_tiny": VitConfig("deit_tiny", 192, 12, 3),
+    "deit_small": VitConfig("deit_small", 384, 12, 6),
+    "deit_base": VitConfig("deit_base", 768, 12, 12),
+    "vit_base": VitConfig("vit_base", 768, 12, 12),
+    # a 2-block, 2-head toy used by fast unit tests (not a reference factory)
+    "toy": VitConfig("toy", 128, 2, 2),
+}
+
+
+def synth_vit_state(cfg: VitConfig, seed: int = 0, negate_ln_frac: float = 0.0) -> dict:
+    """Deterministic fp32 weights, keyed like the reference ``state_dict`` (weights/biases only)."""
+    g = torch.Generator(device="cpu")
+    g.manual_seed(1000 + seed)
+    C, Hd = cfg.embed_dim, cfg.embed_dim * cfg.mlp_ratio
+    P = cfg.patch_size
+
+    def normal(*shape, std):
+        return (torch.randn(*shape, generator=g) * std).clamp_(-2.5 * std, 2.5 * std)
+
+    def ln(prefix, sd):
+        w = torch.rand(C, generator=g) + 0.5
+        if negate_ln_frac > 0:
+            flip = torch.rand(C, generator=g) < negate_ln_frac
+            w = torch.where(flip, -w, w)
+        sd[prefix + ".weight"] = w
+        sd[prefix + ".bias"] = normal(C, std=0.1)
+
+    sd: dict = {}
+    sd["cls_token"] = normal(1, 1, C, std=0.02)
+    sd["pos_embed"] = normal(1, cfg.tokens, C, std=0.02)
+    sd["patch_embed.proj.weight"] = normal(C, cfg.in_chans, P, P, std=0.02)
+    sd["patch_embed.proj.bias"] = normal(C, std=0.1)
+    for i in range(cfg.depth):
+        b = f"blocks.{i}."
+        ln(b + "norm1", sd)
+        sd[b + "attn.qkv.weight"] = normal(3 * C, C, std=0.02) * 6.0
+        sd[b + "attn.qkv.bias"] = normal(3 * C, std=0.1)
+        sd[b + "attn.proj.weight"] = normal(C, C, std=0.02)
+        sd[b + "attn.proj.bias"] = normal(C, std=0.1)
+        ln(b + "norm2", sd)
+        sd[b + "mlp.fc1.weight"] = normal(Hd, C, std=0.02)
+        sd[b + "mlp.fc1.bias"] = normal(Hd, std=0.1)
+        sd[b + "mlp.fc2.weight"] = normal(C, Hd, std=0.02)
+        sd[b + "mlp.fc2.bias"] = normal(C, std=0.1)
+    ln("norm", sd)
+    sd["head.weight"] = normal(cfg.num_classes, C, std=0.02)
+    sd["head.bias"] = normal(cfg.num_classes, std=0.1)
+    return sd
+
+
+def synth_images(batch: int, cfg: VitConfig, seed: int = 0) -> torch.Tensor:
+    """ImageNet-normalised images are ~N(0,1); fp32 [B,3,H,W] on CPU."""
+    g = torch.Generator(device="cpu")
+    g.manual_seed(2000 + seed)
+    return torch.randn(batch, cfg.in_chans, cfg.img_size, cfg.img_size, generator=g)

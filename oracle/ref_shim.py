@@ -1,0 +1,81 @@
+"""TEST INFRASTRUCTURE ONLY -- never imported by the product path.
+
+Imports the *unmodified* reference (lionnus/I-ViT, mounted read-only at
+/root/reference) on a CPU-only box.  The reference cannot be imported as-is
+(SURVEY.md section 0): `ppoly_backend.py:8` imports matplotlib at module top level and
+six sites call `.cuda(device=x.device)` unconditionally (`quant_utils.py:89`,
+`:174-175`; `ivit_modules.py:33`, `:121`, `:176`; `ibert_modules.py:126`,
+`:317`).  Two shims, no source edits:
+
+  * a stub `matplotlib` / `matplotlib.pyplot` in `sys.modules`
+  * `torch.Tensor.cuda` becomes a no-op while the reference runs on CPU
+
+This module only exists in the build container: `/root/reference` is absent on
+the GPU box, so nothing under `tests/ -m gpu`, `smoke()` or `bench.py` imports
+it.  It is used by `oracle/make_golden.py` (fixture generator) and by the
+`-m "not gpu"` tests that pin the numpy oracle against the real reference.
+"""
+from __future__ import annotations
+
+import contextlib
+import os
+import sys
+import types
+
+REFERENCE_ROOT = os.environ.get("IVIT_REFERENCE_ROOT", "/root/reference")
+
+
+def reference_available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "models", "vit_quant.py"))
+
+
+def _install_stubs() -> None:
+    if "matplotlib" not in sys.modules:
+        mpl = types.ModuleType("matplotlib")
+        plt = types.ModuleType("matplotlib.pyplot")
+        mpl.pyplot = plt
+        sys.modules["matplotlib"] = mpl
+        sys.modules["matplotlib.pyplot"] = plt
+    if "tkinter" not in sys.modules:           # swin_quant.py:2 `from tkinter import X`
+        tk = types.ModuleType("tkinter")
+        tk.X = "x"
+        sys.modules["tkinter"] = tk
+
+
+_REF = None
+
+
+def load_reference():
+    """Return the reference's `models` package (ViT/DeiT factories + quantization_utils)."""
+    global _REF
+    if _REF is not None:
+        return _REF
+    if not reference_available():
+        raise RuntimeError(f"reference not mounted at {REFERENCE_ROOT}")
+    import torch
+
+    _install_stubs()
+    # CPU run of code that hard-codes `.cuda(device=...)`.
+    torch.Tensor.cuda = lambda self, device=None, *a, **k: self  # type: ignore[assignment]
+    # The reference's top-level package is called `models`; keep it from
+    # colliding with anything of ours by importing it under its own sys.path entry.
+    sys.path.insert(0, REFERENCE_ROOT)
+    try:
+        import importlib
+
+        _REF = importlib.import_module("models")
+    finally:
+        sys.path.remove(REFERENCE_ROOT)
+    return _REF
+
+
+@contextlib.contextmanager
+def torch_threads(n: int | None = None):
+    import torch
+
+    old = torch.get_num_threads()
+    torch.set_num_threads(n or os.cpu_count() or 1)
+    try:
+        yield
+    finally:
+        torch.set_num_threads(old)
