@@ -1,0 +1,140 @@
+/* ivit_b200 -- C ABI of the B200 (sm_100a) kernels behind the I-ViT `quantization_utils`
+ * module API.
+ *
+ * The reference (lionnus/I-ViT) has no native code and no FFI: its boundary is the Python
+ * module API of `models/quantization_utils`.  This header is the
+ * seam *below* that API: the new Python `quantization_utils` modules call these entry
+ * points through ctypes where the reference calls stock torch ops.  Each entry point names
+ * the reference code it replaces (paths relative to /root/reference).
+ *
+ * Conventions: plain pointers and sizes only (device pointers unless noted), no torch
+ * types; every call enqueues on `stream` (a cudaStream_t passed as void*), never
+ * allocates, never synchronises, is re-entrant per stream, and returns 0 or a
+ * cudaError_t / negative ivit error code.  All integer "codes" are the reference's
+ * `round(x / scale)`; float artefacts of its float32 simulation are replayed on device.
+ */
+#ifndef IVIT_B200_H
+#define IVIT_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IVIT_ERR_BAD_ARG (-1)
+#define IVIT_ERR_UNSUPPORTED (-2)
+#define IVIT_ERR_DRIVER (-3)
+
+/* Library / device probe.  ivit_abi_version() needs no GPU. */
+int ivit_abi_version(void);
+int ivit_device_sm(int* major, int* minor);           /* cudaGetDeviceProperties of current device */
+const char* ivit_last_error(void);
+
+/* ---- QuantAct on a float tensor (no predecessor scale) --------------------------------
+ * quant_modules.py:374-377 -> quant_utils.py:13-49,79-97 (SymmetricQuantFunction):
+ * q = clamp(round(fl32(1/s) * x), -128, 127).  inv_scale = fl32(1/s) computed by the caller. */
+int ivit_quantize_f32_i8(const float* x, int8_t* out, float inv_scale, int64_t n, void* stream);
+/* Same, fused with the im2col of a kernel=stride=P convolution (layers_quant.py:191-198 +
+ * quant_modules.py:478-511): [B,Cin,H,W] fp32 -> [B*(H/P)*(W/P), Cin*P*P] int8. */
+int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float inv_scale, int B, int Cin, int H, int W, int P,
+                                 void* stream);
+
+/* ---- IntLayerNorm + following QuantAct --------------------------------------------------
+ * kind 0: ivit_modules.py:30-65 (IVITIntLayerNorm), kind 1: ibert_modules.py:112-158
+ * (IBERTIntLayerNorm; shift = its `shift` buffer, use_int_sqrt as the ctor flag), then
+ * quant_modules.py:379-387 / quant_utils.py:193-253 (fixedpoint_mul, per-channel ratio).
+ * x: int8 [rows, C] codes with scalar scale s_in; bias_int[C], sf[C] (the LN's per-channel
+ * output scale), mult[C] = m*2^-e of sf[c]/s_out as float64; out int8 [rows, C]. */
+int ivit_layernorm_requant_i8(int kind, const int8_t* x, int8_t* out, int rows, int C, float s_in,
+                              const float* bias_int, const float* sf, const double* mult, int qmin, int qmax,
+                              float shift, int use_int_sqrt, void* stream);
+
+/* ---- GELU (+ mlp.qact1) as a per-layer table --------------------------------------------
+ * kind 0: ivit_modules.py:89-126 (ShiftGELU, n = 23, output_bit), kind 1:
+ * ibert_modules.py:203-235.  Builds lut[256][256] int8, indexed [rowmax+128][code+128], with
+ * the following QuantAct (scalar mult_out, clamp) applied.  s_in = scale of the int8 input. */
+int ivit_gelu_lut_build(int kind, int8_t* lut, float s_in, int output_bit, double mult_out, int qmin, int qmax,
+                        float* s_gelu_out_host, void* stream);
+/* 65536 raw ShiftGELU integers (float32), for tests of the un-fused module. */
+int ivit_gelu_ivit_raw_table(float* out65536, float s_in, int output_bit, void* stream);
+int ivit_gelu_lut_apply_i8(const int8_t* x, int8_t* out, const int8_t* lut, int rows, int C, void* stream);
+
+/* ---- stand-alone QuantAct on int32 accumulators (un-fused path) ------------------------
+ * quant_utils.py:193-253.  z int32 [rows, C]; s_in/mult have C entries if per_channel else 1;
+ * identity (may be NULL) int8 [rows, C] with scalar mult_id. */
+int ivit_requant_i32_i8(const int32_t* z, const float* s_in, const double* mult, int per_channel,
+                        const int8_t* identity, double mult_id, int8_t* out, int64_t rows, int C, int qmin, int qmax,
+                        void* stream);
+int ivit_dequant_i8_f32(const int8_t* q, float scale, float* out, int64_t n, void* stream);
+int ivit_fill_cls_rows_i8(int8_t* out, const int8_t* cls_row, int B, int N, int C, void* stream);
+
+/* ---- QuantLinear / QuantConv2d(im2col) GEMM with fused QuantAct epilogues ---------------
+ * quant_modules.py:186-226 (QuantLinear.forward: F.linear on integer-valued floats) and the
+ * QuantAct(s) that follow it in vit_quant.py / layers_quant.py.  tcgen05 kind::i8 MMA, INT32
+ * accumulators in TMEM, TMA-fed.  A int8 [M,K] (row stride lda bytes), W int8 [N,K]
+ * (row-major, K contiguous), bias int32 [N] or NULL.
+ *
+ * epilogue:
+ *   IVIT_EPI_ACC32    out int32 [M,N] = acc + bias                       (QuantLinear alone)
+ *   IVIT_EPI_REQUANT  out int8 = clamp(rint((acc+bias)*mult[n]), qmin, qmax)
+ *                     (QuantLinear -> QuantAct: attn.qkv/qact1, mlp.fc1/qact_gelu, ...)
+ *   IVIT_EPI_RESIDUAL c1 = clamp(rint((acc+bias)*mult[n]), qmin, qmax);
+ *                     out int8 = clamp(rint(c1*mult2) + rint(id*mult_id), qmin2, qmax2)
+ *                     (attn.proj -> attn.qact3 -> Block.qact2(identity), vit_quant.py:86-87,147;
+ *                      mlp.fc2 -> mlp.qact2 -> Block.qact4(identity), :151-153;
+ *                      patch_embed.proj -> patch_embed.qact -> qact1(identity=pos), :289-296)
+ *   IVIT_EPI_LOGITS   out float32 = float(acc+bias) * scale_out[n]       (head, vit_quant.py:311)
+ * Row remap (patch embed writes tokens 1..N-1 of every image, identity = positional codes):
+ *   out row  = (r / group) * out_group_stride + (r % group) + out_row_off
+ *   id  row  = id_broadcast ? (r % group) + out_row_off : out row
+ * Pass group = 0 for the identity mapping. */
+enum { IVIT_EPI_ACC32 = 0, IVIT_EPI_REQUANT = 1, IVIT_EPI_RESIDUAL = 2, IVIT_EPI_LOGITS = 3 };
+typedef struct {
+  int epilogue;
+  const int32_t* bias;       /* [N] or NULL */
+  const double* mult;        /* [N]  (REQUANT, RESIDUAL) */
+  const float* s_in;         /* [N]  per-channel scale of (acc+bias): slow path for |z| >= 2^22 */
+  int qmin, qmax;
+  double mult2;              /* RESIDUAL */
+  double mult_id;            /* RESIDUAL */
+  int qmin2, qmax2;          /* RESIDUAL */
+  const int8_t* identity;    /* RESIDUAL: int8, row stride ld_id bytes */
+  int64_t ld_id;
+  const float* scale_out;    /* LOGITS: [N] */
+  int group, out_group_stride, out_row_off, id_broadcast;
+  int force_slow;            /* 1: always take the general requant path (|mult| >= 256 or huge codes) */
+} ivit_gemm_epilogue_t;
+int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M, int N, int K, void* out, int64_t ldo,
+                 const ivit_gemm_epilogue_t* epi, void* stream);
+/* Straightforward CUDA-core int8 GEMM with the same epilogues: on-device cross-check for
+ * the tcgen05 kernel at sizes the CPU oracle cannot reach.  Not used by the product path. */
+int ivit_gemm_i8_simple(const int8_t* A, int64_t lda, const int8_t* W, int M, int N, int K, void* out, int64_t ldo,
+                        const ivit_gemm_epilogue_t* epi, void* stream);
+
+/* ---- fused attention ---------------------------------------------------------------------
+ * vit_quant.py:65-85: QuantMatMul(q,k^T) (quant_modules.py:404-409) -> *scale -> qact_attn1
+ * -> IntSoftmax (kind 0: ivit_modules.py:150-179 Shiftmax; kind 1: ibert_modules.py:275-319)
+ * -> QuantMatMul(attn, v) -> transpose(1,2).reshape -> attn.qact2.  Scores never leave the SM.
+ * qkv int8 [B, N, 3, H, hd] (the layout QuantLinear(qkv)+qact1 produce); out int8 [B, N, H*hd]. */
+typedef struct {
+  int kind;                  /* 0 ivit, 1 ibert */
+  int output_bit;            /* softmax output bits (8) */
+  double mult_attn;          /* qact_attn1: m*2^-e of (s_q*s_k*scale)/s_attn */
+  int qmin_attn, qmax_attn;
+  float s_attn;              /* scale of qact_attn1 output = softmax input */
+  double mult_out;           /* attn.qact2: (s_softmax*s_v)/s_out */
+  int qmin_out, qmax_out;
+  /* ibert only: inner QuantAct(16) of IBERTIntSoftmax (ibert_modules.py:262,310) */
+  double mult_exp16;
+  float s_exp16;
+} ivit_attention_params_t;
+int ivit_attention_i8(const int8_t* qkv, int8_t* out, int B, int N, int H, int hd,
+                      const ivit_attention_params_t* p, void* stream);
+/* Debug taps of the same kernel: softmax codes [B,H,N,N] uint8 (what int_softmax emits). */
+int ivit_attention_probs_i8(const int8_t* qkv, uint8_t* probs, int B, int N, int H, int hd,
+                            const ivit_attention_params_t* p, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IVIT_B200_H */

@@ -1,0 +1,476 @@
+// Row-wise (HBM-bound) kernels of the I-ViT integer block: input quantiser (+im2col store
+// layout), integer LayerNorm fused with the following QuantAct, ShiftGELU / I-BERT GELU as a
+// per-layer (row-max, code) table, and small helpers.  One warp per row, 16-byte vector
+// access, shuffle reductions.  All arithmetic through intmath.cuh (bit-exact replay).
+#include "intmath.cuh"
+#include "ivit_b200.h"
+
+namespace ivit {
+
+static inline int cdiv(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
+
+// ------------------------------------------------------------------ input quantiser
+// quant_utils.py:49 + :93: q = clamp(round(fl32(1/s) * x), -128, 127)   (reciprocal-multiply!)
+__device__ __forceinline__ int quant8(float x, float inv_s) {
+  const float q = rintf(__fmul_rn(inv_s, x));
+  return static_cast<int>(fminf(fmaxf(q, -128.f), 127.f));
+}
+
+// fp32 image [B,Cin,H,W] -> int8 patch matrix [B*gh*gw, Cin*P*P] (k = c*P*P + i*P + j): the
+// im2col of a kernel=stride=P convolution is a pure re-indexing, so it is folded into the
+// quantiser's store layout.
+__global__ void quantize_patches_kernel(const float* __restrict__ x, int8_t* __restrict__ out, float inv_s, int B,
+                                        int Cin, int H, int W, int P) {
+  const int gh = H / P, gw = W / P;
+  const int K = Cin * P * P;
+  const long long total4 = static_cast<long long>(B) * gh * gw * K / 4;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total4;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long o = t * 4;
+    const int k = static_cast<int>(o % K);
+    const long long row = o / K;
+    const int pw = static_cast<int>(row % gw);
+    const int ph = static_cast<int>((row / gw) % gh);
+    const int b = static_cast<int>(row / (static_cast<long long>(gw) * gh));
+    const int j = k % P, i = (k / P) % P, c = k / (P * P);
+    const float4 v = *reinterpret_cast<const float4*>(
+        x + ((static_cast<long long>(b) * Cin + c) * H + ph * P + i) * W + pw * P + j);
+    const int q0 = quant8(v.x, inv_s), q1 = quant8(v.y, inv_s), q2 = quant8(v.z, inv_s), q3 = quant8(v.w, inv_s);
+    const uint32_t packed = (q0 & 0xff) | ((q1 & 0xff) << 8) | ((q2 & 0xff) << 16) | (static_cast<uint32_t>(q3) << 24);
+    *reinterpret_cast<uint32_t*>(out + o) = packed;
+  }
+}
+
+// Plain elementwise quantiser (QuantAct without a predecessor scale on an arbitrary tensor).
+__global__ void quantize_kernel(const float* __restrict__ x, int8_t* __restrict__ out, float inv_s, long long n) {
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < n;
+       t += static_cast<long long>(gridDim.x) * blockDim.x)
+    out[t] = static_cast<int8_t>(quant8(x[t], inv_s));
+}
+
+// ------------------------------------------------------------------ LayerNorm + QuantAct
+// One warp per row.  Lane t owns elements {32*i + t}: that is torch's CPU accumulator layout
+// (intmath.cuh TorchSum32), so the tie-break slow path needs no data exchange.  The row is
+// staged through shared memory with 16-byte loads and read back byte-wise (conflict free).
+template <int MAXC>
+struct LnSmem {
+  int8_t row[MAXC];
+};
+
+// ivit_modules.py:30-65 followed by QuantAct (quant_modules.py:379-387, quant_utils.py:220-251).
+// per-channel params: bias_int[c] = floor((b/w)/(sqrt(C)/2^30)), sf[c] = sqrt(C)/2^30*w[c],
+// mult[c] = m*2^-e of sf[c]/s_out.
+template <int NPL>  // elements per lane = C/32 (compile-time for unrolling): 6, 12, 24, ...
+__global__ void __launch_bounds__(256)
+layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, int rows, float s_in,
+                              const float* __restrict__ bias_int, const float* __restrict__ sf,
+                              const double* __restrict__ mult, int qmin, int qmax) {
+  constexpr int C = NPL * 32;
+  __shared__ __align__(16) int8_t stage[8][C];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= rows) return;
+  const int8_t* xr = x + static_cast<long long>(row) * C;
+  // coalesced 16-byte loads -> smem
+  for (int v = lane; v < C / 16; v += 32)
+    *reinterpret_cast<int4*>(&stage[warp][v * 16]) = *reinterpret_cast<const int4*>(xr + v * 16);
+  __syncwarp();
+  int q[NPL];
+  int S = 0;
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) {
+    q[i] = stage[warp][32 * i + lane];
+    S += q[i];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
+  // :36-38  x_int = x/s (un-rounded), p = trunc(x_int)
+  float xe[NPL];
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) xe[i] = x_eff(static_cast<float>(q[i]), s_in);
+  // :37 mean = round(mean(x_int)).  Only an exact tie S/C = k + 1/2 can be moved by the
+  // float32 noise of the un-rounded inputs; then replay torch's summation order.
+  float sum_f = static_cast<float>(S);
+  const int rem = ((S % C) + C) % C;
+  if (rem * 2 == C) {
+    TorchSum32 acc;
+#pragma unroll
+    for (int i = 0; i < NPL; ++i) acc.add(xe[i]);
+    sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+  }
+  const int mean = static_cast<int>(rintf(__fdiv_rn(sum_f, static_cast<float>(C))));
+  int y[NPL];
+  long long var = 0;
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) {
+    y[i] = static_cast<int>(xe[i]) - mean;                    // :38-40 (trunc, int32)
+    var += static_cast<long long>(y[i] * y[i]);               // :41 int32 square (wraps, H9), :42 int64 sum
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) var += __shfl_xor_sync(0xffffffffu, var, o);
+  // :45-49 ten float32 Newton steps from k = 2^16
+  const float var_f = static_cast<float>(var);
+  float k = 65536.f;
+#pragma unroll
+  for (int it = 0; it < 10; ++it) k = floorf(__fmul_rn(__fadd_rn(k, floorf(__fdiv_rn(var_f, k))), 0.5f));
+  const float factor = floorf(__fdiv_rn(2147483648.f, k));   // :51 (2^31-1 -> 2^31 in float32)
+  int8_t* orow = out + static_cast<long long>(row) * C;
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) {
+    const int c = 32 * i + lane;
+    float v = floorf(__fmul_rn(__fmul_rn(static_cast<float>(y[i]), factor), 0.5f));   // :52
+    v = __fadd_rn(v, __ldg(bias_int + c));                                            // :61
+    const float sc = __ldg(sf + c);
+    const float xo = __fmul_rn(v, sc);                                                // :63
+    const float z = rintf(__fdiv_rn(xo, sc));                                         // quant_utils.py:220
+    const double r = requant_d(static_cast<double>(z), __ldg(mult + c));              // :229-230
+    const int code = static_cast<int>(fmin(fmax(r, static_cast<double>(qmin)), static_cast<double>(qmax)));
+    stage[warp][c] = static_cast<int8_t>(code);
+  }
+  __syncwarp();
+  for (int v = lane; v < C / 16; v += 32)
+    *reinterpret_cast<int4*>(orow + v * 16) = *reinterpret_cast<const int4*>(&stage[warp][v * 16]);
+}
+
+// ibert_modules.py:112-158 followed by QuantAct.  shift_pow = 2^shift, inv_shift_pow = 2^-shift.
+template <int NPL>
+__global__ void __launch_bounds__(256)
+layernorm_ibert_requant_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, int rows, float s_in,
+                               const float* __restrict__ bias_int, const float* __restrict__ sf,
+                               const double* __restrict__ mult, int qmin, int qmax, float shift_pow,
+                               float inv_shift_pow, int use_int_sqrt) {
+  constexpr int C = NPL * 32;
+  __shared__ __align__(16) int8_t stage[8][C];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= rows) return;
+  const int8_t* xr = x + static_cast<long long>(row) * C;
+  for (int v = lane; v < C / 16; v += 32)
+    *reinterpret_cast<int4*>(&stage[warp][v * 16]) = *reinterpret_cast<const int4*>(xr + v * 16);
+  __syncwarp();
+  float xe[NPL];
+  TorchSum32 acc;
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) {
+    xe[i] = x_eff(static_cast<float>(stage[warp][32 * i + lane]), s_in);   // :129
+    acc.add(xe[i]);
+  }
+  const float sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+  const float mean = rintf(__fdiv_rn(sum_f, static_cast<float>(C)));        // :130
+  float y[NPL];
+  TorchSum32 vacc;
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) {
+    y[i] = __fsub_rn(xe[i], mean);                                          // :131
+    const float ys = floorf(__fmul_rn(y[i], inv_shift_pow));                // :132
+    vacc.add(__fmul_rn(ys, ys));                                            // :133
+  }
+  const float var_f = torch_sum_finish(vacc.level_sum(), 0.f, nullptr, 0, lane);   // :134
+  float std_i;
+  if (use_int_sqrt) {                                                       // :85-109
+    const float n = fmaxf(var_f, 0.f);
+    const float bits = floorf(log2f(fmaxf(n, 1.f))) + 1.f;
+    float xk = pow2i(static_cast<int>(ceilf(__fmul_rn(bits, 0.5f))));
+    for (int it = 0; it < 4; ++it) {
+      const float inv = floorf(__fdiv_rn(n, fmaxf(xk, 1.f)));
+      xk = floorf(__fmul_rn(__fadd_rn(xk, inv), 0.5f));
+    }
+    std_i = (var_f > 0.f) ? xk : 0.f;
+  } else {
+    std_i = floorf(__fsqrt_rn(var_f));                                      // :145
+  }
+  std_i = __fmul_rn(std_i, shift_pow);
+  const float factor = floorf(__fdiv_rn(2147483648.f, std_i));             // :146 (2^31)
+  int8_t* orow = out + static_cast<long long>(row) * C;
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) {
+    const int c = 32 * i + lane;
+    float v = floorf(__fmul_rn(__fmul_rn(y[i], factor), 0.5f));             // :147
+    v = __fadd_rn(v, __ldg(bias_int + c));                                  // :154
+    const float sc = __ldg(sf + c);
+    const float xo = __fmul_rn(v, sc);                                      // :156
+    const float z = rintf(__fdiv_rn(xo, sc));
+    const double r = requant_d(static_cast<double>(z), __ldg(mult + c));
+    const int code = static_cast<int>(fmin(fmax(r, static_cast<double>(qmin)), static_cast<double>(qmax)));
+    stage[warp][c] = static_cast<int8_t>(code);
+  }
+  __syncwarp();
+  for (int v = lane; v < C / 16; v += 32)
+    *reinterpret_cast<int4*>(orow + v * 16) = *reinterpret_cast<const int4*>(&stage[warp][v * 16]);
+}
+
+// ------------------------------------------------------------------ GELU as a table
+// ShiftGELU's output for one element depends only on (its int8 code, the row-max int8 code):
+// ivit_modules.py:105-126, then mlp.qact1 (scalar requant + clamp).  I-BERT GELU
+// (ibert_modules.py:220-235) depends on the code alone.  Both are tabulated once per layer at
+// freeze time -- by this kernel, with the exact device arithmetic -- as lut[qmax+128][q+128]
+// (I-BERT: every row identical), so the per-element work of the hot kernel is one byte lookup.
+__global__ void gelu_lut_build_kernel(int8_t* __restrict__ lut, int mode, GeluIvitParams gi, GeluIbertParams gb,
+                                      double mult_out, float s_gelu_out, int qmin, int qmax_out) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= 65536) return;
+  const int q = (idx & 255) - 128, mx = (idx >> 8) - 128;
+  float g;   // integer-valued (ivit) or float (ibert) GELU output "x_int"
+  if (mode == 0) {
+    g = (q <= mx) ? gelu_ivit(q, mx, gi) : 0.f;
+  } else {
+    g = gelu_ibert(q, gb);
+  }
+  // module returns x_int * scaling_factor; QuantAct recovers round((x_int*s)/s) (quant_utils.py:220)
+  const float z = rintf(__fdiv_rn(__fmul_rn(g, s_gelu_out), s_gelu_out));
+  const double r = requant_d(static_cast<double>(z), mult_out);
+  lut[idx] = static_cast<int8_t>(static_cast<int>(fmin(fmax(r, (double)qmin), (double)qmax_out)));
+}
+
+// Raw (un-requantised) GELU integer output for tests / the generic path: int32 per table entry.
+__global__ void gelu_ivit_raw_kernel(float* __restrict__ out, GeluIvitParams gi) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= 65536) return;
+  const int q = (idx & 255) - 128, mx = (idx >> 8) - 128;
+  out[idx] = (q <= mx) ? gelu_ivit(q, mx, gi) : 0.f;
+}
+
+// One warp per row: row max (needed by ShiftGELU, ivit_modules.py:110), then table lookup.
+__global__ void __launch_bounds__(256)
+gelu_lut_apply_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, const int8_t* __restrict__ lut,
+                      int rows, int C) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= rows) return;
+  const int4* xr = reinterpret_cast<const int4*>(x + static_cast<long long>(row) * C);
+  int4* orow = reinterpret_cast<int4*>(out + static_cast<long long>(row) * C);
+  const int nv = C / 16;
+  int4 v[6];                       // up to C = 3072 (6 * 32 lanes * 16 B)
+  uint32_t m = 0x80808080u;        // four int8 lanes of -128
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    const int idx = i * 32 + lane;
+    if (idx < nv) {
+      v[i] = __ldg(xr + idx);
+      m = __vmaxs4(m, v[i].x); m = __vmaxs4(m, v[i].y); m = __vmaxs4(m, v[i].z); m = __vmaxs4(m, v[i].w);
+    }
+  }
+  int mx = max(max(static_cast<int8_t>(m), static_cast<int8_t>(m >> 8)),
+               max(static_cast<int8_t>(m >> 16), static_cast<int8_t>(m >> 24)));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  const int8_t* trow = lut + (mx + 128) * 256 + 128;
+  auto look4 = [&](uint32_t w) -> uint32_t {
+    const uint32_t b0 = static_cast<uint8_t>(__ldg(trow + static_cast<int8_t>(w)));
+    const uint32_t b1 = static_cast<uint8_t>(__ldg(trow + static_cast<int8_t>(w >> 8)));
+    const uint32_t b2 = static_cast<uint8_t>(__ldg(trow + static_cast<int8_t>(w >> 16)));
+    const uint32_t b3 = static_cast<uint8_t>(__ldg(trow + static_cast<int8_t>(w >> 24)));
+    return b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+  };
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    const int idx = i * 32 + lane;
+    if (idx < nv) {
+      int4 o;
+      o.x = look4(v[i].x); o.y = look4(v[i].y); o.z = look4(v[i].z); o.w = look4(v[i].w);
+      orow[idx] = o;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ small helpers
+// Row 0 of every image = the (batch independent) class-token row, computed at freeze time.
+__global__ void fill_cls_rows_kernel(int8_t* __restrict__ out, const int8_t* __restrict__ cls_row, int B, int N,
+                                     int C) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= B * C) return;
+  const int b = t / C, c = t % C;
+  out[(static_cast<long long>(b) * N) * C + c] = cls_row[c];
+}
+
+// Stand-alone QuantAct on int32 accumulators (generic / un-fused path and tests):
+// out = clamp(rint(z*mult[c]) [+ rint(id*mult_id)])   quant_utils.py:220-251
+__global__ void requant_i32_kernel(const int32_t* __restrict__ z, const float* __restrict__ s_in,
+                                   const double* __restrict__ mult, int per_channel, const int8_t* __restrict__ id,
+                                   double mult_id, int8_t* __restrict__ out, long long rows, int C, int qmin,
+                                   int qmax) {
+  const long long n = rows * C;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < n;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = per_channel ? static_cast<int>(t % C) : 0;
+    double r = requant_any(z[t], s_in[c], mult[c]);
+    if (id != nullptr) r += requant_d(static_cast<double>(id[t]), mult_id);
+    out[t] = static_cast<int8_t>(static_cast<int>(fmin(fmax(r, (double)qmin), (double)qmax)));
+  }
+}
+
+// codes * scale -> float32 (what the reference hands to un-quantised consumers)
+__global__ void dequant_i8_kernel(const int8_t* __restrict__ q, float s, float* __restrict__ out, long long n) {
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < n;
+       t += static_cast<long long>(gridDim.x) * blockDim.x)
+    out[t] = __fmul_rn(static_cast<float>(q[t]), s);
+}
+
+}  // namespace ivit
+
+// =============================================================================== C ABI
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+namespace ivit {
+thread_local char g_err[256] = "";
+int fail(int code, const char* msg) {
+  snprintf(g_err, sizeof(g_err), "%s", msg);
+  return code;
+}
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+    return static_cast<int>(e);
+  }
+  return 0;
+}
+static int ew_grid(long long n, int block) {
+  long long g = (n + block - 1) / block;
+  const long long cap = 148LL * 16;   // grid-stride: a few waves of the 148 SMs
+  return static_cast<int>(g < cap ? (g > 0 ? g : 1) : cap);
+}
+}  // namespace ivit
+
+using namespace ivit;
+
+extern "C" int ivit_abi_version(void) { return 1; }
+extern "C" const char* ivit_last_error(void) { return g_err; }
+extern "C" int ivit_device_sm(int* major, int* minor) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
+  cudaDeviceProp p;
+  e = cudaGetDeviceProperties(&p, dev);
+  if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
+  *major = p.major;
+  *minor = p.minor;
+  return 0;
+}
+
+extern "C" int ivit_quantize_f32_i8(const float* x, int8_t* out, float inv_scale, int64_t n, void* stream) {
+  if (n <= 0) return 0;
+  quantize_kernel<<<ew_grid(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, out, inv_scale, n);
+  return check_launch("quantize_kernel");
+}
+
+extern "C" int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float inv_scale, int B, int Cin, int H,
+                                            int W, int P, void* stream) {
+  if (P % 4 != 0 || H % P != 0 || W % P != 0) return fail(IVIT_ERR_BAD_ARG, "patch size must divide H, W; P % 4 == 0");
+  const long long n4 = static_cast<long long>(B) * Cin * H * W / 4;
+  if (n4 <= 0) return 0;
+  quantize_patches_kernel<<<ew_grid(n4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, out, inv_scale, B, Cin,
+                                                                                         H, W, P);
+  return check_launch("quantize_patches_kernel");
+}
+
+template <int NPL>
+static int launch_ln(int kind, const int8_t* x, int8_t* out, int rows, float s_in, const float* bias_int,
+                     const float* sf, const double* mult, int qmin, int qmax, float shift, int use_int_sqrt,
+                     cudaStream_t st) {
+  const int grid = (rows + 7) / 8;
+  if (kind == 0) {
+    layernorm_ivit_requant_kernel<NPL><<<grid, 256, 0, st>>>(x, out, rows, s_in, bias_int, sf, mult, qmin, qmax);
+  } else {
+    const float sp = ldexpf(1.f, static_cast<int>(shift));
+    layernorm_ibert_requant_kernel<NPL><<<grid, 256, 0, st>>>(x, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp,
+                                                             1.f / sp, use_int_sqrt);
+  }
+  return check_launch("layernorm_requant_kernel");
+}
+
+extern "C" int ivit_layernorm_requant_i8(int kind, const int8_t* x, int8_t* out, int rows, int C, float s_in,
+                                         const float* bias_int, const float* sf, const double* mult, int qmin,
+                                         int qmax, float shift, int use_int_sqrt, void* stream) {
+  if (rows <= 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define IVIT_LN_CASE(c)                                                                                          \
+  case c:                                                                                                        \
+    return launch_ln<c / 32>(kind, x, out, rows, s_in, bias_int, sf, mult, qmin, qmax, shift, use_int_sqrt, st);
+  switch (C) {
+    IVIT_LN_CASE(96)
+    IVIT_LN_CASE(128)
+    IVIT_LN_CASE(192)
+    IVIT_LN_CASE(384)
+    IVIT_LN_CASE(768)
+    IVIT_LN_CASE(1024)
+    default:
+      return fail(IVIT_ERR_UNSUPPORTED, "layernorm: C must be one of 96,128,192,384,768,1024");
+  }
+#undef IVIT_LN_CASE
+}
+
+static GeluIvitParams make_gelu_ivit(float s_in, int output_bit) {
+  GeluIvitParams g;
+  g.s_in = s_in;
+  const float s_sig = s_in * 1.702f;                 // ivit_modules.py:108 (float32 * python float)
+  g.ex.x0 = floorf(-1.0f / s_sig);                   // :94
+  g.ex.n = 23;
+  g.ex.nx0 = 23.f * g.ex.x0;                         // :95
+  g.two31m1 = 2147483648.f;                          // float32(2^31 - 1)
+  g.inv_shift = 1.f / ldexpf(1.f, 31 - output_bit + 1);
+  return g;
+}
+
+static GeluIbertParams make_gelu_ibert(float s_in) {
+  GeluIbertParams g;
+  g.s_in = s_in;
+  const float k = 1.4142f;
+  const double c0 = -0.2888, c1 = -1.769, c2 = 1.0 / c0;   // ibert_modules.py:194-195 (python floats)
+  const float s = s_in / k;                                // :228
+  g.b_int = floorf(static_cast<float>(c1) / s);            // :205
+  g.c_int = floorf(static_cast<float>(c2) / (s * s));      // :206
+  float s_erf = (s * s) * static_cast<float>(c0);          // :214
+  s_erf = s_erf * 64.f;                                    // :216
+  g.shift = floorf(1.0f / s_erf);                          // :230
+  g.s_out = s_in * s_erf / 2.f;                            // :233
+  return g;
+}
+
+extern "C" int ivit_gelu_lut_build(int kind, int8_t* lut, float s_in, int output_bit, double mult_out, int qmin,
+                                   int qmax, float* s_gelu_out_host, void* stream) {
+  GeluIvitParams gi = make_gelu_ivit(s_in, output_bit);
+  GeluIbertParams gb = make_gelu_ibert(s_in);
+  const float s_out = (kind == 0) ? s_in * (1.f / ldexpf(1.f, output_bit - 1)) : gb.s_out;   // ivit :121,:124
+  if (s_gelu_out_host) *s_gelu_out_host = s_out;
+  gelu_lut_build_kernel<<<256, 256, 0, static_cast<cudaStream_t>(stream)>>>(lut, kind, gi, gb, mult_out, s_out, qmin,
+                                                                            qmax);
+  return check_launch("gelu_lut_build_kernel");
+}
+
+extern "C" int ivit_gelu_ivit_raw_table(float* out65536, float s_in, int output_bit, void* stream) {
+  gelu_ivit_raw_kernel<<<256, 256, 0, static_cast<cudaStream_t>(stream)>>>(out65536, make_gelu_ivit(s_in, output_bit));
+  return check_launch("gelu_ivit_raw_kernel");
+}
+
+extern "C" int ivit_gelu_lut_apply_i8(const int8_t* x, int8_t* out, const int8_t* lut, int rows, int C,
+                                      void* stream) {
+  if (rows <= 0) return 0;
+  if (C % 16 != 0 || C > 3072) return fail(IVIT_ERR_UNSUPPORTED, "gelu: C % 16 == 0 and C <= 3072 required");
+  gelu_lut_apply_kernel<<<(rows + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, out, lut, rows, C);
+  return check_launch("gelu_lut_apply_kernel");
+}
+
+extern "C" int ivit_requant_i32_i8(const int32_t* z, const float* s_in, const double* mult, int per_channel,
+                                   const int8_t* identity, double mult_id, int8_t* out, int64_t rows, int C,
+                                   int qmin, int qmax, void* stream) {
+  const long long n = rows * C;
+  if (n <= 0) return 0;
+  requant_i32_kernel<<<ew_grid(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      z, s_in, mult, per_channel, identity, mult_id, out, rows, C, qmin, qmax);
+  return check_launch("requant_i32_kernel");
+}
+
+extern "C" int ivit_dequant_i8_f32(const int8_t* q, float scale, float* out, int64_t n, void* stream) {
+  if (n <= 0) return 0;
+  dequant_i8_kernel<<<ew_grid(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(q, scale, out, n);
+  return check_launch("dequant_i8_kernel");
+}
+
+extern "C" int ivit_fill_cls_rows_i8(int8_t* out, const int8_t* cls_row, int B, int N, int C, void* stream) {
+  if (B * C <= 0) return 0;
+  fill_cls_rows_kernel<<<(B * C + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(out, cls_row, B, N, C);
+  return check_launch("fill_cls_rows_kernel");
+}
