@@ -1,0 +1,339 @@
+// Fused integer attention for one (image, head, 128-query tile):
+//
+//   S = Q K^T            tcgen05 kind::i8, INT32 in TMEM          (QuantMatMul, quant_modules.py:404-409)
+//   c = qact_attn1(S)    dyadic requant, scalar ratio              (vit_quant.py:74-76)
+//   P = IntSoftmax(c)    Shiftmax (ivit_modules.py:150-179) or I-BERT int-exp (ibert_modules.py:275-319)
+//   O = P V              tcgen05 kind::i8 (u8 x s8), V consumed MN-major straight from its [token][hd] layout
+//   out = qact2(O)       dyadic requant, stored head-interleaved [B,N,H*hd] (vit_quant.py:83-85)
+//
+// The N x N score tile never leaves the SM: it lives in TMEM (256 columns), each of the 128
+// threads owns one query row (thread = TMEM lane), so row max / row sum need no shuffles, and
+// the float32 row sum follows torch's CPU order exactly (intmath.cuh).  TMEM doubles as the
+// scratch for the per-row intermediates between the three softmax passes.
+#include <cuda.h>
+#include <cstdio>
+
+#include "intmath.cuh"
+#include "ivit_b200.h"
+#include "ptx.cuh"
+
+namespace ivit {
+int fail(int code, const char* msg);
+int check_launch(const char* what);
+int make_tmap_2d_u8(CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows, uint64_t ld, uint32_t box_cols,
+                    uint32_t box_rows, CUtensorMapSwizzle swz);
+
+struct AttnArgs {
+  int B, N, H;
+  int NKP;        // N rounded up to 16: columns of S (MMA1 N)
+  int KP2;        // N rounded up to 32: K extent of P.V
+  int8_t* out;
+  uint8_t* probs;  // optional debug tap [B,H,N,N]
+  ivit_attention_params_t p;
+  // derived on the host with float32 arithmetic, mirroring the reference's scalar ops
+  float x0, nx0;              // ivit: floor(-1/s), 15*x0 ; ibert: floor(-0.6931/s), 30*x0
+  float b_int, c_int;         // ibert polynomial (ibert_modules.py:277-278)
+  float exp_scale;            // ibert: 0.35815147*s^2/2^30 (:282,:294)
+  float num;                  // 2^31 (ivit, float32(2^31-1)) or 2^32 (ibert)
+  float out_shift;            // 2^-(31-ob+1) or 2^-(32-ob+1)
+};
+
+constexpr int HD = 64;
+
+// exp term of one score, to be summed over the row.  c, cmax: int8 codes of qact_attn1.
+__device__ __forceinline__ float softmax_term(int c, float xmax, const AttnArgs& a) {
+  const float xi = x_eff(static_cast<float>(c), a.p.s_attn);       // x / s, un-rounded
+  const float d = __fsub_rn(xi, xmax);                             // x_int - max
+  if (a.p.kind == 0) {
+    ExpShiftParams ep;
+    ep.x0 = a.x0; ep.nx0 = a.nx0; ep.n = 15;
+    return exp_shift(d, ep);                                       // ivit_modules.py:150-162
+  }
+  // ibert_modules.py:285-295 int_exp, then :310-311 inner QuantAct(16) and its un-rounded recovery
+  const float t = fmaxf(d, a.nx0);
+  const float q = floorf(__fdiv_rn(t, a.x0));
+  const float r = __fsub_rn(t, __fmul_rn(a.x0, q));
+  float z = __fadd_rn(r, a.b_int);
+  z = __fmul_rn(r, z);
+  z = __fadd_rn(z, a.c_int);
+  const float e = fmaxf(floorf(__fmul_rn(z, pow2i(30 - static_cast<int>(q)))), 0.f);
+  // QuantAct(16)(exp_int, exp_scale): the reference passes the *integers* as the value
+  const float zi = rintf(__fdiv_rn(e, a.exp_scale));                              // quant_utils.py:220
+  double rr = requant_d(static_cast<double>(zi), a.p.mult_exp16);                 // :229-230
+  rr = fmin(fmax(rr, -32768.0), 32767.0);                                         // :247-249
+  return x_eff(static_cast<float>(rr), a.p.s_exp16);                              // ibert_modules.py:311
+}
+
+__global__ void __launch_bounds__(128)
+attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                    const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sP = smem;                       // 2 x [128 rows x 128 B], SWIZZLE_128B (written by threads)
+  uint8_t* sQ = smem + 32768;               // [128 x 64 B]  SWIZZLE_64B (TMA)
+  uint8_t* sK = sQ + 8192;                  // [<=256 x 64 B]
+  uint8_t* sV = sK + 16384;                 // [<=256 x 64 B]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 16384);   // qk, v, s, o
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int mt = blockIdx.x;
+  const int b = blockIdx.y / a.H, h = blockIdx.y % a.H;
+  const int C = a.H * HD;
+  const int N = a.N;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 4; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(&bars[0], 128 * HD + a.NKP * HD);
+    tma_load_2d(sQ, &tmQ, &bars[0], h * HD, b * N + mt * 128);
+    tma_load_2d(sK, &tmK, &bars[0], C + h * HD, b * N);
+    mbar_arrive_expect_tx(&bars[1], a.KP2 * HD);
+    tma_load_2d(sV, &tmV, &bars[1], 2 * C + h * HD, b * N);
+    // S = Q K^T : A, B K-major, 64-byte rows (SWIZZLE_64B: 8-row groups 512 B apart)
+    mbar_wait(&bars[0], 0);
+    tc_fence_after();
+    const uint32_t idesc1 = make_idesc_i8(128, a.NKP, true, true, false, false);
+#pragma unroll
+    for (int k = 0; k < HD / 32; ++k) {
+      const uint64_t da = make_smem_desc(smem_u32(sQ) + k * 32, 16, 512, kLayoutSW64);
+      const uint64_t db = make_smem_desc(smem_u32(sK) + k * 32, 16, 512, kLayoutSW64);
+      mma_i8_ss(tmem_base, da, db, idesc1, k != 0 ? 1u : 0u);
+    }
+    tc_commit(&bars[2]);
+  }
+  __syncwarp();
+
+  // ---------------------------------------------------------------- softmax, thread = query row
+  mbar_wait(&bars[2], 0);
+  tc_fence_after();
+  const int row = mt * 128 + warp * 32 + lane;          // token index within the image
+  const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+  const int nchunks = (N + 31) / 32;
+
+  // pass 1: qact_attn1 requant, row max; codes go back to TMEM
+  int cmax = -1 << 30;
+  for (int ci = 0; ci < nchunks; ++ci) {
+    uint32_t v[32];
+    tmem_ld32(t_row + ci * 32, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      int c = clampi(requant_i32_fast(static_cast<int>(v[j]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
+      if (ci * 32 + j < N) cmax = max(cmax, c);
+      v[j] = static_cast<uint32_t>(c);
+    }
+    uint32_t lo[16], hi[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { lo[j] = v[j]; hi[j] = v[16 + j]; }
+    tmem_st16(t_row + ci * 32, lo);
+    tmem_st16(t_row + ci * 32 + 16, hi);
+  }
+  tmem_st_wait();
+  const float xmax = x_eff(static_cast<float>(cmax), a.p.s_attn);   // max of un-rounded x/s (monotone in code)
+
+  // pass 2: exp terms, float32 row sum in torch's CPU order (8-wide vectors x 4 accumulators)
+  const int nvec = N / 8, size_ilp = nvec / 4;
+  float acc[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) acc[j] = 0.f;
+  float p8[8];
+  float tail = 0.f;
+  for (int ci = 0; ci < nchunks; ++ci) {
+    uint32_t v[32];
+    tmem_ld32(t_row + ci * 32, v);
+    tmem_ld_wait();
+    float e[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      e[j] = (ci * 32 + j < N) ? softmax_term(static_cast<int>(v[j]), xmax, a) : 0.f;
+    if (ci < size_ilp) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) acc[j] = __fadd_rn(acc[j], e[j]);
+    }
+    if (ci == size_ilp) {
+      // last, partial chunk: left-over whole vectors go to accumulator row 0 (before the rows
+      // are merged), the n%8 tail is summed separately
+#pragma unroll
+      for (int l = 0; l < 8; ++l) p8[l] = acc[l];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int col = ci * 32 + j;
+        if (col < nvec * 8) p8[j & 7] = __fadd_rn(p8[j & 7], e[j]);
+        else if (col < N) tail = __fadd_rn(tail, e[j]);
+      }
+    }
+    uint32_t lo[16], hi[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { lo[j] = __float_as_uint(e[j]); hi[j] = __float_as_uint(e[16 + j]); }
+    tmem_st16(t_row + ci * 32, lo);
+    tmem_st16(t_row + ci * 32 + 16, hi);
+  }
+  tmem_st_wait();
+  if (nchunks == size_ilp) {
+#pragma unroll
+    for (int l = 0; l < 8; ++l) p8[l] = acc[l];
+  }
+#pragma unroll
+  for (int k = 1; k < 4; ++k)
+#pragma unroll
+    for (int l = 0; l < 8; ++l) p8[l] = __fadd_rn(p8[l], acc[8 * k + l]);
+  float sum = tail;
+#pragma unroll
+  for (int l = 0; l < 8; ++l) sum = __fadd_rn(sum, p8[l]);
+  if (a.p.kind == 0) sum = fminf(sum, 2147483648.f);               // ivit_modules.py:173
+  const float factor = floorf(__fdiv_rn(a.num, sum));              // :174 / ibert :314
+
+  // pass 3: probabilities -> u8 operand tile in shared memory (K-major, SWIZZLE_128B)
+  const int r_loc = warp * 32 + lane;
+  const int pchunks = (a.KP2 + 31) / 32;
+  for (int ci = 0; ci < pchunks; ++ci) {
+    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (ci < nchunks) {
+      uint32_t v[32];
+      tmem_ld32(t_row + ci * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float pf = floorf(__fmul_rn(__fmul_rn(__uint_as_float(v[j]), factor), a.out_shift));   // :175 / :315
+        const uint32_t pc = (ci * 32 + j < N) ? static_cast<uint32_t>(static_cast<int>(pf)) & 0xffu : 0u;
+        w[j >> 2] |= pc << (8 * (j & 3));
+      }
+      if (a.probs != nullptr && row < N) {
+        uint8_t* pr = a.probs + ((static_cast<long long>(blockIdx.y) * N + row) * N) + ci * 32;
+        for (int j = 0; j < 32 && ci * 32 + j < N; ++j) pr[j] = static_cast<uint8_t>(w[j >> 2] >> (8 * (j & 3)));
+      }
+    }
+    // 32 bytes = two 16-byte units of this row's 128-byte swizzle line
+    const int col = ci * 32;
+    uint8_t* base = sP + (col >> 7) * 16384 + (r_loc >> 3) * 1024 + (r_loc & 7) * 128;
+    const int u0 = (col & 127) >> 4;
+    *reinterpret_cast<int4*>(base + ((u0 ^ (r_loc & 7)) << 4)) = make_int4(w[0], w[1], w[2], w[3]);
+    *reinterpret_cast<int4*>(base + (((u0 + 1) ^ (r_loc & 7)) << 4)) = make_int4(w[4], w[5], w[6], w[7]);
+  }
+  fence_proxy_async_smem();     // generic-proxy smem writes -> visible to tcgen05.mma
+  tc_fence_before();
+  __syncthreads();
+
+  // ---------------------------------------------------------------- O = P V
+  if (threadIdx.x == 0) {
+    mbar_wait(&bars[1], 0);
+    tc_fence_after();
+    const uint32_t idesc2 = make_idesc_i8(128, HD, false, true, false, true);   // A u8 K-major, B s8 MN-major
+    const int ksteps = a.KP2 / 32;
+    for (int k = 0; k < ksteps; ++k) {
+      const uint32_t pa = smem_u32(sP) + (k >> 2) * 16384 + (k & 3) * 32;
+      const uint64_t da = make_smem_desc(pa, 16, 1024, kLayoutSW128);
+      // V tile [token][64 B]: MN-major, one 64-byte swizzle atom wide, 8-token groups 512 B apart
+      const uint64_t db = make_smem_desc(smem_u32(sV) + k * 32 * HD, 512, 512, kLayoutSW64);
+      mma_i8_ss(tmem_base, da, db, idesc2, k != 0 ? 1u : 0u);
+    }
+    tc_commit(&bars[3]);
+  }
+  __syncwarp();
+  mbar_wait(&bars[3], 0);
+  tc_fence_after();
+  {
+    uint32_t o0[32], o1[32];
+    tmem_ld32(t_row, o0);
+    tmem_ld32(t_row + 32, o1);
+    tmem_ld_wait();
+    if (row < N && a.out != nullptr) {
+      uint32_t w[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) w[j] = 0;
+#pragma unroll
+      for (int j = 0; j < 64; ++j) {
+        const int z = static_cast<int>(j < 32 ? o0[j] : o1[j - 32]);
+        const int c = clampi(requant_i32_fast(z, a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
+        w[j >> 2] |= (static_cast<uint32_t>(c) & 0xffu) << (8 * (j & 3));
+      }
+      int8_t* o = a.out + (static_cast<long long>(b) * N + row) * C + h * HD;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        *reinterpret_cast<int4*>(o + 16 * j) = make_int4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 256);
+}
+
+static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int N, int H, int hd,
+                            const ivit_attention_params_t* p, cudaStream_t st) {
+  if (!p) return fail(IVIT_ERR_BAD_ARG, "attention: params NULL");
+  if (hd != HD) return fail(IVIT_ERR_UNSUPPORTED, "attention: head_dim must be 64");
+  if (N < 1 || N > 256) return fail(IVIT_ERR_UNSUPPORTED, "attention: 1 <= N <= 256 tokens");
+  if (p->output_bit != 8) return fail(IVIT_ERR_UNSUPPORTED, "attention: 8-bit softmax output only");
+  if (B * H <= 0) return 0;
+  AttnArgs a;
+  a.B = B; a.N = N; a.H = H;
+  a.NKP = (N + 15) / 16 * 16;
+  a.KP2 = (N + 31) / 32 * 32;
+  a.out = out; a.probs = probs; a.p = *p;
+  const float s = p->s_attn;
+  if (p->kind == 0) {
+    a.x0 = floorf(-1.0f / s);                          // ivit_modules.py:154
+    a.nx0 = 15.f * a.x0;                               // :155
+    a.b_int = a.c_int = a.exp_scale = 0.f;
+    a.num = 2147483648.f;                              // float32(2^31 - 1)
+    a.out_shift = 1.f / ldexpf(1.f, 31 - p->output_bit + 1);
+  } else {
+    const double c0 = 0.35815147, c1 = 0.96963238 / c0, c2 = 1.0 / c0;   // ibert_modules.py:265-267
+    a.x0 = floorf(static_cast<float>(-0.6931) / s);    // :287
+    a.nx0 = 30.f * a.x0;                               // :288
+    a.b_int = floorf(static_cast<float>(c1) / s);      // :277
+    a.c_int = floorf(static_cast<float>(c2) / (s * s));   // :278
+    a.exp_scale = (static_cast<float>(c0) * (s * s)) / 1073741824.f;     // :282, :294
+    a.num = 4294967296.f;                              // 2^32 (:314)
+    a.out_shift = 1.f / ldexpf(1.f, 32 - p->output_bit + 1);
+  }
+  const int C = H * hd;
+  CUtensorMap tq, tk, tv;
+  int rc;
+  const uint64_t rows = static_cast<uint64_t>(B) * N, cols = 3ull * C;
+  if ((rc = make_tmap_2d_u8(&tq, qkv, cols, rows, cols, HD, 128, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+  if ((rc = make_tmap_2d_u8(&tk, qkv, cols, rows, cols, HD, a.NKP, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+  if ((rc = make_tmap_2d_u8(&tv, qkv, cols, rows, cols, HD, a.KP2, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+  const size_t smem = 1024 + 32768 + 8192 + 16384 + 16384 + 64;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(attention_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
+    attr_set = true;
+  }
+  dim3 grid((N + 127) / 128, B * H);
+  attention_i8_kernel<<<grid, 128, smem, st>>>(tq, tk, tv, a);
+  return check_launch("attention_i8_kernel");
+}
+
+}  // namespace ivit
+
+using namespace ivit;
+
+extern "C" int ivit_attention_i8(const int8_t* qkv, int8_t* out, int B, int N, int H, int hd,
+                                 const ivit_attention_params_t* p, void* stream) {
+  return attention_launch(qkv, out, nullptr, B, N, H, hd, p, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ivit_attention_probs_i8(const int8_t* qkv, uint8_t* probs, int B, int N, int H, int hd,
+                                       const ivit_attention_params_t* p, void* stream) {
+  // the regular output is discarded into a scratch row range of `probs`' owner: callers pass a
+  // valid `out` through ivit_attention_i8 when they need both; here only the tap is written.
+  return attention_launch(qkv, nullptr, probs, B, N, H, hd, p, static_cast<cudaStream_t>(stream));
+}

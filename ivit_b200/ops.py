@@ -1,0 +1,142 @@
+"""Tensor-level wrappers over the C ABI: allocate outputs with torch, pass raw pointers.
+
+Every function enqueues on torch's current CUDA stream and returns device tensors of integer
+codes.  No function here has a CPU implementation.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _cabi
+from ._cabi import AttentionParams, GemmEpilogue, check, ptr, stream
+
+
+def dev(a, dtype, device) -> torch.Tensor:
+    """numpy host constant -> device tensor (done once per frozen module, then cached by the caller)."""
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dtype=dtype).to(device)
+
+
+def quantize(x: torch.Tensor, inv_scale: float) -> torch.Tensor:
+    x = x.contiguous()
+    out = torch.empty(x.shape, dtype=torch.int8, device=x.device)
+    check(_cabi.load().ivit_quantize_f32_i8(ptr(x), ptr(out), C.c_float(inv_scale), x.numel(), stream()),
+          "ivit_quantize_f32_i8")
+    return out
+
+
+def quantize_patches(x: torch.Tensor, inv_scale: float, patch: int) -> torch.Tensor:
+    x = x.contiguous()
+    B, Cin, H, W = x.shape
+    out = torch.empty((B * (H // patch) * (W // patch), Cin * patch * patch), dtype=torch.int8, device=x.device)
+    check(_cabi.load().ivit_quantize_patches_f32_i8(ptr(x), ptr(out), C.c_float(inv_scale), B, Cin, H, W, patch,
+                                                    stream()), "ivit_quantize_patches_f32_i8")
+    return out
+
+
+def layernorm_requant(kind: int, x: torch.Tensor, s_in: float, bias_int: torch.Tensor, sf: torch.Tensor,
+                      mult: torch.Tensor, qmin: int, qmax: int, shift: float = 0.0,
+                      use_int_sqrt: bool = False) -> torch.Tensor:
+    assert x.dtype == torch.int8 and x.is_contiguous()
+    Cdim = x.shape[-1]
+    rows = x.numel() // Cdim
+    out = torch.empty_like(x)
+    check(_cabi.load().ivit_layernorm_requant_i8(kind, ptr(x), ptr(out), rows, Cdim, C.c_float(s_in), ptr(bias_int),
+                                                 ptr(sf), ptr(mult), qmin, qmax, C.c_float(shift),
+                                                 int(use_int_sqrt), stream()), "ivit_layernorm_requant_i8")
+    return out
+
+
+def gelu_lut_build(kind: int, s_in: float, output_bit: int, mult_out: float, qmin: int, qmax: int, device):
+    lut = torch.empty((256, 256), dtype=torch.int8, device=device)
+    s_out = C.c_float(0.0)
+    check(_cabi.load().ivit_gelu_lut_build(kind, ptr(lut), C.c_float(s_in), output_bit, C.c_double(mult_out), qmin,
+                                           qmax, C.byref(s_out), stream()), "ivit_gelu_lut_build")
+    return lut, np.float32(s_out.value)
+
+
+def gelu_ivit_raw_table(s_in: float, output_bit: int, device) -> torch.Tensor:
+    out = torch.empty((256, 256), dtype=torch.float32, device=device)
+    check(_cabi.load().ivit_gelu_ivit_raw_table(ptr(out), C.c_float(s_in), output_bit, stream()),
+          "ivit_gelu_ivit_raw_table")
+    return out
+
+
+def gelu_lut_apply(x: torch.Tensor, lut: torch.Tensor) -> torch.Tensor:
+    assert x.dtype == torch.int8 and x.is_contiguous()
+    Cdim = x.shape[-1]
+    out = torch.empty_like(x)
+    check(_cabi.load().ivit_gelu_lut_apply_i8(ptr(x), ptr(out), ptr(lut), x.numel() // Cdim, Cdim, stream()),
+          "ivit_gelu_lut_apply_i8")
+    return out
+
+
+def requant_i32(z: torch.Tensor, s_in: torch.Tensor, mult: torch.Tensor, qmin: int, qmax: int,
+                identity: torch.Tensor | None = None, mult_id: float = 0.0) -> torch.Tensor:
+    assert z.dtype == torch.int32 and z.is_contiguous()
+    Cdim = z.shape[-1]
+    out = torch.empty(z.shape, dtype=torch.int8, device=z.device)
+    check(_cabi.load().ivit_requant_i32_i8(ptr(z), ptr(s_in), ptr(mult), int(mult.numel() > 1), ptr(identity),
+                                           C.c_double(mult_id), ptr(out), z.numel() // Cdim, Cdim, qmin, qmax,
+                                           stream()), "ivit_requant_i32_i8")
+    return out
+
+
+def dequant(q: torch.Tensor, scale: float) -> torch.Tensor:
+    q = q.contiguous()
+    out = torch.empty(q.shape, dtype=torch.float32, device=q.device)
+    check(_cabi.load().ivit_dequant_i8_f32(ptr(q), C.c_float(scale), ptr(out), q.numel(), stream()),
+          "ivit_dequant_i8_f32")
+    return out
+
+
+def fill_cls_rows(out: torch.Tensor, cls_row: torch.Tensor):
+    B, N, Cdim = out.shape
+    check(_cabi.load().ivit_fill_cls_rows_i8(ptr(out), ptr(cls_row), B, N, Cdim, stream()), "ivit_fill_cls_rows_i8")
+
+
+def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=None, s_in=None, qmin=-128, qmax=127,
+         mult2=0.0, mult_id=0.0, qmin2=-128, qmax2=127, identity=None, scale_out=None, out=None, out_rows=None,
+         group=0, out_group_stride=0, out_row_off=0, id_broadcast=False, force_slow=False,
+         simple=False) -> torch.Tensor:
+    """C = A[M,K] @ W[N,K]^T with a fused epilogue (see include/ivit_b200.h)."""
+    assert A.dtype == torch.int8 and W.dtype == torch.int8 and A.dim() == 2 and W.dim() == 2
+    assert A.stride(1) == 1 and W.is_contiguous()
+    M, K = A.shape
+    N = W.shape[0]
+    odt = {_cabi.EPI_ACC32: torch.int32, _cabi.EPI_LOGITS: torch.float32}.get(epilogue, torch.int8)
+    if out is None:
+        out = torch.empty((out_rows if out_rows is not None else M, N), dtype=odt, device=A.device)
+    assert out.dtype == odt and out.stride(-1) == 1
+    e = GemmEpilogue()
+    e.epilogue = epilogue
+    e.bias, e.mult, e.s_in = ptr(bias), ptr(mult), ptr(s_in)
+    e.qmin, e.qmax, e.mult2, e.mult_id, e.qmin2, e.qmax2 = qmin, qmax, mult2, mult_id, qmin2, qmax2
+    e.identity = ptr(identity)
+    e.ld_id = identity.stride(-2) if identity is not None else 0
+    e.scale_out = ptr(scale_out)
+    e.group, e.out_group_stride, e.out_row_off, e.id_broadcast = group, out_group_stride, out_row_off, int(id_broadcast)
+    e.force_slow = int(force_slow)
+    lib = _cabi.load()
+    fn = lib.ivit_gemm_i8_simple if simple else lib.ivit_gemm_i8
+    ldo = out.stride(-2) if out.dim() >= 2 else N
+    check(fn(ptr(A), A.stride(0), ptr(W), M, N, K, ptr(out), ldo, C.byref(e), stream()),
+          "ivit_gemm_i8_simple" if simple else "ivit_gemm_i8")
+    return out
+
+
+def attention(qkv: torch.Tensor, B: int, N: int, H: int, hd: int, params: AttentionParams,
+              want_probs: bool = False):
+    """qkv int8 [B,N,3*H*hd] -> out int8 [B,N,H*hd] (and optionally the softmax codes [B,H,N,N] u8)."""
+    assert qkv.dtype == torch.int8 and qkv.is_contiguous()
+    lib = _cabi.load()
+    out = torch.empty((B, N, H * hd), dtype=torch.int8, device=qkv.device)
+    check(lib.ivit_attention_i8(ptr(qkv), ptr(out), B, N, H, hd, C.byref(params), stream()), "ivit_attention_i8")
+    if not want_probs:
+        return out
+    probs = torch.empty((B, H, N, N), dtype=torch.uint8, device=qkv.device)
+    check(lib.ivit_attention_probs_i8(ptr(qkv), ptr(probs), B, N, H, hd, C.byref(params), stream()),
+          "ivit_attention_probs_i8")
+    return out, probs

@@ -1,0 +1,275 @@
+"""Kernel-level parity (GPU): every C-ABI entry point against the numpy oracle on seeded inputs.
+
+Bar: bit-exact integer codes.  Inputs are sized so the oracle finishes in seconds.
+"""
+import numpy as np
+import pytest
+import torch
+
+from ivit_b200 import _cabi, hostmath as hm, ops
+from oracle import ivit_oracle as O
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+DEV = "cuda"
+
+
+def _cmp(got, exp, name):
+    got = np.asarray(got).astype(np.int64)
+    exp = np.asarray(exp).astype(np.int64)
+    assert got.shape == exp.shape, (name, got.shape, exp.shape)
+    bad = np.argwhere(got != exp)
+    if len(bad):
+        first = [(tuple(int(i) for i in b), int(got[tuple(b)]), int(exp[tuple(b)])) for b in bad[:8]]
+        pytest.fail(f"{name}: {len(bad)}/{got.size} mismatches; first (idx, got, exp): {first}")
+
+
+def _t(a, dtype):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dtype).to(DEV)
+
+
+def test_device_is_blackwell(lib):
+    import ctypes as C
+    ma, mi = C.c_int(0), C.c_int(0)
+    assert lib.ivit_device_sm(C.byref(ma), C.byref(mi)) == 0
+    assert ma.value == 10, f"sm_{ma.value}{mi.value}: these kernels are sm_100a only"
+
+
+def test_quantize_patches():
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((3, 3, 224, 224)).astype(f32) * 1.3
+    s = hm.sym_scale(8, x.min(), x.max()).reshape(1)
+    inv = f32(1.0) / s[0]
+    got = ops.quantize_patches(_t(x, torch.float32), float(inv), 16).cpu().numpy()
+    q = O.sym_quantize(x, 8, s, is_weight=False)
+    exp = q.reshape(3, 3, 14, 16, 14, 16).transpose(0, 2, 4, 1, 3, 5).reshape(3 * 196, 768)
+    _cmp(got, exp, "quantize_patches")
+    got2 = ops.quantize(_t(x, torch.float32), float(inv)).cpu().numpy()
+    _cmp(got2, q, "quantize")
+
+
+def _ln_case(kind, C, rows, seed, s_in=0.0371, ties=True, neg=False, use_int_sqrt=False):
+    rng = np.random.default_rng(seed)
+    q = np.clip(np.rint(rng.standard_normal((1, rows, C)) * 35), -128, 127).astype(np.int64)
+    if ties:   # force exact mean ties k + 1/2 on a third of the rows (hazard H6)
+        for r in range(0, rows, 3):
+            k = int(rng.integers(-3, 4))
+            d = k * C + C // 2 - int(q[0, r].sum())
+            idx = rng.integers(0, C, size=abs(d))
+            np.add.at(q[0, r], idx, np.sign(d))
+            q[0, r] = np.clip(q[0, r], -128, 127)
+    s_in = f32(s_in)
+    w = (rng.random(C) + 0.5).astype(f32)
+    if neg:
+        w[rng.random(C) < 0.1] *= -1
+    b = (rng.standard_normal(C) * 0.1).astype(f32)
+    x = (q.astype(f32) * s_in).astype(f32)
+    if kind == 0:
+        y, sf, _ = O.ivit_layernorm(x, np.array([s_in]), w, b)
+    else:
+        y, sf, _ = O.ibert_layernorm(x, np.array([s_in]), w, b, shift=0.0, use_int_sqrt=use_int_sqrt)
+    x_max = np.array([np.abs(y).max() * 0.7], dtype=f32)      # some saturation
+    _, s_out, codes = O.quant_act(y, 8, -x_max, x_max, pre_scale=sf)
+    p = hm.layernorm_params(w, b, C)
+    assert np.array_equal(p["sf"], sf)
+    mult = hm.dyadic_mult(p["sf"], s_out)
+    got = ops.layernorm_requant(kind, _t(q[0], torch.int8), float(s_in), _t(p["bias_int"], torch.float32),
+                                _t(p["sf"], torch.float32), _t(mult, torch.float64), -128, 127,
+                                use_int_sqrt=use_int_sqrt).cpu().numpy()
+    _cmp(got, codes[0], f"layernorm kind={kind} C={C}")
+
+
+@pytest.mark.parametrize("C", [192, 384, 768])
+def test_layernorm_ivit(C):
+    _ln_case(0, C, 301, seed=C)
+    _ln_case(0, C, 64, seed=C + 1, s_in=0.0123, neg=True)
+
+
+@pytest.mark.parametrize("C", [192, 384, 768])
+def test_layernorm_ibert(C):
+    _ln_case(1, C, 301, seed=C)
+    _ln_case(1, C, 64, seed=C + 1, s_in=0.113, neg=True)
+
+
+@pytest.mark.parametrize("s_in", [0.0371, 0.0123, 0.113, 0.0052])
+def test_gelu_ivit_table_exhaustive(s_in):
+    """All 256 x 256 (row max, code) pairs of ShiftGELU + mlp.qact1 (cf. the reference's own
+    256-code sweep, scripts/gelu_approx_analysis.py:73-77)."""
+    s_in = f32(s_in)
+    codes = np.arange(-128, 128)
+    q = np.minimum(codes[None, :], codes[:, None])          # row mx holds min(q, mx): its max is mx
+    x = (q.astype(f32) * s_in).astype(f32)
+    y, s_g, yi = O.ivit_gelu(x, np.array([s_in]))
+    x_max = np.array([np.abs(y).max() * 0.8], dtype=f32)
+    _, s_out, exp = O.quant_act(y, 8, -x_max, x_max, pre_scale=s_g)
+    mult = float(hm.dyadic_mult(s_g, s_out).reshape(-1)[0])
+    lut, s_g_dev = ops.gelu_lut_build(0, float(s_in), 8, mult, -128, 127, DEV)
+    assert f32(s_g_dev) == s_g[0]
+    got = lut.cpu().numpy().astype(np.int64)
+    got_used = np.take_along_axis(got, (q + 128), axis=1)
+    _cmp(got_used, exp, "gelu ivit lut")
+    raw = ops.gelu_ivit_raw_table(float(s_in), 8, DEV).cpu().numpy()
+    _cmp(np.take_along_axis(raw, (q + 128), axis=1), yi, "gelu ivit raw")
+    # apply kernel on random rows
+    rng = np.random.default_rng(1)
+    xr = np.clip(np.rint(rng.standard_normal((77, 1536)) * 30), -128, 100).astype(np.int8)
+    outk = ops.gelu_lut_apply(_t(xr, torch.int8), lut).cpu().numpy()
+    yr, sgr, _ = O.ivit_gelu((xr.astype(f32) * s_in).astype(f32), np.array([s_in]))
+    _, _, expr = O.quant_act(yr, 8, -x_max, x_max, pre_scale=sgr)
+    _cmp(outk, expr, "gelu ivit apply")
+
+
+@pytest.mark.parametrize("s_in", [0.0371, 0.0123, 0.113])
+def test_gelu_ibert_table(s_in):
+    s_in = f32(s_in)
+    codes = np.arange(-128, 128)
+    x = (codes.astype(f32) * s_in).astype(f32).reshape(1, 256)
+    y, s_g, _ = O.ibert_gelu(x, np.array([s_in]))
+    x_max = np.array([np.abs(y).max() * 0.8], dtype=f32)
+    _, s_out, exp = O.quant_act(y, 8, -x_max, x_max, pre_scale=s_g)
+    mult = float(hm.dyadic_mult(s_g, s_out).reshape(-1)[0])
+    lut, s_g_dev = ops.gelu_lut_build(1, float(s_in), 8, mult, -128, 127, DEV)
+    assert f32(s_g_dev) == s_g[0]
+    _cmp(lut.cpu().numpy()[200], exp[0], "gelu ibert lut")
+
+
+def _gemm_case(M, N, K, seed, epilogue, group=0):
+    rng = np.random.default_rng(seed)
+    A = rng.integers(-128, 128, size=(M, K)).astype(np.int8)
+    W = rng.integers(-127, 128, size=(N, K)).astype(np.int8)
+    bias = rng.integers(-20000, 20000, size=N).astype(np.int32)
+    acc = (A.astype(np.float64) @ W.astype(np.float64).T + bias).astype(np.int64)
+    s_in = (rng.random(N) * 2e-5 + 1e-5).astype(f32)                 # per-channel s_w*s_x
+    kw = dict(bias=_t(bias, torch.int32))
+    exp = None
+    if epilogue == _cabi.EPI_ACC32:
+        exp = acc
+    elif epilogue == _cabi.EPI_LOGITS:
+        exp = (acc.astype(f32) * s_in).astype(f32)
+        kw["scale_out"] = _t(s_in, torch.float32)
+    else:
+        y = (acc.astype(f32) * s_in).astype(f32)
+        x_max = np.array([np.abs(y).max() * 0.6], dtype=f32)
+        _, s1, c1 = O.quant_act(y.reshape(1, M, N), 8, -x_max, x_max, pre_scale=s_in)
+        kw.update(mult=_t(hm.dyadic_mult(s_in, s1), torch.float64), s_in=_t(s_in, torch.float32))
+        exp = c1[0]
+        if epilogue == _cabi.EPI_RESIDUAL:
+            rows_id = M if group == 0 else group + 1
+            idc = rng.integers(-128, 128, size=(rows_id, N)).astype(np.int8)
+            s_id = f32(0.021)
+            x1 = (c1 * s1).astype(f32)
+            if group == 0:
+                ident = (idc.astype(f32) * s_id).astype(f32).reshape(1, M, N)
+            else:
+                ident = np.tile((idc[1:].astype(f32) * s_id).astype(f32), (M // group, 1)).reshape(1, M, N)
+            x_max2 = np.array([np.abs(x1).max() * 0.9], dtype=f32)
+            _, s2, c2 = O.quant_act(x1, 8, -x_max2, x_max2, pre_scale=s1, identity=ident,
+                                    identity_scale=np.array([s_id]))
+            exp = c2[0]
+            kw.update(mult2=float(hm.dyadic_mult(s1, s2).reshape(-1)[0]),
+                      mult_id=float(hm.dyadic_mult(np.array([s_id]), s2).reshape(-1)[0]),
+                      identity=_t(idc, torch.int8))
+    out_rows = None
+    if group:
+        kw.update(group=group, out_group_stride=group + 1, out_row_off=1, id_broadcast=True)
+        out_rows = (M // group) * (group + 1)
+    res = {}
+    for simple in (True, False):
+        out = None
+        if out_rows:
+            odt = torch.int8
+            out = torch.full((out_rows, N), 99, dtype=odt, device=DEV)
+        got = ops.gemm(_t(A, torch.int8), _t(W, torch.int8), epilogue, simple=simple, out=out, **kw).cpu().numpy()
+        if group:
+            got = got.reshape(M // group, group + 1, N)[:, 1:].reshape(M, N)
+        res[simple] = got
+    name = f"gemm M={M} N={N} K={K} epi={epilogue}"
+    if epilogue == _cabi.EPI_LOGITS:
+        assert np.array_equal(res[True], exp), name + " simple"
+        assert np.array_equal(res[False], exp), name + " tcgen05"
+    else:
+        _cmp(res[True], exp, name + " simple")
+        _cmp(res[False], exp, name + " tcgen05")
+
+
+@pytest.mark.parametrize("shape", [(128, 128, 128), (300, 384, 384), (394, 1152, 192), (256, 384, 1536),
+                                   (130, 1000, 384), (1000, 192, 768)])
+def test_gemm_acc32(shape):
+    _gemm_case(*shape, seed=1, epilogue=_cabi.EPI_ACC32)
+
+
+@pytest.mark.parametrize("shape", [(300, 384, 384), (394, 1152, 192), (256, 1536, 384)])
+def test_gemm_requant(shape):
+    _gemm_case(*shape, seed=2, epilogue=_cabi.EPI_REQUANT)
+
+
+@pytest.mark.parametrize("shape", [(300, 384, 384), (394, 192, 768), (256, 384, 1536)])
+def test_gemm_residual(shape):
+    _gemm_case(*shape, seed=3, epilogue=_cabi.EPI_RESIDUAL)
+
+
+def test_gemm_patch_embed_remap():
+    _gemm_case(196 * 3, 192, 768, seed=4, epilogue=_cabi.EPI_RESIDUAL, group=196)
+
+
+def test_gemm_logits():
+    _gemm_case(130, 1000, 384, seed=5, epilogue=_cabi.EPI_LOGITS)
+
+
+def _attention_case(kind, B, N, H, seed, s_qkv=0.05):
+    rng = np.random.default_rng(seed)
+    hd = 64
+    C = H * hd
+    qkv = np.clip(np.rint(rng.standard_normal((B, N, 3, H, hd)) * 40), -128, 127).astype(np.int8)
+    s1 = np.array([s_qkv], dtype=f32)
+    x = (qkv.astype(f32) * s1).astype(f32)
+    t = x.transpose(2, 0, 3, 1, 4)
+    q, k, v = t[0], t[1], t[2]
+    attn, s, _ = O.quant_matmul(q, s1, np.swapaxes(k, -2, -1), s1)
+    sc = f32(hd ** -0.5)
+    attn = (attn * sc).astype(f32)
+    s = (s * sc).astype(f32)
+    a_max = np.array([np.abs(attn).max() * 0.5], dtype=f32)
+    attn_q, s_a, attn_codes = O.quant_act(attn, 8, -a_max, a_max, pre_scale=s)
+    p = _cabi.AttentionParams()
+    p.kind, p.output_bit = kind, 8
+    p.mult_attn = float(hm.dyadic_mult(s, s_a).reshape(-1)[0])
+    p.qmin_attn, p.qmax_attn = -128, 127
+    p.s_attn = float(s_a[0])
+    if kind == 0:
+        sm, s_sm, sm_codes = O.ivit_softmax(attn_q, s_a, 8)
+    else:
+        # calibrate the inner QuantAct(16) range the way the reference would: max of exp_int values
+        xi = attn_q / s_a
+        xi = xi - xi.max(axis=-1, keepdims=True)
+        x0 = np.floor(f32(-0.6931) / s_a)
+        e_max = f32(1.0 / 0.35815147) / (s_a * s_a) * f32(2.0 ** 30)
+        amax = np.array([e_max[0]], dtype=f32)
+        sm, s_sm, sm_codes = O.ibert_softmax(attn_q, s_a, 8, -amax, amax)
+        s16 = O.sym_scale(16, -amax, amax)
+        exp_scale = (f32(0.35815147) * (s_a * s_a) / f32(2 ** 30)).astype(f32)
+        p.mult_exp16 = float(hm.dyadic_mult(exp_scale, s16).reshape(-1)[0])
+        p.s_exp16 = float(s16.reshape(-1)[0])
+    o, s_o, _ = O.quant_matmul(sm, s_sm, v, s1)
+    o = o.transpose(0, 2, 1, 3).reshape(B, N, C)
+    o_max = np.array([np.abs(o).max() * 0.7], dtype=f32)
+    _, s_out, out_codes = O.quant_act(o, 8, -o_max, o_max, pre_scale=s_o)
+    p.mult_out = float(hm.dyadic_mult(s_o, s_out).reshape(-1)[0])
+    p.qmin_out, p.qmax_out = -128, 127
+    out, probs = ops.attention(_t(qkv.reshape(B, N, 3 * C), torch.int8), B, N, H, hd, p, want_probs=True)
+    _cmp(probs.cpu().numpy(), sm_codes, f"attention probs kind={kind}")
+    _cmp(out.cpu().numpy(), out_codes, f"attention out kind={kind}")
+
+
+@pytest.mark.parametrize("N", [197, 64, 49, 256, 130])
+def test_attention_ivit(N):
+    _attention_case(0, 2, N, 3, seed=N)
+
+
+def test_attention_ivit_peaked():
+    _attention_case(0, 2, 197, 2, seed=7, s_qkv=0.2)
+
+
+@pytest.mark.parametrize("N", [197, 49])
+def test_attention_ibert(N):
+    _attention_case(1, 2, N, 3, seed=N + 1)
