@@ -106,3 +106,44 @@ def synth_images(batch: int, cfg: VitConfig, seed: int = 0) -> torch.Tensor:
     g = torch.Generator(device="cpu")
     g.manual_seed(2000 + seed)
     return torch.randn(batch, cfg.in_chans, cfg.img_size, cfg.img_size, generator=g)
+
+
+# ---------------------------------------------------------------------------------------------
+# Calibrated activation ranges.  The frozen plan is a function of (weights, x_min/x_max buffers);
+# for the synthetic weights above those buffers were produced by the reference's own calibration
+# pass (scripts/inference.py:33-91, one forward of `synth_images(4, cfg, seed=1)` with
+# running_stat=True, then freeze_model) and are committed in tests/golden/vit_<case>.npz by
+# oracle/make_golden.py.  A real deployment reads the same buffers from a reference checkpoint.
+# name -> (config, gelu, softmax, layernorm, negate_ln_frac)
+CASES = {
+    "toy_ivit": ("toy", "ivit", "ivit", "ivit", 0.0),
+    "toy_ibert": ("toy", "ibert", "ibert", "ibert", 0.0),
+    "toy_mixed": ("toy", "ivit", "ibert", "ivit", 0.05),
+    "toy_ibert_intsqrt": ("toy", "ibert", "ibert", "ibert_use-int-sqrt_true", 0.0),
+    "deit_tiny_ivit": ("deit_tiny", "ivit", "ivit", "ivit", 0.0),
+    "deit_tiny_ibert": ("deit_tiny", "ibert", "ibert", "ibert", 0.0),
+    "deit_small_ivit": ("deit_small", "ivit", "ivit", "ivit", 0.0),
+    "vit_base_mixed": ("vit_base", "ivit", "ibert", "ivit", 0.0),
+    "deit_base_ibert": ("deit_base", "ibert", "ibert", "ibert", 0.0),
+}
+
+
+def golden_path(case: str) -> str:
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    return os.path.join(root, "tests", "golden", f"vit_{case}.npz")
+
+
+def load_case(case: str):
+    """Returns (cfg, state) for a committed case: seeded weights + the calibrated range buffers
+    (``*.x_min``, ``*.x_max``, ``*.shift``) as float32 numpy arrays, keyed like the reference
+    state_dict.  Also returns the raw fixture (reference logits, tap hashes) as third element."""
+    import numpy as np
+    cfg_name, g, s, l, neg = CASES[case]
+    cfg = CONFIGS[cfg_name].with_layers(gelu=g, softmax=s, layernorm=l)
+    state = {k: v.numpy() for k, v in synth_vit_state(cfg, seed=0, negate_ln_frac=neg).items()}
+    fix = np.load(golden_path(case))
+    for k in fix.files:
+        if k.startswith("range/"):
+            state[k[len("range/"):]] = fix[k].astype(np.float32)
+    return cfg, state, fix

@@ -32,7 +32,9 @@ def build_reference_vit(cfg, state: dict):
     if cfg.name in _FACTORY:
         model = getattr(ref, _FACTORY[cfg.name])(pretrained=False, **kw)
     else:  # e.g. the "toy" config: same class, custom sizes
-        model = ref.VisionTransformer(patch_size=cfg.patch_size, embed_dim=cfg.embed_dim, depth=cfg.depth,
+        import sys
+        vq = sys.modules[ref.__name__ + ".vit_quant"]      # VisionTransformer is not in models.__all__
+        model = vq.VisionTransformer(patch_size=cfg.patch_size, embed_dim=cfg.embed_dim, depth=cfg.depth,
                                       num_heads=cfg.num_heads, mlp_ratio=cfg.mlp_ratio, qkv_bias=True,
                                       img_size=cfg.img_size, num_classes=cfg.num_classes, **kw)
     missing, unexpected = model.load_state_dict({k: torch.as_tensor(v) for k, v in state.items()}, strict=False)
