@@ -43,9 +43,10 @@ int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float inv_scale, i
  * kind 0: ivit_modules.py:30-65 (IVITIntLayerNorm), kind 1: ibert_modules.py:112-158
  * (IBERTIntLayerNorm; shift = its `shift` buffer, use_int_sqrt as the ctor flag), then
  * quant_modules.py:379-387 / quant_utils.py:193-253 (fixedpoint_mul, per-channel ratio).
- * x: int8 [rows, C] codes with scalar scale s_in; bias_int[C], sf[C] (the LN's per-channel
+ * x: int8 [rows, C] codes (row stride ldx bytes: the final `norm` runs on the class-token rows
+ * only, vit_quant.py:302-303) with scalar scale s_in; bias_int[C], sf[C] (the LN's per-channel
  * output scale), mult[C] = m*2^-e of sf[c]/s_out as float64; out int8 [rows, C]. */
-int ivit_layernorm_requant_i8(int kind, const int8_t* x, int8_t* out, int rows, int C, float s_in,
+int ivit_layernorm_requant_i8(int kind, const int8_t* x, int64_t ldx, int8_t* out, int rows, int C, float s_in,
                               const float* bias_int, const float* sf, const double* mult, int qmin, int qmax,
                               float shift, int use_int_sqrt, void* stream);
 

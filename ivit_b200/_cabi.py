@@ -55,7 +55,7 @@ _SIGS = {
     "ivit_quantize_f32_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_int64, C.c_void_p]),
     "ivit_quantize_patches_f32_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_int,
                                                C.c_int, C.c_int, C.c_void_p]),
-    "ivit_layernorm_requant_i8": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
+    "ivit_layernorm_requant_i8": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_float,
                                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
                                             C.c_int, C.c_void_p]),
     "ivit_gelu_lut_build": (C.c_int, [C.c_int, C.c_void_p, C.c_float, C.c_int, C.c_double, C.c_int, C.c_int,

@@ -1,0 +1,64 @@
+"""Public inference call: host images in, host logits out.
+
+``InferenceSession`` owns one ``FrozenVitPlan`` on one GPU and what a serving loop needs around
+it: CUDA-graph replays of the launch sequence, a copy stream, and two pinned-memory-fed staging
+slots so that the host->device copy of chunk i+1 overlaps the forward of chunk i.  This is the
+call ``bench.py`` times as ``e2e`` and the one ``scripts/inference.py:248`` (``model(imgs)`` per
+batch) maps to.  No CPU path: construction fails without a CUDA device and the in-tree library.
+"""
+from __future__ import annotations
+
+import torch
+
+from .plan import FrozenVitPlan
+from .synthetic import VitConfig
+
+
+class InferenceSession:
+    def __init__(self, cfg: VitConfig, state: dict, batch: int, device="cuda", chunks: int = 1):
+        if batch % chunks != 0:
+            raise ValueError("batch must be divisible by chunks")
+        self.plan = FrozenVitPlan(cfg, state, device)
+        self.device = self.plan.device
+        self.batch, self.chunks, self.cb = batch, chunks, batch // chunks
+        self.compute = torch.cuda.Stream(device=self.device)
+        self.copy = torch.cuda.Stream(device=self.device)
+        with torch.cuda.device(self.device):
+            self.slots = [self.plan.capture(self.cb, slot=s) for s in range(2 if chunks > 1 else 1)]
+            self.ready = [torch.cuda.Event() for _ in self.slots]
+            self.consumed = [torch.cuda.Event() for _ in self.slots]
+        self.out_host = torch.empty((batch, cfg.num_classes), dtype=torch.float32).pin_memory()
+        self.h2d_bytes = batch * cfg.in_chans * cfg.img_size * cfg.img_size * 4
+        self.d2h_bytes = batch * cfg.num_classes * 4
+        self.launches_per_infer = sum(self.slots[c % len(self.slots)].launches for c in range(chunks))
+
+    def infer_async(self, images: torch.Tensor) -> torch.Tensor:
+        """Enqueue one batch.  images: float32 [batch,3,H,W] in HOST memory (pinned for an
+        asynchronous copy).  Returns the pinned host logits buffer; valid after ``synchronize()``."""
+        if images.is_cuda:
+            raise ValueError("infer() takes host images; use FrozenVitPlan.forward for device tensors")
+        if images.shape[0] != self.batch:
+            raise ValueError(f"session was built for batch {self.batch}")
+        ns = len(self.slots)
+        for c in range(self.chunks):
+            s = c % ns
+            g = self.slots[s]
+            lo, hi = c * self.cb, (c + 1) * self.cb
+            with torch.cuda.stream(self.copy):
+                self.copy.wait_event(self.consumed[s])          # the slot's previous forward has read it
+                g.static_in.copy_(images[lo:hi], non_blocking=True)
+                self.ready[s].record(self.copy)
+            with torch.cuda.stream(self.compute):
+                self.compute.wait_event(self.ready[s])
+                g.replay()
+                self.consumed[s].record(self.compute)
+                self.out_host[lo:hi].copy_(g.static_out, non_blocking=True)
+        return self.out_host
+
+    def synchronize(self):
+        self.compute.synchronize()
+
+    def infer(self, images: torch.Tensor) -> torch.Tensor:
+        out = self.infer_async(images)
+        self.synchronize()
+        return out

@@ -62,7 +62,7 @@ struct LnSmem {
 // mult[c] = m*2^-e of sf[c]/s_out.
 template <int NPL>  // elements per lane = C/32 (compile-time for unrolling): 6, 12, 24, ...
 __global__ void __launch_bounds__(256)
-layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, int rows, float s_in,
+layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows, float s_in,
                               const float* __restrict__ bias_int, const float* __restrict__ sf,
                               const double* __restrict__ mult, int qmin, int qmax) {
   constexpr int C = NPL * 32;
@@ -70,7 +70,7 @@ layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, int8_t* __restrict__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= rows) return;
-  const int8_t* xr = x + static_cast<long long>(row) * C;
+  const int8_t* xr = x + static_cast<long long>(row) * ldx;
   // coalesced 16-byte loads -> smem
   for (int v = lane; v < C / 16; v += 32)
     *reinterpret_cast<int4*>(&stage[warp][v * 16]) = *reinterpret_cast<const int4*>(xr + v * 16);
@@ -135,7 +135,7 @@ layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, int8_t* __restrict__
 // ibert_modules.py:112-158 followed by QuantAct.  shift_pow = 2^shift, inv_shift_pow = 2^-shift.
 template <int NPL>
 __global__ void __launch_bounds__(256)
-layernorm_ibert_requant_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, int rows, float s_in,
+layernorm_ibert_requant_kernel(const int8_t* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows, float s_in,
                                const float* __restrict__ bias_int, const float* __restrict__ sf,
                                const double* __restrict__ mult, int qmin, int qmax, float shift_pow,
                                float inv_shift_pow, int use_int_sqrt) {
@@ -144,7 +144,7 @@ layernorm_ibert_requant_kernel(const int8_t* __restrict__ x, int8_t* __restrict_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= rows) return;
-  const int8_t* xr = x + static_cast<long long>(row) * C;
+  const int8_t* xr = x + static_cast<long long>(row) * ldx;
   for (int v = lane; v < C / 16; v += 32)
     *reinterpret_cast<int4*>(&stage[warp][v * 16]) = *reinterpret_cast<const int4*>(xr + v * 16);
   __syncwarp();
@@ -367,28 +367,29 @@ extern "C" int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float i
 }
 
 template <int NPL>
-static int launch_ln(int kind, const int8_t* x, int8_t* out, int rows, float s_in, const float* bias_int,
+static int launch_ln(int kind, const int8_t* x, long long ldx, int8_t* out, int rows, float s_in, const float* bias_int,
                      const float* sf, const double* mult, int qmin, int qmax, float shift, int use_int_sqrt,
                      cudaStream_t st) {
   const int grid = (rows + 7) / 8;
   if (kind == 0) {
-    layernorm_ivit_requant_kernel<NPL><<<grid, 256, 0, st>>>(x, out, rows, s_in, bias_int, sf, mult, qmin, qmax);
+    layernorm_ivit_requant_kernel<NPL><<<grid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax);
   } else {
     const float sp = ldexpf(1.f, static_cast<int>(shift));
-    layernorm_ibert_requant_kernel<NPL><<<grid, 256, 0, st>>>(x, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp,
+    layernorm_ibert_requant_kernel<NPL><<<grid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp,
                                                              1.f / sp, use_int_sqrt);
   }
   return check_launch("layernorm_requant_kernel");
 }
 
-extern "C" int ivit_layernorm_requant_i8(int kind, const int8_t* x, int8_t* out, int rows, int C, float s_in,
+extern "C" int ivit_layernorm_requant_i8(int kind, const int8_t* x, int64_t ldx, int8_t* out, int rows, int C, float s_in,
                                          const float* bias_int, const float* sf, const double* mult, int qmin,
                                          int qmax, float shift, int use_int_sqrt, void* stream) {
   if (rows <= 0) return 0;
+  if (ldx % 16 != 0 || ldx < C) return fail(IVIT_ERR_BAD_ARG, "layernorm: row stride must be >= C and a multiple of 16");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define IVIT_LN_CASE(c)                                                                                          \
   case c:                                                                                                        \
-    return launch_ln<c / 32>(kind, x, out, rows, s_in, bias_int, sf, mult, qmin, qmax, shift, use_int_sqrt, st);
+    return launch_ln<c / 32>(kind, x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, shift, use_int_sqrt, st);
   switch (C) {
     IVIT_LN_CASE(96)
     IVIT_LN_CASE(128)

@@ -27,10 +27,12 @@ def quantize(x: torch.Tensor, inv_scale: float) -> torch.Tensor:
     return out
 
 
-def quantize_patches(x: torch.Tensor, inv_scale: float, patch: int) -> torch.Tensor:
+def quantize_patches(x: torch.Tensor, inv_scale: float, patch: int, out: torch.Tensor | None = None) -> torch.Tensor:
     x = x.contiguous()
     B, Cin, H, W = x.shape
-    out = torch.empty((B * (H // patch) * (W // patch), Cin * patch * patch), dtype=torch.int8, device=x.device)
+    if out is None:
+        out = torch.empty((B * (H // patch) * (W // patch), Cin * patch * patch), dtype=torch.int8, device=x.device)
+    assert out.is_contiguous() and out.numel() == x.numel() and out.dtype == torch.int8
     check(_cabi.load().ivit_quantize_patches_f32_i8(ptr(x), ptr(out), C.c_float(inv_scale), B, Cin, H, W, patch,
                                                     stream()), "ivit_quantize_patches_f32_i8")
     return out
@@ -38,12 +40,16 @@ def quantize_patches(x: torch.Tensor, inv_scale: float, patch: int) -> torch.Ten
 
 def layernorm_requant(kind: int, x: torch.Tensor, s_in: float, bias_int: torch.Tensor, sf: torch.Tensor,
                       mult: torch.Tensor, qmin: int, qmax: int, shift: float = 0.0,
-                      use_int_sqrt: bool = False) -> torch.Tensor:
-    assert x.dtype == torch.int8 and x.is_contiguous()
+                      use_int_sqrt: bool = False, out: torch.Tensor | None = None) -> torch.Tensor:
+    """x: int8 [..., C] (last dim contiguous, uniform row stride), e.g. a [B, C] view of the class rows."""
+    assert x.dtype == torch.int8 and x.stride(-1) == 1
     Cdim = x.shape[-1]
     rows = x.numel() // Cdim
-    out = torch.empty_like(x)
-    check(_cabi.load().ivit_layernorm_requant_i8(kind, ptr(x), ptr(out), rows, Cdim, C.c_float(s_in), ptr(bias_int),
+    ldx = x.stride(-2) if x.dim() >= 2 else Cdim
+    assert x.dim() <= 2 or x.is_contiguous()
+    if out is None:
+        out = torch.empty(x.shape, dtype=torch.int8, device=x.device)
+    check(_cabi.load().ivit_layernorm_requant_i8(kind, ptr(x), ldx, ptr(out), rows, Cdim, C.c_float(s_in), ptr(bias_int),
                                                  ptr(sf), ptr(mult), qmin, qmax, C.c_float(shift),
                                                  int(use_int_sqrt), stream()), "ivit_layernorm_requant_i8")
     return out
@@ -64,10 +70,11 @@ def gelu_ivit_raw_table(s_in: float, output_bit: int, device) -> torch.Tensor:
     return out
 
 
-def gelu_lut_apply(x: torch.Tensor, lut: torch.Tensor) -> torch.Tensor:
+def gelu_lut_apply(x: torch.Tensor, lut: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     assert x.dtype == torch.int8 and x.is_contiguous()
     Cdim = x.shape[-1]
-    out = torch.empty_like(x)
+    if out is None:
+        out = torch.empty_like(x)
     check(_cabi.load().ivit_gelu_lut_apply_i8(ptr(x), ptr(out), ptr(lut), x.numel() // Cdim, Cdim, stream()),
           "ivit_gelu_lut_apply_i8")
     return out
@@ -128,11 +135,13 @@ def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=Non
 
 
 def attention(qkv: torch.Tensor, B: int, N: int, H: int, hd: int, params: AttentionParams,
-              want_probs: bool = False):
+              want_probs: bool = False, out: torch.Tensor | None = None):
     """qkv int8 [B,N,3*H*hd] -> out int8 [B,N,H*hd] (and optionally the softmax codes [B,H,N,N] u8)."""
     assert qkv.dtype == torch.int8 and qkv.is_contiguous()
     lib = _cabi.load()
-    out = torch.empty((B, N, H * hd), dtype=torch.int8, device=qkv.device)
+    if out is None:
+        out = torch.empty((B, N, H * hd), dtype=torch.int8, device=qkv.device)
+    assert out.is_contiguous() and out.dtype == torch.int8 and out.numel() == B * N * H * hd
     check(lib.ivit_attention_i8(ptr(qkv), ptr(out), B, N, H, hd, C.byref(params), stream()), "ivit_attention_i8")
     if not want_probs:
         return out

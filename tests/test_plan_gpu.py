@@ -1,0 +1,95 @@
+"""GPU parity of the whole frozen forward (FrozenVitPlan -> C ABI -> sm_100a kernels) against
+the numpy oracle at every materialised module boundary, and against the committed reference
+logits (tests/golden/).  Bar: bit-exact int8 codes and argmax; logits within 1e-6 relative of the
+reference's float32-carried logits (exactly equal to the oracle's)."""
+import numpy as np
+import pytest
+import torch
+
+from ivit_b200.plan import FrozenVitPlan
+from ivit_b200.synthetic import load_case, synth_images
+from oracle import vit_oracle as VO
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+
+
+def _run_case(case, batch, seed=0):
+    cfg, state, fix = load_case(case)
+    x = synth_images(batch, cfg, seed=seed)
+    plan = FrozenVitPlan(cfg, state, "cuda")
+    taps = {}
+    logits = plan.forward(x.cuda(), taps=taps).cpu().numpy()
+    o = VO.VitOracle(cfg, state)
+    exp_logits = o.forward(x.numpy(), record=True)
+    bad = []
+    for name, t in taps.items():
+        got = t.cpu().numpy().astype(np.int64)
+        exp = VO.codes_of(o.taps[name]).astype(np.int64).reshape(got.shape)
+        n = int((got != exp).sum())
+        if n:
+            idx = tuple(np.argwhere(got != exp)[0])
+            bad.append(f"{name}: {n}/{got.size} (first {idx}: got {got[idx]} exp {exp[idx]})")
+    assert not bad, f"{case}: {len(bad)}/{len(taps)} boundaries differ:\n" + "\n".join(bad[:12])
+    assert np.array_equal(logits, exp_logits), np.abs(logits - exp_logits).max()
+    return cfg, plan, x, logits, fix
+
+
+@pytest.mark.parametrize("case", ["toy_ivit", "toy_ibert", "toy_mixed", "toy_ibert_intsqrt"])
+def test_toy_all_boundaries(case):
+    _, _, _, logits, fix = _run_case(case, 2)
+    ref = fix["logits"]
+    assert np.array_equal(logits.argmax(1), ref.argmax(1))
+    assert np.allclose(logits, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
+def test_deit_tiny_ivit_b8_configs0():
+    """BASELINE.json configs[0]: DeiT-Tiny INT8 ivit, synthetic 224x224, batch 8."""
+    _, _, _, logits, fix = _run_case("deit_tiny_ivit", 8)
+    ref = fix["logits"]
+    assert np.array_equal(logits.argmax(1), ref.argmax(1))
+    assert np.allclose(logits, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
+def test_deit_tiny_ibert():
+    _, _, _, logits, fix = _run_case("deit_tiny_ibert", 2)
+    assert np.allclose(logits, fix["logits"], rtol=1e-6, atol=1e-6 * np.abs(fix["logits"]).max())
+
+
+def test_fresh_inputs_and_graph_replay():
+    cfg, plan, x, logits, _ = _run_case("toy_ivit", 3, seed=11)
+    g = plan.capture(3)
+    out = g(x.cuda()).cpu().numpy()
+    assert np.array_equal(out, logits)
+    x2 = synth_images(3, cfg, seed=12)
+    out2 = g(x2.cuda()).clone().cpu().numpy()
+    assert np.array_equal(out2, plan.forward(x2.cuda()).cpu().numpy())
+    assert not np.array_equal(out2, out)
+
+
+def test_deit_small_b256_configs1():
+    """BASELINE.json configs[1] at full size: batch 256 on one GPU.  The first 4 images are
+    checked against the reference logits (fixture); the rest through shard invariance: every
+    image's logits are independent of batch size and position."""
+    cfg, state, fix = load_case("deit_small_ivit")
+    plan = FrozenVitPlan(cfg, state, "cuda")
+    x = synth_images(256, cfg, seed=0).cuda()
+    full = plan.forward(x).clone()
+    ref = fix["logits"]
+    got = full[:4].cpu().numpy()
+    assert np.array_equal(got.argmax(1), ref.argmax(1))
+    assert np.allclose(got, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+    for lo, hi in ((0, 4), (100, 164), (250, 256)):
+        part = plan.forward(x[lo:hi].contiguous())
+        assert torch.equal(part, full[lo:hi]), (lo, hi)
+    perm = torch.randperm(256, generator=torch.Generator().manual_seed(0)).cuda()
+    assert torch.equal(plan.forward(x[perm].contiguous()), full[perm])
+
+
+@pytest.mark.parametrize("case", ["vit_base_mixed", "deit_base_ibert"])
+def test_base_models_vs_reference_logits(case):
+    """configs[2] (ViT-Base, --gelu ivit --softmax ibert --layernorm ivit) and DeiT-Base ibert."""
+    _, _, _, logits, fix = _run_case(case, 2)
+    ref = fix["logits"]
+    assert np.array_equal(logits.argmax(1), ref.argmax(1))
+    assert np.allclose(logits, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
