@@ -128,7 +128,13 @@ typedef struct {
   /* ibert only: inner QuantAct(16) of IBERTIntSoftmax (ibert_modules.py:262,310) */
   double mult_exp16;
   float s_exp16;
+  /* optional device table [256][256] float32 built by ivit_softmax_table_build from the SAME
+   * params: exp term indexed [row-max code + 128][code + 128].  NULL: computed per element. */
+  const float* exp_table;
 } ivit_attention_params_t;
+/* The integer-exp term of IntSoftmax depends only on (code, row-max code) of qact_attn1's int8
+ * output: tabulate it once per frozen layer with the kernel's own arithmetic. */
+int ivit_softmax_table_build(const ivit_attention_params_t* p, float* table65536, void* stream);
 int ivit_attention_i8(const int8_t* qkv, int8_t* out, int B, int N, int H, int hd,
                       const ivit_attention_params_t* p, void* stream);
 /* Debug taps of the same kernel: softmax codes [B,H,N,N] uint8 (what int_softmax emits). */

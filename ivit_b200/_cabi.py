@@ -45,6 +45,7 @@ class AttentionParams(C.Structure):
         ("qmin_out", C.c_int), ("qmax_out", C.c_int),
         ("mult_exp16", C.c_double),
         ("s_exp16", C.c_float),
+        ("exp_table", C.c_void_p),
     ]
 
 
@@ -72,6 +73,7 @@ _SIGS = {
                                       C.c_int64, C.POINTER(GemmEpilogue), C.c_void_p]),
     "ivit_attention_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.POINTER(AttentionParams), C.c_void_p]),
+    "ivit_softmax_table_build": (C.c_int, [C.POINTER(AttentionParams), C.c_void_p, C.c_void_p]),
     "ivit_attention_probs_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                           C.POINTER(AttentionParams), C.c_void_p]),
 }

@@ -29,6 +29,7 @@ struct AttnArgs {
   int KP2;        // N rounded up to 32: K extent of P.V
   int8_t* out;
   uint8_t* probs;  // optional debug tap [B,H,N,N]
+  const float* exp_table;  // optional [256][256]: softmax_term(c, cmax) tabulated (bit-identical)
   ivit_attention_params_t p;
   // derived on the host with float32 arithmetic, mirroring the reference's scalar ops
   float x0, nx0;              // ivit: floor(-1/s), 15*x0 ; ibert: floor(-0.6931/s), 30*x0
@@ -62,6 +63,15 @@ __device__ __forceinline__ float softmax_term(int c, float xmax, const AttnArgs&
   double rr = requant_d(static_cast<double>(zi), a.p.mult_exp16);                 // :229-230
   rr = fmin(fmax(rr, -32768.0), 32767.0);                                         // :247-249
   return x_eff(static_cast<float>(rr), a.p.s_exp16);                              // ibert_modules.py:311
+}
+
+// The exp term of one score depends only on (its int8 code, the row-max int8 code): tabulated once
+// per layer at freeze time by the very same device function, as table[cmax+128][c+128].
+__global__ void softmax_table_kernel(float* __restrict__ table, const AttnArgs a) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= 65536) return;
+  const int c = (idx & 255) - 128, mx = (idx >> 8) - 128;
+  table[idx] = (c <= mx) ? softmax_term(c, x_eff(static_cast<float>(mx), a.p.s_attn), a) : 0.f;
 }
 
 __global__ void __launch_bounds__(128)
@@ -124,6 +134,10 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const int row = mt * 128 + warp * 32 + lane;          // token index within the image
   const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
   const int nchunks = (N + 31) / 32;
+  const bool warp_active = mt * 128 + warp * 32 < N;     // warp-uniform: rows past the last token do no work
+  const int r_loc = warp * 32 + lane;
+  const int pchunks = (a.KP2 + 31) / 32;
+  if (warp_active) {
 
   // pass 1: qact_attn1 requant, row max; codes go back to TMEM
   int cmax = -1 << 30;
@@ -145,6 +159,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   }
   tmem_st_wait();
   const float xmax = x_eff(static_cast<float>(cmax), a.p.s_attn);   // max of un-rounded x/s (monotone in code)
+  const float* trow = a.exp_table != nullptr ? a.exp_table + (cmax + 128) * 256 + 128 : nullptr;
 
   // pass 2: exp terms, float32 row sum in torch's CPU order (8-wide vectors x 4 accumulators)
   const int nvec = N / 8, size_ilp = nvec / 4;
@@ -159,8 +174,10 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     tmem_ld_wait();
     float e[32];
 #pragma unroll
-    for (int j = 0; j < 32; ++j)
-      e[j] = (ci * 32 + j < N) ? softmax_term(static_cast<int>(v[j]), xmax, a) : 0.f;
+    for (int j = 0; j < 32; ++j) {
+      const int c = static_cast<int>(v[j]);
+      e[j] = (ci * 32 + j < N) ? (trow != nullptr ? __ldg(trow + c) : softmax_term(c, xmax, a)) : 0.f;
+    }
     if (ci < size_ilp) {
 #pragma unroll
       for (int j = 0; j < 32; ++j) acc[j] = __fadd_rn(acc[j], e[j]);
@@ -199,8 +216,6 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const float factor = floorf(__fdiv_rn(a.num, sum));              // :174 / ibert :314
 
   // pass 3: probabilities -> u8 operand tile in shared memory (K-major, SWIZZLE_128B)
-  const int r_loc = warp * 32 + lane;
-  const int pchunks = (a.KP2 + 31) / 32;
   for (int ci = 0; ci < pchunks; ++ci) {
     uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (ci < nchunks) {
@@ -225,6 +240,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     *reinterpret_cast<int4*>(base + ((u0 ^ (r_loc & 7)) << 4)) = make_int4(w[0], w[1], w[2], w[3]);
     *reinterpret_cast<int4*>(base + (((u0 + 1) ^ (r_loc & 7)) << 4)) = make_int4(w[4], w[5], w[6], w[7]);
   }
+  }  // warp_active
   fence_proxy_async_smem();     // generic-proxy smem writes -> visible to tcgen05.mma
   tc_fence_before();
   __syncthreads();
@@ -252,7 +268,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     tmem_ld32(t_row, o0);
     tmem_ld32(t_row + 32, o1);
     tmem_ld_wait();
-    if (row < N && a.out != nullptr) {
+    if (warp_active && row < N && a.out != nullptr) {
       uint32_t w[16];
 #pragma unroll
       for (int j = 0; j < 16; ++j) w[j] = 0;
@@ -273,18 +289,8 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   if (warp == 1) tmem_dealloc(tmem_base, 256);
 }
 
-static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int N, int H, int hd,
-                            const ivit_attention_params_t* p, cudaStream_t st) {
-  if (!p) return fail(IVIT_ERR_BAD_ARG, "attention: params NULL");
-  if (hd != HD) return fail(IVIT_ERR_UNSUPPORTED, "attention: head_dim must be 64");
-  if (N < 1 || N > 256) return fail(IVIT_ERR_UNSUPPORTED, "attention: 1 <= N <= 256 tokens");
-  if (p->output_bit != 8) return fail(IVIT_ERR_UNSUPPORTED, "attention: 8-bit softmax output only");
-  if (B * H <= 0) return 0;
-  AttnArgs a;
-  a.B = B; a.N = N; a.H = H;
-  a.NKP = (N + 15) / 16 * 16;
-  a.KP2 = (N + 31) / 32 * 32;
-  a.out = out; a.probs = probs; a.p = *p;
+static void derive_softmax_consts(AttnArgs& a, const ivit_attention_params_t* p) {
+  a.p = *p;
   const float s = p->s_attn;
   if (p->kind == 0) {
     a.x0 = floorf(-1.0f / s);                          // ivit_modules.py:154
@@ -302,6 +308,21 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
     a.num = 4294967296.f;                              // 2^32 (:314)
     a.out_shift = 1.f / ldexpf(1.f, 32 - p->output_bit + 1);
   }
+}
+
+static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int N, int H, int hd,
+                            const ivit_attention_params_t* p, cudaStream_t st) {
+  if (!p) return fail(IVIT_ERR_BAD_ARG, "attention: params NULL");
+  if (hd != HD) return fail(IVIT_ERR_UNSUPPORTED, "attention: head_dim must be 64");
+  if (N < 1 || N > 256) return fail(IVIT_ERR_UNSUPPORTED, "attention: 1 <= N <= 256 tokens");
+  if (p->output_bit != 8) return fail(IVIT_ERR_UNSUPPORTED, "attention: 8-bit softmax output only");
+  if (B * H <= 0) return 0;
+  AttnArgs a;
+  a.B = B; a.N = N; a.H = H;
+  a.NKP = (N + 15) / 16 * 16;
+  a.KP2 = (N + 31) / 32 * 32;
+  a.out = out; a.probs = probs; a.exp_table = p->exp_table;
+  derive_softmax_consts(a, p);
   const int C = H * hd;
   CUtensorMap tq, tk, tv;
   int rc;
@@ -329,6 +350,14 @@ using namespace ivit;
 extern "C" int ivit_attention_i8(const int8_t* qkv, int8_t* out, int B, int N, int H, int hd,
                                  const ivit_attention_params_t* p, void* stream) {
   return attention_launch(qkv, out, nullptr, B, N, H, hd, p, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ivit_softmax_table_build(const ivit_attention_params_t* p, float* table65536, void* stream) {
+  if (!p || !table65536) return fail(IVIT_ERR_BAD_ARG, "softmax table: NULL argument");
+  AttnArgs a{};
+  derive_softmax_consts(a, p);
+  softmax_table_kernel<<<256, 256, 0, static_cast<cudaStream_t>(stream)>>>(table65536, a);
+  return check_launch("softmax_table_kernel");
 }
 
 extern "C" int ivit_attention_probs_i8(const int8_t* qkv, uint8_t* probs, int B, int N, int H, int hd,

@@ -49,87 +49,150 @@ __global__ void quantize_kernel(const float* __restrict__ x, int8_t* __restrict_
 }
 
 // ------------------------------------------------------------------ LayerNorm + QuantAct
-// One warp per row.  Lane t owns elements {32*i + t}: that is torch's CPU accumulator layout
-// (intmath.cuh TorchSum32), so the tie-break slow path needs no data exchange.  The row is
+// Lane t owns elements {32*i + t} of a row: that is torch's CPU accumulator layout
+// (intmath.cuh TorchSum32), so the tie-break slow path needs no data exchange.  Rows are
 // staged through shared memory with 16-byte loads and read back byte-wise (conflict free).
-template <int MAXC>
-struct LnSmem {
-  int8_t row[MAXC];
-};
 
 // ivit_modules.py:30-65 followed by QuantAct (quant_modules.py:379-387, quant_utils.py:220-251).
 // per-channel params: bias_int[c] = floor((b/w)/(sqrt(C)/2^30)), sf[c] = sqrt(C)/2^30*w[c],
 // mult[c] = m*2^-e of sf[c]/s_out.
-template <int NPL>  // elements per lane = C/32 (compile-time for unrolling): 6, 12, 24, ...
+//
+// Persistent grid; a warp owns R rows per iteration.  What keeps it off the ALU roof:
+//  * x_eff(q) = fl32(fl32(q*s)/s) and its truncation have 256 possible values: per-block LUT.
+//  * per-channel constants live in registers for the warp's whole lifetime.
+//  * the ten float32 Newton steps run once per R rows (lane r iterates row r's variance).
+//  * QuantAct: exact value is rint(z*mult) with z = rint(fl32(fl32(v*sf)/sf)), |z - v| <= |v| 2^-22.
+//    Inside the clamp range |v*mult| < 130 the float32 product v*fl32(mult) is within 5e-5 of
+//    z*mult, so unless it lies within 1e-4 of a rounding tie (p ~ 2e-4) rintf of it IS the
+//    exact answer; outside the range both clamp.  Near ties take the replay path.
+template <int NPL, int R>
 __global__ void __launch_bounds__(256)
-layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows, float s_in,
-                              const float* __restrict__ bias_int, const float* __restrict__ sf,
+layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows,
+                              float s_in, const float* __restrict__ bias_int, const float* __restrict__ sf,
                               const double* __restrict__ mult, int qmin, int qmax) {
   constexpr int C = NPL * 32;
-  __shared__ __align__(16) int8_t stage[8][C];
+  constexpr int VPR = C / 16;                       // 16-byte vectors per row
+  __shared__ __align__(16) int8_t stage[8][2][R][C];     // double buffered: cp.async prefetch of the next group
+  __shared__ float lut_f[256];
+  __shared__ int lut_i[256];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * 8 + warp;
-  if (row >= rows) return;
-  const int8_t* xr = x + static_cast<long long>(row) * ldx;
-  // coalesced 16-byte loads -> smem
-  for (int v = lane; v < C / 16; v += 32)
-    *reinterpret_cast<int4*>(&stage[warp][v * 16]) = *reinterpret_cast<const int4*>(xr + v * 16);
-  __syncwarp();
-  int q[NPL];
-  int S = 0;
+  {
+    const float xe = x_eff(static_cast<float>(static_cast<int>(threadIdx.x) - 128), s_in);   // :36
+    lut_f[threadIdx.x] = xe;
+    lut_i[threadIdx.x] = static_cast<int>(xe);                                               // :38 trunc
+  }
+  float bia[NPL], mf[NPL];
 #pragma unroll
   for (int i = 0; i < NPL; ++i) {
-    q[i] = stage[warp][32 * i + lane];
-    S += q[i];
+    bia[i] = __ldg(bias_int + 32 * i + lane);
+    mf[i] = static_cast<float>(__ldg(mult + 32 * i + lane));
   }
+  const bool fast_ok = qmin >= -128 && qmax <= 127;
+  const int ngroups = (rows + R - 1) / R;
+  auto prefetch = [&](int g, int buf) {
+    if (g < ngroups) {
+      const int row0 = g * R, nr = min(R, rows - row0);
+      for (int v = lane; v < R * VPR; v += 32) {
+        const int r = v / VPR, vv = v - r * VPR;
+        if (r < nr) {
+          const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(&stage[warp][buf][r][vv * 16]));
+          const int8_t* src = x + static_cast<long long>(row0 + r) * ldx + vv * 16;
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  prefetch(blockIdx.x * 8 + warp, 0);
+  __syncthreads();
+  int buf = 0;
+  for (int g = blockIdx.x * 8 + warp; g < ngroups; g += gridDim.x * 8, buf ^= 1) {
+    const int row0 = g * R;
+    const int nr = min(R, rows - row0);
+    prefetch(g + gridDim.x * 8, buf ^ 1);
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncwarp();
+    int y[R][NPL];
+    float factor[R];
+    long long var[R];
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
-  // :36-38  x_int = x/s (un-rounded), p = trunc(x_int)
-  float xe[NPL];
+    for (int r = 0; r < R; ++r) {
+      int qi[NPL];
+      int S = 0;
 #pragma unroll
-  for (int i = 0; i < NPL; ++i) xe[i] = x_eff(static_cast<float>(q[i]), s_in);
-  // :37 mean = round(mean(x_int)).  Only an exact tie S/C = k + 1/2 can be moved by the
-  // float32 noise of the un-rounded inputs; then replay torch's summation order.
-  float sum_f = static_cast<float>(S);
-  const int rem = ((S % C) + C) % C;
-  if (rem * 2 == C) {
-    TorchSum32 acc;
+      for (int i = 0; i < NPL; ++i) {
+        qi[i] = static_cast<int>(stage[warp][buf][r][32 * i + lane]) + 128;
+        S += qi[i] - 128;
+      }
 #pragma unroll
-    for (int i = 0; i < NPL; ++i) acc.add(xe[i]);
-    sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+      for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
+      // :37 mean = round(mean(x_int)).  Only an exact tie S/C = k + 1/2 can be moved by the
+      // float32 noise of the un-rounded inputs; then replay torch's summation order.
+      float sum_f = static_cast<float>(S);
+      const int rem = ((S % C) + C) % C;
+      if (rem * 2 == C) {
+        TorchSum32 acc;
+#pragma unroll
+        for (int i = 0; i < NPL; ++i) acc.add(lut_f[qi[i]]);
+        sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+      }
+      const int mean = static_cast<int>(rintf(__fdiv_rn(sum_f, static_cast<float>(C))));
+      long long vr = 0;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        y[r][i] = lut_i[qi[i]] - mean;                              // :38-40 (trunc, int32)
+        vr += static_cast<long long>(y[r][i] * y[r][i]);            // :41 int32 square (wraps, H9), :42 int64 sum
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) vr += __shfl_xor_sync(0xffffffffu, vr, o);
+      var[r] = vr;
+    }
+    // :45-49 ten float32 Newton steps from k = 2^16, once per R rows: lane r iterates row r
+    {
+      long long mv = var[0];
+#pragma unroll
+      for (int r = 1; r < R; ++r) mv = (lane == r) ? var[r] : mv;
+      const float var_f = static_cast<float>(mv);
+      float k = 65536.f;
+#pragma unroll
+      for (int it = 0; it < 10; ++it) k = floorf(__fmul_rn(__fadd_rn(k, floorf(__fdiv_rn(var_f, k))), 0.5f));
+      const float fct = floorf(__fdiv_rn(2147483648.f, k));        // :51 (2^31-1 -> 2^31 in float32)
+#pragma unroll
+      for (int r = 0; r < R; ++r) factor[r] = __shfl_sync(0xffffffffu, fct, r);
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        const int c = 32 * i + lane;
+        float v = floorf(__fmul_rn(__fmul_rn(static_cast<float>(y[r][i]), factor[r]), 0.5f));   // :52
+        v = __fadd_rn(v, bia[i]);                                                               // :61
+        const float ra = __fmul_rn(v, mf[i]);
+        const float rr = rintf(ra);
+        int code;
+        if (fast_ok && fabsf(ra) >= 130.f) {
+          code = ra > 0.f ? qmax : qmin;
+        } else if (fast_ok && fabsf(__fsub_rn(ra, rr)) < 0.4999f) {
+          code = clampi(static_cast<int>(rr), qmin, qmax);
+        } else {
+          const float sc = __ldg(sf + c);
+          const float xo = __fmul_rn(v, sc);                                                    // :63
+          const float z = rintf(__fdiv_rn(xo, sc));                                             // quant_utils.py:220
+          const double rd = requant_d(static_cast<double>(z), __ldg(mult + c));                 // :229-230
+          code = static_cast<int>(fmin(fmax(rd, static_cast<double>(qmin)), static_cast<double>(qmax)));
+        }
+        stage[warp][buf][r][c] = static_cast<int8_t>(code);
+      }
+    }
+    __syncwarp();
+    for (int v = lane; v < R * VPR; v += 32) {
+      const int r = v / VPR, vv = v - r * VPR;
+      if (r < nr)
+        *reinterpret_cast<int4*>(out + static_cast<long long>(row0 + r) * C + vv * 16) =
+            *reinterpret_cast<const int4*>(&stage[warp][buf][r][vv * 16]);
+    }
+    __syncwarp();
   }
-  const int mean = static_cast<int>(rintf(__fdiv_rn(sum_f, static_cast<float>(C))));
-  int y[NPL];
-  long long var = 0;
-#pragma unroll
-  for (int i = 0; i < NPL; ++i) {
-    y[i] = static_cast<int>(xe[i]) - mean;                    // :38-40 (trunc, int32)
-    var += static_cast<long long>(y[i] * y[i]);               // :41 int32 square (wraps, H9), :42 int64 sum
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) var += __shfl_xor_sync(0xffffffffu, var, o);
-  // :45-49 ten float32 Newton steps from k = 2^16
-  const float var_f = static_cast<float>(var);
-  float k = 65536.f;
-#pragma unroll
-  for (int it = 0; it < 10; ++it) k = floorf(__fmul_rn(__fadd_rn(k, floorf(__fdiv_rn(var_f, k))), 0.5f));
-  const float factor = floorf(__fdiv_rn(2147483648.f, k));   // :51 (2^31-1 -> 2^31 in float32)
-  int8_t* orow = out + static_cast<long long>(row) * C;
-#pragma unroll
-  for (int i = 0; i < NPL; ++i) {
-    const int c = 32 * i + lane;
-    float v = floorf(__fmul_rn(__fmul_rn(static_cast<float>(y[i]), factor), 0.5f));   // :52
-    v = __fadd_rn(v, __ldg(bias_int + c));                                            // :61
-    const float sc = __ldg(sf + c);
-    const float xo = __fmul_rn(v, sc);                                                // :63
-    const float z = rintf(__fdiv_rn(xo, sc));                                         // quant_utils.py:220
-    const double r = requant_d(static_cast<double>(z), __ldg(mult + c));              // :229-230
-    const int code = static_cast<int>(fmin(fmax(r, static_cast<double>(qmin)), static_cast<double>(qmax)));
-    stage[warp][c] = static_cast<int8_t>(code);
-  }
-  __syncwarp();
-  for (int v = lane; v < C / 16; v += 32)
-    *reinterpret_cast<int4*>(orow + v * 16) = *reinterpret_cast<const int4*>(&stage[warp][v * 16]);
 }
 
 // ibert_modules.py:112-158 followed by QuantAct.  shift_pow = 2^shift, inv_shift_pow = 2^-shift.
@@ -372,7 +435,11 @@ static int launch_ln(int kind, const int8_t* x, long long ldx, int8_t* out, int 
                      cudaStream_t st) {
   const int grid = (rows + 7) / 8;
   if (kind == 0) {
-    layernorm_ivit_requant_kernel<NPL><<<grid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax);
+    constexpr int R = NPL <= 12 ? 4 : 2;
+    const int groups = (rows + R - 1) / R;
+    const int pgrid = min((groups + 7) / 8, 148 * 4);     // persistent: a few CTAs per SM
+    layernorm_ivit_requant_kernel<NPL, R><<<pgrid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin,
+                                                                qmax);
   } else {
     const float sp = ldexpf(1.f, static_cast<int>(shift));
     layernorm_ibert_requant_kernel<NPL><<<grid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp,

@@ -134,6 +134,16 @@ def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=Non
     return out
 
 
+def softmax_table_build(params: AttentionParams, device) -> torch.Tensor:
+    """Tabulate the softmax exp term over (row-max code, code) and attach it to `params`.  The
+    returned tensor owns the memory: keep it alive as long as `params` is used."""
+    table = torch.empty((256, 256), dtype=torch.float32, device=device)
+    params.exp_table = None
+    check(_cabi.load().ivit_softmax_table_build(C.byref(params), ptr(table), stream()), "ivit_softmax_table_build")
+    params.exp_table = table.data_ptr()
+    return table
+
+
 def attention(qkv: torch.Tensor, B: int, N: int, H: int, hd: int, params: AttentionParams,
               want_probs: bool = False, out: torch.Tensor | None = None):
     """qkv int8 [B,N,3*H*hd] -> out int8 [B,N,H*hd] (and optionally the softmax codes [B,H,N,N] u8)."""

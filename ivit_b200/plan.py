@@ -130,6 +130,7 @@ class FrozenVitPlan:
         self.H = cfg.num_heads
         self.hd = cfg.embed_dim // cfg.num_heads
         self._bufs = {}
+        self._tables = []
         self._graphs = {}
         self.launches_per_forward = 0
         self.trace = None
@@ -198,6 +199,8 @@ class FrozenVitPlan:
         s_out = self._act_scale(p + "qact2")
         a.mult_out = float(hm.dyadic_mult(s_mm2, s_out).reshape(-1)[0])
         a.qmin_out, a.qmax_out = -128, 127
+        if not self.host_only:
+            self._tables.append(ops.softmax_table_build(a, self.device))
         return a, s_out
 
     def _build(self):

@@ -259,6 +259,12 @@ def _attention_case(kind, B, N, H, seed, s_qkv=0.05):
     out, probs = ops.attention(_t(qkv.reshape(B, N, 3 * C), torch.int8), B, N, H, hd, p, want_probs=True)
     _cmp(probs.cpu().numpy(), sm_codes, f"attention probs kind={kind}")
     _cmp(out.cpu().numpy(), out_codes, f"attention out kind={kind}")
+    # same kernel with the exp term tabulated over (row-max code, code)
+    table = ops.softmax_table_build(p, DEV)
+    out, probs = ops.attention(_t(qkv.reshape(B, N, 3 * C), torch.int8), B, N, H, hd, p, want_probs=True)
+    _cmp(probs.cpu().numpy(), sm_codes, f"attention probs (table) kind={kind}")
+    _cmp(out.cpu().numpy(), out_codes, f"attention out (table) kind={kind}")
+    del table
 
 
 @pytest.mark.parametrize("N", [197, 64, 49, 256, 130])
