@@ -104,6 +104,8 @@ typedef struct {
   const float* scale_out;    /* LOGITS: [N] */
   int group, out_group_stride, out_row_off, id_broadcast;
   int force_slow;            /* 1: always take the general requant path (|mult| >= 256 or huge codes) */
+  int z_bound_ok;            /* 1: caller proved |acc + bias| < 2^22 for every output (weights-only bound):
+                              * the epilogue skips its per-element range check */
 } ivit_gemm_epilogue_t;
 int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M, int N, int K, void* out, int64_t ldo,
                  const ivit_gemm_epilogue_t* epi, void* stream);

@@ -31,6 +31,7 @@ class GemmEpilogue(C.Structure):
         ("scale_out", C.c_void_p),
         ("group", C.c_int), ("out_group_stride", C.c_int), ("out_row_off", C.c_int), ("id_broadcast", C.c_int),
         ("force_slow", C.c_int),
+        ("z_bound_ok", C.c_int),
     ]
 
 

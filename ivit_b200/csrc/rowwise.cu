@@ -112,42 +112,55 @@ layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, long long ldx, int8_
     prefetch(g + gridDim.x * 8, buf ^ 1);
     asm volatile("cp.async.wait_group 1;" ::: "memory");
     __syncwarp();
+    // Phase-ordered (all R rows per phase, branch-free main path) so that independent rows and
+    // elements interleave in the instruction stream; the rare paths are warp-level exceptions.
     int y[R][NPL];
-    float factor[R];
+    int S[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      S[r] = 0;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        y[r][i] = static_cast<int>(stage[warp][buf][r][32 * i + lane]) + 128;     // LUT index for now
+        S[r] += y[r][i];
+      }
+      S[r] -= 128 * NPL;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+      for (int r = 0; r < R; ++r) S[r] += __shfl_xor_sync(0xffffffffu, S[r], o);
+    int mean[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      // :37 mean = round(mean(x_int)).  Only an exact tie S/C = k + 1/2 can be moved by the
+      // float32 noise of the un-rounded inputs; then replay torch's summation order.
+      float sum_f = static_cast<float>(S[r]);
+      if (((S[r] % C) + C) % C * 2 == C) {                      // warp-uniform, rare
+        TorchSum32 acc;
+#pragma unroll
+        for (int i = 0; i < NPL; ++i) acc.add(lut_f[y[r][i]]);
+        sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+      }
+      mean[r] = static_cast<int>(rintf(__fdiv_rn(sum_f, static_cast<float>(C))));
+    }
     long long var[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      int qi[NPL];
-      int S = 0;
-#pragma unroll
-      for (int i = 0; i < NPL; ++i) {
-        qi[i] = static_cast<int>(stage[warp][buf][r][32 * i + lane]) + 128;
-        S += qi[i] - 128;
-      }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
-      // :37 mean = round(mean(x_int)).  Only an exact tie S/C = k + 1/2 can be moved by the
-      // float32 noise of the un-rounded inputs; then replay torch's summation order.
-      float sum_f = static_cast<float>(S);
-      const int rem = ((S % C) + C) % C;
-      if (rem * 2 == C) {
-        TorchSum32 acc;
-#pragma unroll
-        for (int i = 0; i < NPL; ++i) acc.add(lut_f[qi[i]]);
-        sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
-      }
-      const int mean = static_cast<int>(rintf(__fdiv_rn(sum_f, static_cast<float>(C))));
       long long vr = 0;
 #pragma unroll
       for (int i = 0; i < NPL; ++i) {
-        y[r][i] = lut_i[qi[i]] - mean;                              // :38-40 (trunc, int32)
+        y[r][i] = lut_i[y[r][i]] - mean[r];                         // :38-40 (trunc, int32)
         vr += static_cast<long long>(y[r][i] * y[r][i]);            // :41 int32 square (wraps, H9), :42 int64 sum
       }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) vr += __shfl_xor_sync(0xffffffffu, vr, o);
       var[r] = vr;
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+      for (int r = 0; r < R; ++r) var[r] += __shfl_xor_sync(0xffffffffu, var[r], o);
     // :45-49 ten float32 Newton steps from k = 2^16, once per R rows: lane r iterates row r
+    float factor[R];
     {
       long long mv = var[0];
 #pragma unroll
@@ -160,28 +173,44 @@ layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, long long ldx, int8_
 #pragma unroll
       for (int r = 0; r < R; ++r) factor[r] = __shfl_sync(0xffffffffu, fct, r);
     }
+    uint32_t slow[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
+      slow[r] = 0;
 #pragma unroll
       for (int i = 0; i < NPL; ++i) {
-        const int c = 32 * i + lane;
-        float v = floorf(__fmul_rn(__fmul_rn(static_cast<float>(y[r][i]), factor[r]), 0.5f));   // :52
+        // int -> float and float -> nearest int through the 1.5*2^23 magic constant (exact for
+        // |.| < 2^22): conversions share the quarter-rate XU pipe
+        const float yf = __fsub_rn(__int_as_float(0x4B400000 + y[r][i]), 12582912.f);
+        float v = floorf(__fmul_rn(__fmul_rn(yf, factor[r]), 0.5f));                            // :52
         v = __fadd_rn(v, bia[i]);                                                               // :61
-        const float ra = __fmul_rn(v, mf[i]);
-        const float rr = rintf(ra);
-        int code;
-        if (fast_ok && fabsf(ra) >= 130.f) {
-          code = ra > 0.f ? qmax : qmin;
-        } else if (fast_ok && fabsf(__fsub_rn(ra, rr)) < 0.4999f) {
-          code = clampi(static_cast<int>(rr), qmin, qmax);
-        } else {
-          const float sc = __ldg(sf + c);
-          const float xo = __fmul_rn(v, sc);                                                    // :63
-          const float z = rintf(__fdiv_rn(xo, sc));                                             // quant_utils.py:220
-          const double rd = requant_d(static_cast<double>(z), __ldg(mult + c));                 // :229-230
-          code = static_cast<int>(fmin(fmax(rd, static_cast<double>(qmin)), static_cast<double>(qmax)));
+        const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -200.f), 200.f);   // beyond +-130 both paths clamp
+        const float tm = __fadd_rn(ra, 12582912.f);             // rint(ra) in the low mantissa bits
+        const float rr = __fsub_rn(tm, 12582912.f);
+        // near a rounding tie (or a NaN from a zero scale): exact replay below
+        slow[r] |= (fabsf(__fsub_rn(ra, rr)) < 0.4999f) ? 0u : (1u << i);
+        stage[warp][buf][r][32 * i + lane] = static_cast<int8_t>(clampi(__float_as_int(tm) - 0x4B400000, qmin, qmax));
+      }
+      if (!fast_ok) slow[r] = 0xffffffffu;
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (slow[r] != 0) {
+#pragma unroll
+        for (int i = 0; i < NPL; ++i) {
+          if ((slow[r] >> i) & 1u) {
+            const int c = 32 * i + lane;
+            const float yf = static_cast<float>(y[r][i]);
+            float v = floorf(__fmul_rn(__fmul_rn(yf, factor[r]), 0.5f));                        // :52
+            v = __fadd_rn(v, bia[i]);                                                           // :61
+            const float sc = __ldg(sf + c);
+            const float xo = __fmul_rn(v, sc);                                                  // :63
+            const float z = rintf(__fdiv_rn(xo, sc));                                           // quant_utils.py:220
+            const double rd = requant_d(static_cast<double>(z), __ldg(mult + c));               // :229-230
+            const int code = static_cast<int>(fmin(fmax(rd, static_cast<double>(qmin)), static_cast<double>(qmax)));
+            stage[warp][buf][r][c] = static_cast<int8_t>(code);
+          }
         }
-        stage[warp][buf][r][c] = static_cast<int8_t>(code);
       }
     }
     __syncwarp();

@@ -107,7 +107,7 @@ def fill_cls_rows(out: torch.Tensor, cls_row: torch.Tensor):
 def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=None, s_in=None, qmin=-128, qmax=127,
          mult2=0.0, mult_id=0.0, qmin2=-128, qmax2=127, identity=None, scale_out=None, out=None, out_rows=None,
          group=0, out_group_stride=0, out_row_off=0, id_broadcast=False, force_slow=False,
-         simple=False) -> torch.Tensor:
+         z_bound_ok=False, simple=False) -> torch.Tensor:
     """C = A[M,K] @ W[N,K]^T with a fused epilogue (see include/ivit_b200.h)."""
     assert A.dtype == torch.int8 and W.dtype == torch.int8 and A.dim() == 2 and W.dim() == 2
     assert A.stride(1) == 1 and W.is_contiguous()
@@ -126,6 +126,7 @@ def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=Non
     e.scale_out = ptr(scale_out)
     e.group, e.out_group_stride, e.out_row_off, e.id_broadcast = group, out_group_stride, out_row_off, int(id_broadcast)
     e.force_slow = int(force_slow)
+    e.z_bound_ok = int(z_bound_ok)
     lib = _cabi.load()
     fn = lib.ivit_gemm_i8_simple if simple else lib.ivit_gemm_i8
     ldo = out.stride(-2) if out.dim() >= 2 else N

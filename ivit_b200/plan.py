@@ -54,6 +54,7 @@ class _Linear:
     qmin: int = -128
     qmax: int = 127
     force_slow: bool = False
+    z_bound_ok: bool = False
     s_out: np.float32 = f32(0)
     # second requant + identity (RESIDUAL)
     mult2: float = 0.0
@@ -155,7 +156,11 @@ class FrozenVitPlan:
                                                                else 0).max() >= 2 ** 30)
             mult = self._dev(m.reshape(-1), torch.float64)
         lo, hi = hm.qrange(bits)
-        return _Linear(w=self._dev(p["w_int"], torch.int8), bias=self._dev(p["b_int"], torch.int32),
+        # weights-only bound on |acc + bias| for int8 inputs (|x| <= 128): below 2^22 the epilogue's
+        # fast requant is exact for every possible activation and needs no per-element range check
+        zb = np.abs(p["w_int_f32"]).sum(axis=1).max() * 128.0 + np.abs(p["b_int"].astype(np.float64)).max()
+        self_zb = bool(zb < 2 ** 22) and not slow
+        return _Linear(z_bound_ok=self_zb, w=self._dev(p["w_int"], torch.int8), bias=self._dev(p["b_int"], torch.int32),
                        b_scale=self._dev(p["b_scale"], torch.float32), mult=mult, qmin=lo, qmax=hi,
                        force_slow=slow, s_out=(s_out[0] if s_out is not None else f32(0)))
 
@@ -314,7 +319,7 @@ class FrozenVitPlan:
     def _gemm(self, A, lin: _Linear, epilogue, out, name="gemm", **kw):
         r = ops.gemm(A, lin.w, epilogue, bias=lin.bias, mult=lin.mult, s_in=lin.b_scale, qmin=lin.qmin,
                      qmax=lin.qmax, mult2=lin.mult2, mult_id=lin.mult_id, qmin2=lin.qmin2, qmax2=lin.qmax2,
-                     out=out, force_slow=lin.force_slow, **kw)
+                     out=out, force_slow=lin.force_slow, z_bound_ok=lin.z_bound_ok, **kw)
         M, K = A.shape
         Nn = lin.w.shape[0]
         by = M * K + Nn * K + M * Nn * out.element_size() + (M * Nn if epilogue == EPI_RESIDUAL else 0) + Nn * 16

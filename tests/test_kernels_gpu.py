@@ -133,10 +133,13 @@ def test_gelu_ibert_table(s_in):
     _cmp(lut.cpu().numpy()[200], exp[0], "gelu ibert lut")
 
 
-def _gemm_case(M, N, K, seed, epilogue, group=0):
+def _gemm_case(M, N, K, seed, epilogue, group=0, bounded=False):
     rng = np.random.default_rng(seed)
     A = rng.integers(-128, 128, size=(M, K)).astype(np.int8)
     W = rng.integers(-127, 128, size=(N, K)).astype(np.int8)
+    if bounded:      # weights small enough that sum_k |W| * 128 + |bias| < 2^22: unchecked fast epilogue
+        W = rng.integers(-40, 41, size=(N, K)).astype(np.int8)
+        assert np.abs(W.astype(np.int64)).sum(axis=1).max() * 128 + 20000 < 2 ** 22
     bias = rng.integers(-20000, 20000, size=N).astype(np.int32)
     acc = (A.astype(np.float64) @ W.astype(np.float64).T + bias).astype(np.int64)
     s_in = (rng.random(N) * 2e-5 + 1e-5).astype(f32)                 # per-channel s_w*s_x
@@ -179,7 +182,8 @@ def _gemm_case(M, N, K, seed, epilogue, group=0):
         if out_rows:
             odt = torch.int8
             out = torch.full((out_rows, N), 99, dtype=odt, device=DEV)
-        got = ops.gemm(_t(A, torch.int8), _t(W, torch.int8), epilogue, simple=simple, out=out, **kw).cpu().numpy()
+        got = ops.gemm(_t(A, torch.int8), _t(W, torch.int8), epilogue, simple=simple, out=out,
+                       z_bound_ok=(bounded and not simple), **kw).cpu().numpy()
         if group:
             got = got.reshape(M // group, group + 1, N)[:, 1:].reshape(M, N)
         res[simple] = got
@@ -206,6 +210,17 @@ def test_gemm_requant(shape):
 @pytest.mark.parametrize("shape", [(300, 384, 384), (394, 192, 768), (256, 384, 1536)])
 def test_gemm_residual(shape):
     _gemm_case(*shape, seed=3, epilogue=_cabi.EPI_RESIDUAL)
+
+
+@pytest.mark.parametrize("shape", [(700, 384, 384), (394, 1152, 384), (40000, 1536, 384)])
+def test_gemm_requant_unchecked(shape):
+    _gemm_case(*shape, seed=6, epilogue=_cabi.EPI_REQUANT, bounded=True)
+
+
+def test_gemm_residual_unchecked_many_tiles():
+    """More tiles than SMs: every CTA walks several tiles through both TMEM accumulators."""
+    _gemm_case(30000, 384, 384, seed=7, epilogue=_cabi.EPI_RESIDUAL, bounded=True)
+    _gemm_case(20000, 384, 1536, seed=8, epilogue=_cabi.EPI_RESIDUAL)
 
 
 def test_gemm_patch_embed_remap():
