@@ -74,7 +74,13 @@ __global__ void softmax_table_kernel(float* __restrict__ table, const AttnArgs a
   table[idx] = (c <= mx) ? softmax_term(c, x_eff(static_cast<float>(mx), a.p.s_attn), a) : 0.f;
 }
 
-__global__ void __launch_bounds__(128)
+// 256 threads = two threads per query row: thread A (warps 0-3) owns columns [32i, 32i+16) of
+// every 32-column chunk, thread B (warps 4-7) columns [32i+16, 32i+32).  That split keeps torch's
+// float32 summation order (accumulator e % 32 lives in exactly one thread) while doubling the
+// warps that hide the TMEM / table-gather latency.  TABLE: exp term from the (row max, code)
+// table; TAP: also dump the softmax codes (tests).
+template <bool TABLE, bool TAP>
+__global__ void __launch_bounds__(256, 2)
 attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -83,10 +89,15 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint8_t* sQ = smem + 32768;               // [128 x 64 B]  SWIZZLE_64B (TMA)
   uint8_t* sK = sQ + 8192;                  // [<=256 x 64 B]
   uint8_t* sV = sK + 16384;                 // [<=256 x 64 B]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 16384);   // qk, v, s, o
+  float* sAcc = reinterpret_cast<float*>(sV + 16384);          // [16][128] B's accumulators -> A
+  int* sMax = reinterpret_cast<int*>(sAcc + 16 * 128);         // [2][128]
+  float* sFac = reinterpret_cast<float*>(sMax + 256);          // [128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sFac + 128);    // qk, v, s, o
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int half = warp >> 2;               // 0: thread A, 1: thread B
+  const int quarter = warp & 3;             // TMEM lane quarter
   const int mt = blockIdx.x;
   const int b = blockIdx.y / a.H, h = blockIdx.y % a.H;
   const int C = a.H * HD;
@@ -128,119 +139,155 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   }
   __syncwarp();
 
-  // ---------------------------------------------------------------- softmax, thread = query row
+  // ---------------------------------------------------------------- softmax
   mbar_wait(&bars[2], 0);
   tc_fence_after();
-  const int row = mt * 128 + warp * 32 + lane;          // token index within the image
-  const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+  const int r_loc = quarter * 32 + lane;
+  const int row = mt * 128 + r_loc;                     // token index within the image
+  const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + half * 16;
+  const int nfull = N / 32;                             // chunks with all 32 columns valid
   const int nchunks = (N + 31) / 32;
-  const bool warp_active = mt * 128 + warp * 32 < N;     // warp-uniform: rows past the last token do no work
-  const int r_loc = warp * 32 + lane;
-  const int pchunks = (a.KP2 + 31) / 32;
-  if (warp_active) {
+  const int pchunks = a.KP2 / 32;
+  const bool warp_active = mt * 128 + quarter * 32 < N; // warp-uniform: rows past the last token do no work
+  const int cbase = half * 16;                          // this thread's first column inside a chunk
 
   // pass 1: qact_attn1 requant, row max; codes go back to TMEM
-  int cmax = -1 << 30;
-  for (int ci = 0; ci < nchunks; ++ci) {
-    uint32_t v[32];
-    tmem_ld32(t_row + ci * 32, v);
-    tmem_ld_wait();
+  int cmax = -(1 << 30);
+  if (warp_active) {
+    for (int ci = 0; ci < nchunks; ++ci) {
+      uint32_t v[16];
+      tmem_ld16(t_row + ci * 32, v);
+      tmem_ld_wait();
+      if (ci < nfull) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      int c = clampi(requant_i32_fast(static_cast<int>(v[j]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
-      if (ci * 32 + j < N) cmax = max(cmax, c);
-      v[j] = static_cast<uint32_t>(c);
-    }
-    uint32_t lo[16], hi[16];
+        for (int j = 0; j < 16; ++j) {
+          const int c = clampi(requant_i32_fast(static_cast<int>(v[j]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
+          cmax = max(cmax, c);
+          v[j] = static_cast<uint32_t>(c);
+        }
+      } else {
 #pragma unroll
-    for (int j = 0; j < 16; ++j) { lo[j] = v[j]; hi[j] = v[16 + j]; }
-    tmem_st16(t_row + ci * 32, lo);
-    tmem_st16(t_row + ci * 32 + 16, hi);
-  }
-  tmem_st_wait();
-  const float xmax = x_eff(static_cast<float>(cmax), a.p.s_attn);   // max of un-rounded x/s (monotone in code)
-  const float* trow = a.exp_table != nullptr ? a.exp_table + (cmax + 128) * 256 + 128 : nullptr;
-
-  // pass 2: exp terms, float32 row sum in torch's CPU order (8-wide vectors x 4 accumulators)
-  const int nvec = N / 8, size_ilp = nvec / 4;
-  float acc[32];
-#pragma unroll
-  for (int j = 0; j < 32; ++j) acc[j] = 0.f;
-  float p8[8];
-  float tail = 0.f;
-  for (int ci = 0; ci < nchunks; ++ci) {
-    uint32_t v[32];
-    tmem_ld32(t_row + ci * 32, v);
-    tmem_ld_wait();
-    float e[32];
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      const int c = static_cast<int>(v[j]);
-      e[j] = (ci * 32 + j < N) ? (trow != nullptr ? __ldg(trow + c) : softmax_term(c, xmax, a)) : 0.f;
-    }
-    if (ci < size_ilp) {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) acc[j] = __fadd_rn(acc[j], e[j]);
-    }
-    if (ci == size_ilp) {
-      // last, partial chunk: left-over whole vectors go to accumulator row 0 (before the rows
-      // are merged), the n%8 tail is summed separately
-#pragma unroll
-      for (int l = 0; l < 8; ++l) p8[l] = acc[l];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int col = ci * 32 + j;
-        if (col < nvec * 8) p8[j & 7] = __fadd_rn(p8[j & 7], e[j]);
-        else if (col < N) tail = __fadd_rn(tail, e[j]);
+        for (int j = 0; j < 16; ++j) {
+          const int c = clampi(requant_i32_fast(static_cast<int>(v[j]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
+          if (ci * 32 + cbase + j < N) cmax = max(cmax, c);
+          v[j] = static_cast<uint32_t>(c);
+        }
       }
+      tmem_st16(t_row + ci * 32, v);
     }
-    uint32_t lo[16], hi[16];
-#pragma unroll
-    for (int j = 0; j < 16; ++j) { lo[j] = __float_as_uint(e[j]); hi[j] = __float_as_uint(e[16 + j]); }
-    tmem_st16(t_row + ci * 32, lo);
-    tmem_st16(t_row + ci * 32 + 16, hi);
+    tmem_st_wait();
+    sMax[half * 128 + r_loc] = cmax;
   }
-  tmem_st_wait();
-  if (nchunks == size_ilp) {
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  float xmax = 0.f;
+  const float* trow = nullptr;
+  if (warp_active) {
+    cmax = max(sMax[r_loc], sMax[128 + r_loc]);
+    xmax = x_eff(static_cast<float>(cmax), a.p.s_attn);   // max of un-rounded x/s (monotone in code)
+    if (TABLE) trow = a.exp_table + (cmax + 128) * 256 + 128;
+  }
+  auto term = [&](int c) -> float { return TABLE ? __ldg(trow + c) : softmax_term(c, xmax, a); };
+
+  // pass 2: exp terms -> TMEM; float32 row sum in torch's CPU order: accumulator (col % 32) is
+  // acc[col % 16] of thread (col % 32) / 16, fed in ascending column order.
+  const int nvec = N / 8, size_ilp = nvec / 4;           // size_ilp == nfull
+  float acc[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+  if (warp_active) {
+    for (int ci = 0; ci < size_ilp; ++ci) {
+      uint32_t v[16];
+      tmem_ld16(t_row + ci * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const float e = term(static_cast<int>(v[j]));
+        acc[j] = __fadd_rn(acc[j], e);
+        v[j] = __float_as_uint(e);
+      }
+      tmem_st16(t_row + ci * 32, v);
+    }
+    if (nchunks > size_ilp) {          // partial chunk: exp terms only; its sum is thread A's job below
+      uint32_t v[16];
+      tmem_ld16(t_row + size_ilp * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        v[j] = (size_ilp * 32 + cbase + j < N) ? __float_as_uint(term(static_cast<int>(v[j]))) : 0u;
+      tmem_st16(t_row + size_ilp * 32, v);
+    }
+    tmem_st_wait();
+    if (half == 1) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) sAcc[j * 128 + r_loc] = acc[j];
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp_active && half == 0) {
+    // torch: ps[0] (lanes 0..7) += left-over whole vectors, THEN rows 1..3 are added, then the tail scalars
+    float p8[8];
 #pragma unroll
     for (int l = 0; l < 8; ++l) p8[l] = acc[l];
-  }
-#pragma unroll
-  for (int k = 1; k < 4; ++k)
-#pragma unroll
-    for (int l = 0; l < 8; ++l) p8[l] = __fadd_rn(p8[l], acc[8 * k + l]);
-  float sum = tail;
-#pragma unroll
-  for (int l = 0; l < 8; ++l) sum = __fadd_rn(sum, p8[l]);
-  if (a.p.kind == 0) sum = fminf(sum, 2147483648.f);               // ivit_modules.py:173
-  const float factor = floorf(__fdiv_rn(a.num, sum));              // :174 / ibert :314
-
-  // pass 3: probabilities -> u8 operand tile in shared memory (K-major, SWIZZLE_128B)
-  for (int ci = 0; ci < pchunks; ++ci) {
-    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (ci < nchunks) {
+    float tail = 0.f;
+    if (nchunks > size_ilp) {
       uint32_t v[32];
-      tmem_ld32(t_row + ci * 32, v);
+      tmem_ld32(t_row + size_ilp * 32, v);             // whole partial chunk (both halves' exp terms)
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
-        const float pf = floorf(__fmul_rn(__fmul_rn(__uint_as_float(v[j]), factor), a.out_shift));   // :175 / :315
-        const uint32_t pc = (ci * 32 + j < N) ? static_cast<uint32_t>(static_cast<int>(pf)) & 0xffu : 0u;
-        w[j >> 2] |= pc << (8 * (j & 3));
-      }
-      if (a.probs != nullptr && row < N) {
-        uint8_t* pr = a.probs + ((static_cast<long long>(blockIdx.y) * N + row) * N) + ci * 32;
-        for (int j = 0; j < 32 && ci * 32 + j < N; ++j) pr[j] = static_cast<uint8_t>(w[j >> 2] >> (8 * (j & 3)));
+        const int col = size_ilp * 32 + j;
+        const float e = __uint_as_float(v[j]);
+        if (col < nvec * 8) p8[j & 7] = __fadd_rn(p8[j & 7], e);
+        else if (col < N) tail = __fadd_rn(tail, e);
       }
     }
-    // 32 bytes = two 16-byte units of this row's 128-byte swizzle line
-    const int col = ci * 32;
-    uint8_t* base = sP + (col >> 7) * 16384 + (r_loc >> 3) * 1024 + (r_loc & 7) * 128;
-    const int u0 = (col & 127) >> 4;
-    *reinterpret_cast<int4*>(base + ((u0 ^ (r_loc & 7)) << 4)) = make_int4(w[0], w[1], w[2], w[3]);
-    *reinterpret_cast<int4*>(base + (((u0 + 1) ^ (r_loc & 7)) << 4)) = make_int4(w[4], w[5], w[6], w[7]);
+#pragma unroll
+    for (int l = 0; l < 8; ++l) p8[l] = __fadd_rn(p8[l], acc[8 + l]);
+#pragma unroll
+    for (int l = 0; l < 8; ++l) p8[l] = __fadd_rn(p8[l], sAcc[l * 128 + r_loc]);
+#pragma unroll
+    for (int l = 0; l < 8; ++l) p8[l] = __fadd_rn(p8[l], sAcc[(8 + l) * 128 + r_loc]);
+    float sum = tail;
+#pragma unroll
+    for (int l = 0; l < 8; ++l) sum = __fadd_rn(sum, p8[l]);
+    if (a.p.kind == 0) sum = fminf(sum, 2147483648.f);               // ivit_modules.py:173
+    const float factor = floorf(__fdiv_rn(a.num, sum));              // :174 / ibert :314
+    // floor(e*factor / 2^k) == floor(e * (factor / 2^k)): scaling by a power of two is exact
+    sFac[r_loc] = __fmul_rn(factor, a.out_shift);
   }
-  }  // warp_active
+  __syncthreads();
+
+  // pass 3: probabilities -> u8 operand tile in shared memory (K-major, SWIZZLE_128B)
+  if (warp_active) {
+    const float fs = sFac[r_loc];
+    for (int ci = 0; ci < pchunks; ++ci) {
+      uint32_t w[4] = {0, 0, 0, 0};
+      if (ci < nchunks) {
+        uint32_t v[16];
+        tmem_ld16(t_row + ci * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          // :175 / :315 (terms past column N were stored as 0)
+          const uint32_t pc = static_cast<uint32_t>(__float2int_rd(__fmul_rn(__uint_as_float(v[j]), fs))) & 0xffu;
+          w[j >> 2] |= pc << (8 * (j & 3));
+        }
+        if (TAP && a.probs != nullptr && row < N) {
+          uint8_t* pr = a.probs + ((static_cast<long long>(blockIdx.y) * N + row) * N) + ci * 32 + cbase;
+          for (int j = 0; j < 16 && ci * 32 + cbase + j < N; ++j) pr[j] = static_cast<uint8_t>(w[j >> 2] >> (8 * (j & 3)));
+        }
+      }
+      // 16 bytes = one 16-byte unit of this row's 128-byte swizzle line
+      const int col = ci * 32 + cbase;
+      uint8_t* base = sP + (col >> 7) * 16384 + (r_loc >> 3) * 1024 + (r_loc & 7) * 128;
+      const int u0 = (col & 127) >> 4;
+      *reinterpret_cast<int4*>(base + ((u0 ^ (r_loc & 7)) << 4)) = make_int4(w[0], w[1], w[2], w[3]);
+    }
+  }
   fence_proxy_async_smem();     // generic-proxy smem writes -> visible to tcgen05.mma
   tc_fence_before();
   __syncthreads();
@@ -263,25 +310,24 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   __syncwarp();
   mbar_wait(&bars[3], 0);
   tc_fence_after();
-  {
-    uint32_t o0[32], o1[32];
-    tmem_ld32(t_row, o0);
-    tmem_ld32(t_row + 32, o1);
+  if (warp_active) {
+    // O tile: columns [0,64); thread A stores head-dim 0..31, thread B 32..63.  The TMEM load is
+    // warp-collective (.sync.aligned): it must stay outside the per-lane row guard.
+    uint32_t o[32];
+    tmem_ld32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + half * 32, o);
     tmem_ld_wait();
-    if (warp_active && row < N && a.out != nullptr) {
-      uint32_t w[16];
+    if (row < N && a.out != nullptr) {
+      uint32_t w[8];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) w[j] = 0;
+      for (int j = 0; j < 8; ++j) w[j] = 0;
 #pragma unroll
-      for (int j = 0; j < 64; ++j) {
-        const int z = static_cast<int>(j < 32 ? o0[j] : o1[j - 32]);
-        const int c = clampi(requant_i32_fast(z, a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
+      for (int j = 0; j < 32; ++j) {
+        const int c = clampi(requant_i32_fast(static_cast<int>(o[j]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
         w[j >> 2] |= (static_cast<uint32_t>(c) & 0xffu) << (8 * (j & 3));
       }
-      int8_t* o = a.out + (static_cast<long long>(b) * N + row) * C + h * HD;
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        *reinterpret_cast<int4*>(o + 16 * j) = make_int4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+      int8_t* op = a.out + (static_cast<long long>(b) * N + row) * C + h * HD + half * 32;
+      *reinterpret_cast<int4*>(op) = make_int4(w[0], w[1], w[2], w[3]);
+      *reinterpret_cast<int4*>(op + 16) = make_int4(w[4], w[5], w[6], w[7]);
     }
   }
   tc_fence_before();
@@ -330,16 +376,24 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
   if ((rc = make_tmap_2d_u8(&tq, qkv, cols, rows, cols, HD, 128, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   if ((rc = make_tmap_2d_u8(&tk, qkv, cols, rows, cols, HD, a.NKP, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   if ((rc = make_tmap_2d_u8(&tv, qkv, cols, rows, cols, HD, a.KP2, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
-  const size_t smem = 1024 + 32768 + 8192 + 16384 + 16384 + 64;
+  const size_t smem = 1024 + 32768 + 8192 + 16384 + 16384 + 16 * 128 * 4 + 256 * 4 + 128 * 4 + 64;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(attention_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>(smem));
+    cudaError_t e = cudaSuccess;
+    const int sm = static_cast<int>(smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_i8_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_i8_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_i8_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_i8_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
     if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
     attr_set = true;
   }
   dim3 grid((N + 127) / 128, B * H);
-  attention_i8_kernel<<<grid, 128, smem, st>>>(tq, tk, tv, a);
+  const bool table = a.exp_table != nullptr, tap = probs != nullptr;
+  if (table && !tap) attention_i8_kernel<true, false><<<grid, 256, smem, st>>>(tq, tk, tv, a);
+  else if (table && tap) attention_i8_kernel<true, true><<<grid, 256, smem, st>>>(tq, tk, tv, a);
+  else if (!table && !tap) attention_i8_kernel<false, false><<<grid, 256, smem, st>>>(tq, tk, tv, a);
+  else attention_i8_kernel<false, true><<<grid, 256, smem, st>>>(tq, tk, tv, a);
   return check_launch("attention_i8_kernel");
 }
 

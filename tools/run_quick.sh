@@ -2,9 +2,10 @@
 # quick iteration: parity (kernels + plan) then one bench line
 mkdir -p gpurun_out
 T=${1:-q}
-timeout 900 python -m pytest tests/test_kernels_gpu.py tests/test_plan_gpu.py -q --timeout 600 -p no:cacheprovider -x > gpurun_out/${T}_tests.log 2>&1
+timeout 300 python -m pytest tests/test_kernels_gpu.py tests/test_plan_gpu.py -q --timeout 120 -p no:cacheprovider -x > gpurun_out/${T}_tests.log 2>&1
 echo "tests exit $?" >> gpurun_out/${T}_tests.log
-timeout 900 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err
+grep -q "tests exit 0" gpurun_out/${T}_tests.log || { tail -n 30 gpurun_out/${T}_tests.log; exit 1; }
+timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err
 echo "bench exit $?" >> gpurun_out/${T}_bench.err
 tail -n 12 gpurun_out/${T}_tests.log gpurun_out/${T}_bench.err
 python - <<PY
