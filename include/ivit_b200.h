@@ -60,12 +60,17 @@ int ivit_gelu_lut_build(int kind, int8_t* lut, float s_in, int output_bit, doubl
 int ivit_gelu_ivit_raw_table(float* out65536, float s_in, int output_bit, void* stream);
 int ivit_gelu_lut_apply_i8(const int8_t* x, int8_t* out, const int8_t* lut, int rows, int C, void* stream);
 
-/* ---- stand-alone QuantAct on int32 accumulators (un-fused path) ------------------------
- * quant_utils.py:193-253.  z int32 [rows, C]; s_in/mult have C entries if per_channel else 1;
- * identity (may be NULL) int8 [rows, C] with scalar mult_id. */
+/* ---- stand-alone QuantAct on integer codes (un-fused module path) -----------------------
+ * quant_utils.py:193-253.  z int32 accumulators (after QuantLinear / QuantMatMul) or int8 codes
+ * (after a previous QuantAct) [rows, C]; s_in/mult have C entries if per_channel else 1;
+ * identity (may be NULL) int8 [id_rows, C] with scalar mult_id, broadcast over rows when
+ * 0 < id_rows < rows (the positional embedding of vit_quant.py:295-296). */
 int ivit_requant_i32_i8(const int32_t* z, const float* s_in, const double* mult, int per_channel,
-                        const int8_t* identity, double mult_id, int8_t* out, int64_t rows, int C, int qmin, int qmax,
-                        void* stream);
+                        const int8_t* identity, int64_t id_rows, double mult_id, int8_t* out, int64_t rows, int C,
+                        int qmin, int qmax, void* stream);
+int ivit_requant_i8_i8(const int8_t* z, const float* s_in, const double* mult, int per_channel,
+                       const int8_t* identity, int64_t id_rows, double mult_id, int8_t* out, int64_t rows, int C,
+                       int qmin, int qmax, void* stream);
 int ivit_dequant_i8_f32(const int8_t* q, float scale, float* out, int64_t n, void* stream);
 int ivit_fill_cls_rows_i8(int8_t* out, const int8_t* cls_row, int B, int N, int C, void* stream);
 

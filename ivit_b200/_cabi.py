@@ -64,8 +64,10 @@ _SIGS = {
                                       C.POINTER(C.c_float), C.c_void_p]),
     "ivit_gelu_ivit_raw_table": (C.c_int, [C.c_void_p, C.c_float, C.c_int, C.c_void_p]),
     "ivit_gelu_lut_apply_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
-    "ivit_requant_i32_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_double,
+    "ivit_requant_i32_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_double,
                                       C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "ivit_requant_i8_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_double,
+                                     C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "ivit_dequant_i8_f32": (C.c_int, [C.c_void_p, C.c_float, C.c_void_p, C.c_int64, C.c_void_p]),
     "ivit_fill_cls_rows_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "ivit_gemm_i8": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,

@@ -375,18 +375,24 @@ __global__ void fill_cls_rows_kernel(int8_t* __restrict__ out, const int8_t* __r
   out[(static_cast<long long>(b) * N) * C + c] = cls_row[c];
 }
 
-// Stand-alone QuantAct on int32 accumulators (generic / un-fused path and tests):
+// Stand-alone QuantAct on integer codes (un-fused module path and tests):
 // out = clamp(rint(z*mult[c]) [+ rint(id*mult_id)])   quant_utils.py:220-251
-__global__ void requant_i32_kernel(const int32_t* __restrict__ z, const float* __restrict__ s_in,
-                                   const double* __restrict__ mult, int per_channel, const int8_t* __restrict__ id,
-                                   double mult_id, int8_t* __restrict__ out, long long rows, int C, int qmin,
-                                   int qmax) {
+// z int32 (accumulators) or int8 (codes of a previous QuantAct); identity int8 [id_rows, C] with
+// id_rows dividing rows (positional embedding broadcast over the batch: row % id_rows).
+template <typename ZT>
+__global__ void requant_kernel(const ZT* __restrict__ z, const float* __restrict__ s_in,
+                               const double* __restrict__ mult, int per_channel, const int8_t* __restrict__ id,
+                               long long id_rows, double mult_id, int8_t* __restrict__ out, long long rows, int C,
+                               int qmin, int qmax) {
   const long long n = rows * C;
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < n;
        t += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int c = per_channel ? static_cast<int>(t % C) : 0;
-    double r = requant_any(z[t], s_in[c], mult[c]);
-    if (id != nullptr) r += requant_d(static_cast<double>(id[t]), mult_id);
+    double r = requant_any(static_cast<int>(z[t]), s_in[c], mult[c]);
+    if (id != nullptr) {
+      const long long it = (id_rows > 0 && id_rows < rows) ? ((t / C) % id_rows) * C + t % C : t;
+      r += requant_d(static_cast<double>(id[it]), mult_id);
+    }
     out[t] = static_cast<int8_t>(static_cast<int>(fmin(fmax(r, (double)qmin), (double)qmax)));
   }
 }
@@ -551,13 +557,25 @@ extern "C" int ivit_gelu_lut_apply_i8(const int8_t* x, int8_t* out, const int8_t
 }
 
 extern "C" int ivit_requant_i32_i8(const int32_t* z, const float* s_in, const double* mult, int per_channel,
-                                   const int8_t* identity, double mult_id, int8_t* out, int64_t rows, int C,
-                                   int qmin, int qmax, void* stream) {
+                                   const int8_t* identity, int64_t id_rows, double mult_id, int8_t* out, int64_t rows,
+                                   int C, int qmin, int qmax, void* stream) {
   const long long n = rows * C;
   if (n <= 0) return 0;
-  requant_i32_kernel<<<ew_grid(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      z, s_in, mult, per_channel, identity, mult_id, out, rows, C, qmin, qmax);
-  return check_launch("requant_i32_kernel");
+  if (identity != nullptr && id_rows > 0 && rows % id_rows != 0) return fail(IVIT_ERR_BAD_ARG, "requant: id_rows must divide rows");
+  requant_kernel<int32_t><<<ew_grid(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      z, s_in, mult, per_channel, identity, id_rows, mult_id, out, rows, C, qmin, qmax);
+  return check_launch("requant_kernel<int32>");
+}
+
+extern "C" int ivit_requant_i8_i8(const int8_t* z, const float* s_in, const double* mult, int per_channel,
+                                  const int8_t* identity, int64_t id_rows, double mult_id, int8_t* out, int64_t rows,
+                                  int C, int qmin, int qmax, void* stream) {
+  const long long n = rows * C;
+  if (n <= 0) return 0;
+  if (identity != nullptr && id_rows > 0 && rows % id_rows != 0) return fail(IVIT_ERR_BAD_ARG, "requant: id_rows must divide rows");
+  requant_kernel<int8_t><<<ew_grid(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      z, s_in, mult, per_channel, identity, id_rows, mult_id, out, rows, C, qmin, qmax);
+  return check_launch("requant_kernel<int8>");
 }
 
 extern "C" int ivit_dequant_i8_f32(const int8_t* q, float scale, float* out, int64_t n, void* stream) {

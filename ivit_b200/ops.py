@@ -80,15 +80,27 @@ def gelu_lut_apply(x: torch.Tensor, lut: torch.Tensor, out: torch.Tensor | None 
     return out
 
 
-def requant_i32(z: torch.Tensor, s_in: torch.Tensor, mult: torch.Tensor, qmin: int, qmax: int,
-                identity: torch.Tensor | None = None, mult_id: float = 0.0) -> torch.Tensor:
-    assert z.dtype == torch.int32 and z.is_contiguous()
+def requant(z: torch.Tensor, s_in: torch.Tensor, mult: torch.Tensor, qmin: int, qmax: int,
+            identity: torch.Tensor | None = None, mult_id: float = 0.0, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Stand-alone QuantAct on int32 or int8 codes [..., C]; identity int8 [id_rows, C] broadcast over rows."""
+    assert z.dtype in (torch.int32, torch.int8) and z.is_contiguous()
     Cdim = z.shape[-1]
-    out = torch.empty(z.shape, dtype=torch.int8, device=z.device)
-    check(_cabi.load().ivit_requant_i32_i8(ptr(z), ptr(s_in), ptr(mult), int(mult.numel() > 1), ptr(identity),
-                                           C.c_double(mult_id), ptr(out), z.numel() // Cdim, Cdim, qmin, qmax,
-                                           stream()), "ivit_requant_i32_i8")
+    rows = z.numel() // Cdim
+    if out is None:
+        out = torch.empty(z.shape, dtype=torch.int8, device=z.device)
+    id_rows = 0
+    if identity is not None:
+        assert identity.dtype == torch.int8 and identity.is_contiguous() and identity.shape[-1] == Cdim
+        id_rows = identity.numel() // Cdim
+    lib = _cabi.load()
+    fn = lib.ivit_requant_i32_i8 if z.dtype == torch.int32 else lib.ivit_requant_i8_i8
+    check(fn(ptr(z), ptr(s_in), ptr(mult), int(mult.numel() > 1), ptr(identity), id_rows, C.c_double(mult_id),
+             ptr(out), rows, Cdim, qmin, qmax, stream()), "ivit_requant")
     return out
+
+
+def requant_i32(z, s_in, mult, qmin, qmax, identity=None, mult_id=0.0):
+    return requant(z, s_in, mult, qmin, qmax, identity, mult_id)
 
 
 def dequant(q: torch.Tensor, scale: float) -> torch.Tensor:

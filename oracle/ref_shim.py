@@ -79,3 +79,24 @@ def torch_threads(n: int | None = None):
         yield
     finally:
         torch.set_num_threads(old)
+
+
+def load_reference_callers_on(qu_package, alias: str = "models_on_b200"):
+    """Import the reference's UNMODIFIED caller files (vit_quant.py, layers_quant.py, model_utils.py)
+    with `.quantization_utils` resolved to `qu_package` (e.g. ivit_b200.quantization_utils): the
+    "vit_quant.py runs unchanged on top of it" check.  Returns (vit_quant, model_utils) modules."""
+    import importlib
+
+    if alias + ".vit_quant" in sys.modules:
+        return sys.modules[alias + ".vit_quant"], sys.modules[alias + ".model_utils"]
+    if not reference_available():
+        raise RuntimeError(f"reference not mounted at {REFERENCE_ROOT}")
+    _install_stubs()
+    pkg = types.ModuleType(alias)
+    pkg.__path__ = [os.path.join(REFERENCE_ROOT, "models")]      # a package without running models/__init__.py
+    pkg.__package__ = alias
+    sys.modules[alias] = pkg
+    sys.modules[alias + ".quantization_utils"] = qu_package
+    vq = importlib.import_module(alias + ".vit_quant")
+    mu = importlib.import_module(alias + ".model_utils")
+    return vq, mu
