@@ -62,3 +62,30 @@ class InferenceSession:
         out = self.infer_async(images)
         self.synchronize()
         return out
+
+
+def config_from_model(model) -> VitConfig:
+    """VitConfig of a VisionTransformer built on the quantization_utils module API (the reference's
+    vit_quant.py class or any caller with the same attribute names)."""
+    blk = model.blocks[0]
+    C = model.head.in_features
+    P = model.patch_embed.proj.kernel_size[0]
+    tokens = model.pos_embed.shape[1]
+    side = int(round((tokens - 1) ** 0.5))
+
+    def kind(mod):
+        name = "ivit" if getattr(mod, "_kind", 0) == 0 else "ibert"
+        return name + ("_use-int-sqrt_true" if getattr(mod, "use_int_sqrt", False) else "")
+    bw = (model.patch_embed.qact.activation_bit, model.qact_pos.activation_bit, model.qact1.activation_bit,
+          blk.attn.qact3.activation_bit, blk.attn.int_softmax.output_bit, blk.mlp.qact2.activation_bit,
+          blk.qact2.activation_bit, blk.qact4.activation_bit)
+    return VitConfig(name="custom", embed_dim=C, depth=len(model.blocks), num_heads=blk.attn.num_heads,
+                     mlp_ratio=blk.mlp.fc1.out_features // C, img_size=side * P, patch_size=P,
+                     in_chans=model.patch_embed.proj.in_channels, num_classes=model.head.out_features, bitwidths=bw,
+                     gelu_type=kind(blk.mlp.act), softmax_type=kind(blk.attn.int_softmax), layernorm_type=kind(blk.norm1))
+
+
+def compile_frozen(model, batch: int, device="cuda", chunks: int = 1) -> InferenceSession:
+    """Frozen module-API model (after calibration + freeze_model) -> the fused static plan: same
+    integer results, ~100 launches per forward instead of one Python call per module."""
+    return InferenceSession(config_from_model(model), model.state_dict(), batch, device, chunks)
