@@ -65,8 +65,26 @@ __global__ void quantize_kernel(const float* __restrict__ x, int8_t* __restrict_
 //    Inside the clamp range |v*mult| < 130 the float32 product v*fl32(mult) is within 5e-5 of
 //    z*mult, so unless it lies within 1e-4 of a rounding tie (p ~ 2e-4) rintf of it IS the
 //    exact answer; outside the range both clamp.  Near ties take the replay path.
-template <int NPL, int R>
-__global__ void __launch_bounds__(256)
+// Exact replay of the QuantAct that follows the LayerNorm for one element (out of line: it runs for
+// ~2e-4 of the elements, and inlining it 48 times made the loop body miss the instruction cache).
+__device__ __noinline__ int ln_requant_exact(float v, float sc, double mult, int qmin, int qmax) {
+  const float xo = __fmul_rn(v, sc);                                                            // :63
+  const float z = rintf(__fdiv_rn(xo, sc));                                                     // quant_utils.py:220
+  const double rd = requant_d(static_cast<double>(z), mult);                                    // :229-230
+  return static_cast<int>(fmin(fmax(rd, static_cast<double>(qmin)), static_cast<double>(qmax)));
+}
+
+// float32 sum of one row's un-rounded x/s in torch's CPU order (exact-tie rows only; out of line).
+template <int NPL>
+__device__ __noinline__ float ln_torch_row_sum(const float (&xe)[NPL], int lane) {
+  TorchSum32 acc;
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) acc.add(xe[i]);
+  return torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+}
+
+template <int NPL, int R, int MINB>
+__global__ void __launch_bounds__(256, MINB)
 layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows,
                               float s_in, const float* __restrict__ bias_int, const float* __restrict__ sf,
                               const double* __restrict__ mult, int qmin, int qmax) {
@@ -137,10 +155,10 @@ layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, long long ldx, int8_
       // float32 noise of the un-rounded inputs; then replay torch's summation order.
       float sum_f = static_cast<float>(S[r]);
       if (((S[r] % C) + C) % C * 2 == C) {                      // warp-uniform, rare
-        TorchSum32 acc;
+        float xe[NPL];
 #pragma unroll
-        for (int i = 0; i < NPL; ++i) acc.add(lut_f[y[r][i]]);
-        sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+        for (int i = 0; i < NPL; ++i) xe[i] = lut_f[y[r][i]];
+        sum_f = ln_torch_row_sum<NPL>(xe, lane);
       }
       mean[r] = static_cast<int>(rintf(__fdiv_rn(sum_f, static_cast<float>(C))));
     }
@@ -203,12 +221,7 @@ layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, long long ldx, int8_
             const float yf = static_cast<float>(y[r][i]);
             float v = floorf(__fmul_rn(__fmul_rn(yf, factor[r]), 0.5f));                        // :52
             v = __fadd_rn(v, bia[i]);                                                           // :61
-            const float sc = __ldg(sf + c);
-            const float xo = __fmul_rn(v, sc);                                                  // :63
-            const float z = rintf(__fdiv_rn(xo, sc));                                           // quant_utils.py:220
-            const double rd = requant_d(static_cast<double>(z), __ldg(mult + c));               // :229-230
-            const int code = static_cast<int>(fmin(fmax(rd, static_cast<double>(qmin)), static_cast<double>(qmax)));
-            stage[warp][buf][r][c] = static_cast<int8_t>(code);
+            stage[warp][buf][r][c] = static_cast<int8_t>(ln_requant_exact(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax));
           }
         }
       }
@@ -409,6 +422,7 @@ __global__ void dequant_i8_kernel(const int8_t* __restrict__ q, float s, float* 
 // =============================================================================== C ABI
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace ivit {
@@ -473,8 +487,8 @@ static int launch_ln(int kind, const int8_t* x, long long ldx, int8_t* out, int 
     constexpr int R = NPL <= 12 ? 4 : 2;
     const int groups = (rows + R - 1) / R;
     const int pgrid = min((groups + 7) / 8, 148 * 4);     // persistent: a few CTAs per SM
-    layernorm_ivit_requant_kernel<NPL, R><<<pgrid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin,
-                                                                qmax);
+    layernorm_ivit_requant_kernel<NPL, R, 2><<<pgrid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin,
+                                                                   qmax);
   } else {
     const float sp = ldexpf(1.f, static_cast<int>(shift));
     layernorm_ibert_requant_kernel<NPL><<<grid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp,
