@@ -114,6 +114,10 @@ typedef struct {
 } ivit_gemm_epilogue_t;
 int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M, int N, int K, void* out, int64_t ldo,
                  const ivit_gemm_epilogue_t* epi, void* stream);
+/* ivit_gemm_i8 has two tcgen05 kernels: tokens on TMEM lanes (every epilogue) and channels on
+ * TMEM lanes (REQUANT / RESIDUAL hot shapes).  layout 0 = choose per call (default), 1 = always
+ * the first.  Returns the previous setting.  Process-wide; for A/B timing and tests. */
+int ivit_gemm_set_layout(int layout);
 /* Straightforward CUDA-core int8 GEMM with the same epilogues: on-device cross-check for
  * the tcgen05 kernel at sizes the CPU oracle cannot reach.  Not used by the product path. */
 int ivit_gemm_i8_simple(const int8_t* A, int64_t lda, const int8_t* W, int M, int N, int K, void* out, int64_t ldo,

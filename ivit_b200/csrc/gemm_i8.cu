@@ -401,6 +401,267 @@ gemm_i8_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
 }
 
+// ------------------------------------------------------------------ channels-on-lanes kernel
+// Same pipeline with the operand roles swapped: D^T[n, token] = W[n,:] . A[token,:], i.e. the
+// WEIGHT tile (128 output channels) is the M operand and a 192-token tile the N operand.  In TMEM
+// a lane is now an output CHANNEL and a column a token, so every per-channel epilogue constant
+// (mult, bias) is a per-thread register loaded once per tile -- the row-major kernel above pays a
+// 16-byte shared-memory broadcast per column per warp for them, which is what bounds it (l1tex).
+// Codes of 4 tokens are packed per register and 4x4-byte-transposed across lane quads (two
+// SHFL.BFLY + two PRMT), after which lane 4k+i holds channels 4k..4k+3 of token 4g+i: 4-byte
+// stores, 32 contiguous bytes per token per warp.  The residual identity comes in the same way.
+// Streamlined REQUANT / RESIDUAL only (no row remap); everything else stays on the kernel above.
+struct ClCfg {
+  static constexpr int CB = 128;                                 // channels per tile (UMMA M)
+  static constexpr int TB = 192;                                 // tokens per tile (UMMA N)
+  static constexpr int W_BYTES = CB * BK;
+  static constexpr int A_BYTES = TB * BK;
+  static constexpr int STAGE_BYTES = W_BYTES + A_BYTES;
+  static constexpr int STAGES = 5;
+  static constexpr int ACC_STRIDE = 256;
+  static constexpr uint32_t TMEM_COLS = 512;
+  static constexpr int PART = 64;                                // tokens per epilogue warp
+  static constexpr int NPARTS = TB / PART;
+  static constexpr int EPI_WARPS = 4 * NPARTS;
+  static constexpr int THREADS = 64 + 32 * EPI_WARPS;
+  static constexpr int NCH = PART / 16;
+  static constexpr size_t SMEM = STAGES * STAGE_BYTES + 256;
+};
+
+// 4x4 byte transpose across the 4 lanes of a quad: in: lane i holds bytes T[i][0..3]; out: T[0..3][i]
+__device__ __forceinline__ uint32_t quad_transpose(uint32_t x, uint32_t sel1, uint32_t sel2) {
+  uint32_t y = __shfl_xor_sync(0xffffffffu, x, 1);
+  x = __byte_perm(x, y, sel1);
+  y = __shfl_xor_sync(0xffffffffu, x, 2);
+  return __byte_perm(x, y, sel2);
+}
+
+__device__ __noinline__ int cl_requant_exact(int z, float s_in, double mult, int qmin, int qmax) {
+  const double r = requant_any(z, s_in, mult);
+  return static_cast<int>(fmin(fmax(r, static_cast<double>(qmin)), static_cast<double>(qmax)));
+}
+
+template <int MODE, bool CHECKED>
+__global__ void __launch_bounds__(ClCfg::THREADS, 1)
+gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                  const GemmArgs args) {
+  using Cfg = ClCfg;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* tail = smem + STAGES * Cfg::STAGE_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ncb = (args.N + Cfg::CB - 1) / Cfg::CB;
+  const int ntiles = ((args.M + Cfg::TB - 1) / Cfg::TB) * ncb;
+  const int kblocks = (args.K + BK - 1) / BK;
+  const ivit_gemm_epilogue_t& e = args.e;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], Cfg::EPI_WARPS);
+    }
+    fence_mbar_init();
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer (channel block fastest:
+    // the CTAs running together read the same token tile; the weights stay in L2 throughout)
+    if (elect_one()) {
+      int it = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int c0 = (t % ncb) * Cfg::CB, t0 = (t / ncb) * Cfg::TB;
+        for (int kb = 0; kb < kblocks; ++kb, ++it) {
+          const int s = it % STAGES;
+          mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+          uint8_t* sw = smem + s * Cfg::STAGE_BYTES;
+          mbar_arrive_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
+          tma_load_2d(sw, &tmW, &full_bar[s], kb * BK, c0);
+          tma_load_2d(sw + Cfg::W_BYTES, &tmA, &full_bar[s], kb * BK, t0);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_i8(Cfg::CB, Cfg::TB, true, true, false, false);
+      int it = 0, i = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++i) {
+        const int a = i & 1;
+        mbar_wait(&tempty_bar[a], ((i >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + a * Cfg::ACC_STRIDE;
+        for (int kb = 0; kb < kblocks; ++kb, ++it) {
+          const int s = it % STAGES;
+          mbar_wait(&full_bar[s], (it / STAGES) & 1);
+          tc_fence_after();
+          const uint32_t sw = smem_u32(smem + s * Cfg::STAGE_BYTES);
+          const uint32_t sa = sw + Cfg::W_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t dw = make_smem_desc(sw + k * UMMA_K, 16, 1024, kLayoutSW128);
+            const uint64_t da = make_smem_desc(sa + k * UMMA_K, 16, 1024, kLayoutSW128);
+            mma_i8_ss(d_tmem, dw, da, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          tc_commit(&empty_bar[s]);
+        }
+        tc_commit(&tfull_bar[a]);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===================================================== epilogue (thread = output channel)
+    const int ew = warp - 2;
+    const int quarter = warp & 3;
+    const int part = ew >> 2;
+    const uint32_t sel1 = (lane & 1) ? 0x3715u : 0x6240u;
+    const uint32_t sel2 = (lane & 2) ? 0x3276u : 0x5410u;
+    const int qi = lane & 3;                 // after the transpose: this lane's token within a group of 4
+    const int qc = (lane >> 2) * 4;          //                      and its first channel within the warp's 32
+    int pb = 0;
+    double pm = 0.0;
+    auto fetch_params = [&](int t) {
+      const int n = (t % ncb) * Cfg::CB + quarter * 32 + lane;
+      pb = (e.bias != nullptr && n < args.N) ? __ldg(e.bias + n) : 0;
+      pm = n < args.N ? __ldg(e.mult + n) : 0.0;
+    };
+    if (blockIdx.x < ntiles) fetch_params(blockIdx.x);
+    int8_t* const outp = static_cast<int8_t*>(args.out);
+    const double m2 = e.mult2, mi = e.mult_id;
+    int i = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++i) {
+      const int a = i & 1;
+      const int c0 = (t % ncb) * Cfg::CB + quarter * 32;       // the warp's first channel
+      const int tok_w = (t / ncb) * Cfg::TB + part * Cfg::PART;  // the warp's first token
+      const int n = c0 + lane;
+      const double mult = pm;
+      const double kb = kMagicInt - static_cast<double>(pb);
+      const int brange = pb + (1 << 22);                       // CHECKED: 0 <= acc + brange < 2^23
+      if (t + gridDim.x < ntiles) fetch_params(t + gridDim.x);
+      const int nq = c0 + qc;                                  // channels nq..nq+3 after the transpose
+      const bool nq_ok = nq < args.N;                          // N % 4 == 0 (host-checked)
+
+      // lane-private row pointers (token tok_w + qi, channel nq), bumped 4 rows per group
+      const bool all_ok = tok_w + Cfg::PART <= args.M && c0 + 32 <= args.N;   // warp-uniform: no guards
+      const long long ldo4 = 4 * args.ldo, ldi4 = 4 * e.ld_id;
+      int8_t* op = outp + static_cast<long long>(tok_w + qi) * args.ldo + nq;
+      const int8_t* ip = MODE == 2 ? e.identity + static_cast<long long>(tok_w + qi) * e.ld_id + nq : nullptr;
+      auto load_identity = [&](int ch, uint32_t (&w)[4]) {
+        if (all_ok) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) w[g] = __ldg(reinterpret_cast<const uint32_t*>(ip + g * ldi4));
+        } else {
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            w[g] = (nq_ok && tok_w + ch * 16 + 4 * g + qi < args.M)
+                       ? __ldg(reinterpret_cast<const uint32_t*>(ip + g * ldi4)) : 0u;
+        }
+        ip += 4 * ldi4;
+      };
+      uint32_t idw[2][4];
+      if (MODE == 2) load_identity(0, idw[0]);
+
+      mbar_wait(&tfull_bar[a], (i >> 1) & 1);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + a * Cfg::ACC_STRIDE + part * Cfg::PART +
+                             (static_cast<uint32_t>(quarter * 32) << 16);
+      uint32_t acc[2][16];
+      tmem_ld16(t_row, acc[0]);
+#pragma unroll
+      for (int ch = 0; ch < Cfg::NCH; ++ch) {
+        tmem_ld_wait();
+        if (ch + 1 < Cfg::NCH) {
+          tmem_ld16(t_row + (ch + 1) * 16, acc[(ch + 1) & 1]);
+          if (MODE == 2) load_identity(ch + 1, idw[(ch + 1) & 1]);
+        } else {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty_bar[a]);
+        }
+        const uint32_t(&z)[16] = acc[ch & 1];
+        const int tok0 = tok_w + ch * 16;
+        if (tok0 >= args.M) continue;        // warp-uniform (and nothing collective follows for this chunk)
+        int c[16];
+        bool fast = true;
+        if (CHECKED) {
+          uint32_t bits = 0;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) bits |= static_cast<uint32_t>(static_cast<int>(z[j]) + brange);
+          fast = __all_sync(0xffffffffu, (bits & 0xff800000u) == 0u);
+        }
+        if (fast) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const double zd = __hiloint2double(0x43300000, static_cast<int>(z[j] ^ 0x80000000u)) - kb;
+            c[j] = __double2loint(__fma_rn(zd, mult, kMagicRnd));
+          }
+        } else {
+#pragma unroll
+          const float s_in = n < args.N ? __ldg(e.s_in + n) : 1.0f;      // rare: out-of-range chunk
+          const int bias = brange - (1 << 22);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) c[j] = cl_requant_exact(static_cast<int>(z[j]) + bias, s_in, mult, e.qmin, e.qmax);
+        }
+        if (MODE == 2) {
+          // identity words arrive token-major (lane = token, bytes = channels): transpose to
+          // channel-major (lane = channel, bytes = tokens) to meet the accumulators
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const uint32_t iw = quad_transpose(idw[ch & 1][g], sel1, sel2);
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+              const int j = 4 * g + b;
+              const int c1 = clampi(c[j], -128, 127);
+              const int id = static_cast<int8_t>(iw >> (8 * b));
+              const double cd = __hiloint2double(0x43300000, c1 ^ 0x80000000) - kMagicInt;
+              const double dd = __hiloint2double(0x43300000, id ^ 0x80000000) - kMagicInt;
+              c[j] = __double2loint(__fma_rn(cd, m2, kMagicRnd)) + __double2loint(__fma_rn(dd, mi, kMagicRnd));
+            }
+          }
+        }
+        uint32_t w[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          w[g] = quad_transpose(pack4_sat_s8(c[4 * g], c[4 * g + 1], c[4 * g + 2], c[4 * g + 3]), sel1, sel2);
+        int8_t* o = op + ch * (4 * ldo4);
+        if (all_ok) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) *reinterpret_cast<uint32_t*>(o + g * ldo4) = w[g];
+        } else {
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            if (nq_ok && tok0 + 4 * g + qi < args.M) *reinterpret_cast<uint32_t*>(o + g * ldo4) = w[g];
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
 // ------------------------------------------------------------------ simple cross-check kernel
 __global__ void gemm_i8_simple_kernel(const int8_t* __restrict__ A, long long lda, const int8_t* __restrict__ W,
                                       const GemmArgs args) {
@@ -523,6 +784,37 @@ static int launch_ws(const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& ar
   return check_launch("gemm_i8_ws_kernel");
 }
 
+template <int MODE, bool CHECKED>
+static int launch_cl(const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& args, cudaStream_t st) {
+  using Cfg = ClCfg;
+  CUtensorMap tmA, tmW;
+  int rc = make_tmap_2d_u8(&tmA, A, args.K, args.M, lda, BK, Cfg::TB, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  rc = make_tmap_2d_u8(&tmW, W, args.K, args.N, args.K, BK, Cfg::CB, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  args.stages = Cfg::STAGES;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_i8_cl_kernel<MODE, CHECKED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(Cfg::SMEM));
+    if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
+    attr_set = true;
+  }
+  const int ntiles = ((args.M + Cfg::TB - 1) / Cfg::TB) * ((args.N + Cfg::CB - 1) / Cfg::CB);
+  const int grid = ntiles < sm_count() ? ntiles : sm_count();
+  gemm_i8_cl_kernel<MODE, CHECKED><<<grid, Cfg::THREADS, Cfg::SMEM, st>>>(tmA, tmW, args);
+  return check_launch("gemm_i8_cl_kernel");
+}
+
+// 0: pick per call (default); 1: keep every GEMM on the row-major-epilogue kernel (A/B timing, tests)
+static int g_gemm_layout = 0;
+extern "C" int ivit_gemm_set_layout(int layout) {
+  const int prev = g_gemm_layout;
+  g_gemm_layout = layout;
+  return prev;
+}
+static bool channels_on_lanes_enabled() { return g_gemm_layout == 0; }
+
 template <int BN>
 static int launch_mode(int mode, bool checked, const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& args,
                        cudaStream_t st) {
@@ -553,8 +845,15 @@ extern "C" int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M
              fabs(epi->mult_id) < 65536.0)
       mode = 2;
   }
-  // BN = 192 divides every DeiT/ViT width (3C, C, 4C for C = 192/384/768); 128 otherwise
   const bool checked = epi->z_bound_ok == 0;
+  // Hot shapes: channels-on-lanes kernel (per-channel constants in registers).  Needs 4-byte
+  // aligned output / identity rows and no row remap.
+  if (mode != 0 && epi->group <= 0 && N % 4 == 0 && ldo % 4 == 0 && (mode == 1 || epi->ld_id % 4 == 0) &&
+      channels_on_lanes_enabled()) {
+    if (mode == 1) return checked ? launch_cl<1, true>(A, lda, W, args, st) : launch_cl<1, false>(A, lda, W, args, st);
+    return checked ? launch_cl<2, true>(A, lda, W, args, st) : launch_cl<2, false>(A, lda, W, args, st);
+  }
+  // BN = 192 divides every DeiT/ViT width (3C, C, 4C for C = 192/384/768); 128 otherwise
   if (N % 192 == 0 || N > 512) return launch_mode<192>(mode, checked, A, lda, W, args, st);
   return launch_mode<128>(mode, checked, A, lda, W, args, st);
 }

@@ -147,6 +147,11 @@ def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=Non
     return out
 
 
+def set_gemm_layout(layout: int) -> int:
+    """0: ivit_gemm_i8 picks its kernel per call; 1: tokens-on-lanes kernel only.  Returns the old value."""
+    return _cabi.load().ivit_gemm_set_layout(int(layout))
+
+
 def softmax_table_build(params: AttentionParams, device) -> torch.Tensor:
     """Tabulate the softmax exp term over (row-max code, code) and attach it to `params`.  The
     returned tensor owns the memory: keep it alive as long as `params` is used."""

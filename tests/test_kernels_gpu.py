@@ -177,23 +177,27 @@ def _gemm_case(M, N, K, seed, epilogue, group=0, bounded=False):
         kw.update(group=group, out_group_stride=group + 1, out_row_off=1, id_broadcast=True)
         out_rows = (M // group) * (group + 1)
     res = {}
-    for simple in (True, False):
+    for variant in ("simple", "rows", "auto"):       # CUDA-core cross-check, tokens-on-lanes, per-call choice
+        simple = variant == "simple"
         out = None
         if out_rows:
             odt = torch.int8
             out = torch.full((out_rows, N), 99, dtype=odt, device=DEV)
-        got = ops.gemm(_t(A, torch.int8), _t(W, torch.int8), epilogue, simple=simple, out=out,
-                       z_bound_ok=(bounded and not simple), **kw).cpu().numpy()
+        prev = ops.set_gemm_layout(1 if variant == "rows" else 0)
+        try:
+            got = ops.gemm(_t(A, torch.int8), _t(W, torch.int8), epilogue, simple=simple, out=out,
+                           z_bound_ok=(bounded and not simple), **kw).cpu().numpy()
+        finally:
+            ops.set_gemm_layout(prev)
         if group:
             got = got.reshape(M // group, group + 1, N)[:, 1:].reshape(M, N)
-        res[simple] = got
+        res[variant] = got
     name = f"gemm M={M} N={N} K={K} epi={epilogue}"
-    if epilogue == _cabi.EPI_LOGITS:
-        assert np.array_equal(res[True], exp), name + " simple"
-        assert np.array_equal(res[False], exp), name + " tcgen05"
-    else:
-        _cmp(res[True], exp, name + " simple")
-        _cmp(res[False], exp, name + " tcgen05")
+    for variant, got in res.items():
+        if epilogue == _cabi.EPI_LOGITS:
+            assert np.array_equal(got, exp), f"{name} {variant}"
+        else:
+            _cmp(got, exp, f"{name} {variant}")
 
 
 @pytest.mark.parametrize("shape", [(128, 128, 128), (300, 384, 384), (394, 1152, 192), (256, 384, 1536),
@@ -202,12 +206,14 @@ def test_gemm_acc32(shape):
     _gemm_case(*shape, seed=1, epilogue=_cabi.EPI_ACC32)
 
 
-@pytest.mark.parametrize("shape", [(300, 384, 384), (394, 1152, 192), (256, 1536, 384)])
+@pytest.mark.parametrize("shape", [(300, 384, 384), (394, 1152, 192), (256, 1536, 384), (197, 192, 192),
+                                   (50, 112, 64), (1, 16, 16), (191, 144, 400)])
 def test_gemm_requant(shape):
     _gemm_case(*shape, seed=2, epilogue=_cabi.EPI_REQUANT)
 
 
-@pytest.mark.parametrize("shape", [(300, 384, 384), (394, 192, 768), (256, 384, 1536)])
+@pytest.mark.parametrize("shape", [(300, 384, 384), (394, 192, 768), (256, 384, 1536), (193, 112, 64),
+                                   (577, 272, 128)])
 def test_gemm_residual(shape):
     _gemm_case(*shape, seed=3, epilogue=_cabi.EPI_RESIDUAL)
 

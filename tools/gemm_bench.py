@@ -15,7 +15,8 @@ for name, (m, n, k, epi) in shapes.items():
     s_in = torch.full((n,), 1e-5, device="cuda", dtype=torch.float32)
     ident = torch.randint(-128, 128, (m, n), device="cuda", dtype=torch.int8, generator=g)
     out = torch.empty((m, n), device="cuda", dtype=torch.int8)
-    for zb in (False, True):
+    for layout, zb in ((1, False), (1, True), (0, False), (0, True)):
+        ops.set_gemm_layout(layout)
         kw = dict(bias=bias, mult=mult, s_in=s_in, out=out, z_bound_ok=zb)
         if epi == 2:
             kw.update(identity=ident, mult2=0.7, mult_id=0.4)
@@ -29,4 +30,4 @@ for name, (m, n, k, epi) in shapes.items():
         e1.record()
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) / 20 * 1e3
-        print(f"{name:6s} M={m} N={n} K={k} epi={epi} z_bound_ok={zb}: {us:7.1f} us  {2.0*m*n*k/us/1e6:7.1f} TOP/s", flush=True)
+        print(f"{name:6s} layout={"rows" if layout else "auto"} M={m} N={n} K={k} epi={epi} z_bound_ok={zb}: {us:7.1f} us  {2.0*m*n*k/us/1e6:7.1f} TOP/s", flush=True)
