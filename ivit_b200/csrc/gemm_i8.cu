@@ -11,6 +11,7 @@
 #include <cuda.h>
 #include <cmath>
 #include <cstdio>
+#include <type_traits>
 
 #include "intmath.cuh"
 #include "ivit_b200.h"
@@ -411,21 +412,34 @@ gemm_i8_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 // SHFL.BFLY + two PRMT), after which lane 4k+i holds channels 4k..4k+3 of token 4g+i: 4-byte
 // stores, 32 contiguous bytes per token per warp.  The residual identity comes in the same way.
 // Streamlined REQUANT / RESIDUAL only (no row remap); everything else stays on the kernel above.
+template <int TB_>
 struct ClCfg {
   static constexpr int CB = 128;                                 // channels per tile (UMMA M)
-  static constexpr int TB = 192;                                 // tokens per tile (UMMA N)
+  static constexpr int TB = TB_;                                 // tokens per tile (UMMA N): 192 or 256
   static constexpr int W_BYTES = CB * BK;
   static constexpr int A_BYTES = TB * BK;
   static constexpr int STAGE_BYTES = W_BYTES + A_BYTES;
-  static constexpr int STAGES = 5;
+  static constexpr int STAGES = TB <= 192 ? 5 : 4;
   static constexpr int ACC_STRIDE = 256;
   static constexpr uint32_t TMEM_COLS = 512;
   static constexpr int PART = 64;                                // tokens per epilogue warp
   static constexpr int NPARTS = TB / PART;
-  static constexpr int EPI_WARPS = 4 * NPARTS;
+  static constexpr int EPI_WARPS = 4 * NPARTS;                   // 12 (<= 128 registers) or 16 (<= 96)
   static constexpr int THREADS = 64 + 32 * EPI_WARPS;
   static constexpr int NCH = PART / 16;
   static constexpr size_t SMEM = STAGES * STAGE_BYTES + 256;
+};
+
+// Walks t = blockIdx.x + i * gridDim.x as (channel block, token block) without dividing per tile.
+struct TileWalk {
+  int cb, tb, dq, dr, ncb;
+  __device__ __forceinline__ TileWalk(int t0, int step, int ncb_) : ncb(ncb_) {
+    cb = t0 % ncb_; tb = t0 / ncb_; dq = step / ncb_; dr = step % ncb_;
+  }
+  __device__ __forceinline__ void next() {
+    cb += dr; tb += dq;
+    if (cb >= ncb) { cb -= ncb; ++tb; }
+  }
 };
 
 // 4x4 byte transpose across the 4 lanes of a quad: in: lane i holds bytes T[i][0..3]; out: T[0..3][i]
@@ -441,11 +455,11 @@ __device__ __noinline__ int cl_requant_exact(int z, float s_in, double mult, int
   return static_cast<int>(fmin(fmax(r, static_cast<double>(qmin)), static_cast<double>(qmax)));
 }
 
-template <int MODE, bool CHECKED>
-__global__ void __launch_bounds__(ClCfg::THREADS, 1)
+template <int TB, int MODE, bool CHECKED>
+__global__ void __launch_bounds__(ClCfg<TB>::THREADS, 1)
 gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                   const GemmArgs args) {
-  using Cfg = ClCfg;
+  using Cfg = ClCfg<TB>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
@@ -456,7 +470,8 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle: the compiler then knows the role branches are warp-uniform
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int ncb = (args.N + Cfg::CB - 1) / Cfg::CB;
   const int ntiles = ((args.M + Cfg::TB - 1) / Cfg::TB) * ncb;
   const int kblocks = (args.K + BK - 1) / BK;
@@ -489,8 +504,9 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // the CTAs running together read the same token tile; the weights stay in L2 throughout)
     if (elect_one()) {
       int it = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const int c0 = (t % ncb) * Cfg::CB, t0 = (t / ncb) * Cfg::TB;
+      TileWalk tw(blockIdx.x, gridDim.x, ncb);
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, tw.next()) {
+        const int c0 = tw.cb * Cfg::CB, t0 = tw.tb * Cfg::TB;
         for (int kb = 0; kb < kblocks; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
@@ -541,119 +557,121 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int qc = (lane >> 2) * 4;          //                      and its first channel within the warp's 32
     int pb = 0;
     double pm = 0.0;
-    auto fetch_params = [&](int t) {
-      const int n = (t % ncb) * Cfg::CB + quarter * 32 + lane;
+    auto fetch_params = [&](int cb) {
+      const int n = cb * Cfg::CB + quarter * 32 + lane;
       pb = (e.bias != nullptr && n < args.N) ? __ldg(e.bias + n) : 0;
       pm = n < args.N ? __ldg(e.mult + n) : 0.0;
     };
-    if (blockIdx.x < ntiles) fetch_params(blockIdx.x);
+    TileWalk tw(blockIdx.x, gridDim.x, ncb), tw_next = tw;
+    if (blockIdx.x < ntiles) fetch_params(tw.cb);
+    tw_next.next();
     int8_t* const outp = static_cast<int8_t*>(args.out);
     const double m2 = e.mult2, mi = e.mult_id;
     int i = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++i) {
+    const uint32_t ldo = static_cast<uint32_t>(args.ldo), ldi = static_cast<uint32_t>(e.ld_id);   // offsets < 2^31 (host)
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++i, tw.next(), tw_next.next()) {
       const int a = i & 1;
-      const int c0 = (t % ncb) * Cfg::CB + quarter * 32;       // the warp's first channel
-      const int tok_w = (t / ncb) * Cfg::TB + part * Cfg::PART;  // the warp's first token
+      const int c0 = tw.cb * Cfg::CB + quarter * 32;           // the warp's first channel
+      const int tok_w = tw.tb * Cfg::TB + part * Cfg::PART;    // the warp's first token
       const int n = c0 + lane;
       const double mult = pm;
       const double kb = kMagicInt - static_cast<double>(pb);
       const int brange = pb + (1 << 22);                       // CHECKED: 0 <= acc + brange < 2^23
-      if (t + gridDim.x < ntiles) fetch_params(t + gridDim.x);
+      if (t + gridDim.x < ntiles) fetch_params(tw_next.cb);
       const int nq = c0 + qc;                                  // channels nq..nq+3 after the transpose
       const bool nq_ok = nq < args.N;                          // N % 4 == 0 (host-checked)
 
-      // lane-private row pointers (token tok_w + qi, channel nq), bumped 4 rows per group
+      // lane-private byte offsets of (token tok_w + qi, channel nq) in the output / identity
       const bool all_ok = tok_w + Cfg::PART <= args.M && c0 + 32 <= args.N;   // warp-uniform: no guards
-      const long long ldo4 = 4 * args.ldo, ldi4 = 4 * e.ld_id;
-      int8_t* op = outp + static_cast<long long>(tok_w + qi) * args.ldo + nq;
-      const int8_t* ip = MODE == 2 ? e.identity + static_cast<long long>(tok_w + qi) * e.ld_id + nq : nullptr;
-      auto load_identity = [&](int ch, uint32_t (&w)[4]) {
-        if (all_ok) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) w[g] = __ldg(reinterpret_cast<const uint32_t*>(ip + g * ldi4));
-        } else {
-#pragma unroll
-          for (int g = 0; g < 4; ++g)
-            w[g] = (nq_ok && tok_w + ch * 16 + 4 * g + qi < args.M)
-                       ? __ldg(reinterpret_cast<const uint32_t*>(ip + g * ldi4)) : 0u;
-        }
-        ip += 4 * ldi4;
-      };
-      uint32_t idw[2][4];
-      if (MODE == 2) load_identity(0, idw[0]);
-
-      mbar_wait(&tfull_bar[a], (i >> 1) & 1);
-      tc_fence_after();
+      const uint32_t off_o = static_cast<uint32_t>(tok_w + qi) * ldo + nq;
+      const uint32_t off_i = static_cast<uint32_t>(tok_w + qi) * ldi + nq;
       const uint32_t t_row = tmem_base + a * Cfg::ACC_STRIDE + part * Cfg::PART +
                              (static_cast<uint32_t>(quarter * 32) << 16);
-      uint32_t acc[2][16];
-      tmem_ld16(t_row, acc[0]);
-#pragma unroll
-      for (int ch = 0; ch < Cfg::NCH; ++ch) {
-        tmem_ld_wait();
-        if (ch + 1 < Cfg::NCH) {
-          tmem_ld16(t_row + (ch + 1) * 16, acc[(ch + 1) & 1]);
-          if (MODE == 2) load_identity(ch + 1, idw[(ch + 1) & 1]);
-        } else {
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty_bar[a]);
-        }
-        const uint32_t(&z)[16] = acc[ch & 1];
-        const int tok0 = tok_w + ch * 16;
-        if (tok0 >= args.M) continue;        // warp-uniform (and nothing collective follows for this chunk)
-        int c[16];
-        bool fast = true;
-        if (CHECKED) {
-          uint32_t bits = 0;
-#pragma unroll
-          for (int j = 0; j < 16; ++j) bits |= static_cast<uint32_t>(static_cast<int>(z[j]) + brange);
-          fast = __all_sync(0xffffffffu, (bits & 0xff800000u) == 0u);
-        }
-        if (fast) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const double zd = __hiloint2double(0x43300000, static_cast<int>(z[j] ^ 0x80000000u)) - kb;
-            c[j] = __double2loint(__fma_rn(zd, mult, kMagicRnd));
-          }
-        } else {
-#pragma unroll
-          const float s_in = n < args.N ? __ldg(e.s_in + n) : 1.0f;      // rare: out-of-range chunk
-          const int bias = brange - (1 << 22);
-#pragma unroll
-          for (int j = 0; j < 16; ++j) c[j] = cl_requant_exact(static_cast<int>(z[j]) + bias, s_in, mult, e.qmin, e.qmax);
-        }
-        if (MODE == 2) {
-          // identity words arrive token-major (lane = token, bytes = channels): transpose to
-          // channel-major (lane = channel, bytes = tokens) to meet the accumulators
+      // One tile.  FULL: every token / channel of the warp's 64 x 32 block exists, no guards.
+      // The transposes + stores of chunk k-1 sit in the same basic block as the requantisation
+      // of chunk k, so the scheduler can overlap the FP64 pipe with the ALU / LSU work.
+      auto process = [&](auto full_tag) {
+        constexpr bool FULL = decltype(full_tag)::value;
+        auto load_identity = [&](int ch, uint32_t (&w)[4]) {
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            const uint32_t iw = quad_transpose(idw[ch & 1][g], sel1, sel2);
+            const bool ok = FULL || (nq_ok && tok_w + ch * 16 + 4 * g + qi < args.M);
+            w[g] = ok ? __ldg(reinterpret_cast<const uint32_t*>(e.identity + (off_i + (ch * 16 + 4 * g) * ldi))) : 0u;
+          }
+        };
+        auto store_chunk = [&](int ch, const uint32_t (&packed)[4]) {
 #pragma unroll
-            for (int b = 0; b < 4; ++b) {
-              const int j = 4 * g + b;
-              const int c1 = clampi(c[j], -128, 127);
-              const int id = static_cast<int8_t>(iw >> (8 * b));
-              const double cd = __hiloint2double(0x43300000, c1 ^ 0x80000000) - kMagicInt;
-              const double dd = __hiloint2double(0x43300000, id ^ 0x80000000) - kMagicInt;
-              c[j] = __double2loint(__fma_rn(cd, m2, kMagicRnd)) + __double2loint(__fma_rn(dd, mi, kMagicRnd));
+          for (int g = 0; g < 4; ++g) {
+            const uint32_t w = quad_transpose(packed[g], sel1, sel2);
+            if (FULL || (nq_ok && tok_w + ch * 16 + 4 * g + qi < args.M))
+              *reinterpret_cast<uint32_t*>(outp + (off_o + (ch * 16 + 4 * g) * ldo)) = w;
+          }
+        };
+        uint32_t idw[2][4];
+        if (MODE == 2) load_identity(0, idw[0]);
+        mbar_wait(&tfull_bar[a], (i >> 1) & 1);
+        tc_fence_after();
+        uint32_t acc[2][16];
+        uint32_t packed[4];
+        tmem_ld16(t_row, acc[0]);
+#pragma unroll
+        for (int ch = 0; ch < Cfg::NCH; ++ch) {
+          tmem_ld_wait();
+          if (ch + 1 < Cfg::NCH) {
+            tmem_ld16(t_row + (ch + 1) * 16, acc[(ch + 1) & 1]);
+            if (MODE == 2) load_identity(ch + 1, idw[(ch + 1) & 1]);
+          } else {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[a]);
+          }
+          const uint32_t(&z)[16] = acc[ch & 1];        // rows past M are TMA zero fill: harmless, stores are guarded
+          int c[16];
+          bool fast = true;
+          if (CHECKED) {
+            uint32_t bits = 0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) bits |= static_cast<uint32_t>(static_cast<int>(z[j]) + brange);
+            fast = __all_sync(0xffffffffu, (bits & 0xff800000u) == 0u);
+          }
+          if (fast) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const double zd = __hiloint2double(0x43300000, static_cast<int>(z[j] ^ 0x80000000u)) - kb;
+              c[j] = __double2loint(__fma_rn(zd, mult, kMagicRnd));
+            }
+          } else {
+            const float s_in = n < args.N ? __ldg(e.s_in + n) : 1.0f;      // rare: out-of-range chunk
+            const int bias = brange - (1 << 22);
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              c[j] = cl_requant_exact(static_cast<int>(z[j]) + bias, s_in, mult, e.qmin, e.qmax);
+          }
+          if (ch > 0) store_chunk(ch - 1, packed);
+          if (MODE == 2) {
+            // identity words arrive token-major (lane = token, bytes = channels): transpose to
+            // channel-major (lane = channel, bytes = tokens) to meet the accumulators
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              const uint32_t iw = quad_transpose(idw[ch & 1][g], sel1, sel2);
+#pragma unroll
+              for (int b = 0; b < 4; ++b) {
+                const int j = 4 * g + b;
+                const int c1 = clampi(c[j], -128, 127);
+                const int id = static_cast<int8_t>(iw >> (8 * b));
+                const double cd = __hiloint2double(0x43300000, c1 ^ 0x80000000) - kMagicInt;
+                const double dd = __hiloint2double(0x43300000, id ^ 0x80000000) - kMagicInt;
+                c[j] = __double2loint(__fma_rn(cd, m2, kMagicRnd)) + __double2loint(__fma_rn(dd, mi, kMagicRnd));
+              }
             }
           }
+#pragma unroll
+          for (int g = 0; g < 4; ++g) packed[g] = pack4_sat_s8(c[4 * g], c[4 * g + 1], c[4 * g + 2], c[4 * g + 3]);
         }
-        uint32_t w[4];
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-          w[g] = quad_transpose(pack4_sat_s8(c[4 * g], c[4 * g + 1], c[4 * g + 2], c[4 * g + 3]), sel1, sel2);
-        int8_t* o = op + ch * (4 * ldo4);
-        if (all_ok) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) *reinterpret_cast<uint32_t*>(o + g * ldo4) = w[g];
-        } else {
-#pragma unroll
-          for (int g = 0; g < 4; ++g)
-            if (nq_ok && tok0 + 4 * g + qi < args.M) *reinterpret_cast<uint32_t*>(o + g * ldo4) = w[g];
-        }
-      }
+        store_chunk(Cfg::NCH - 1, packed);
+      };
+      if (all_ok) process(std::true_type{});
+      else process(std::false_type{});
     }
   }
 
@@ -784,9 +802,9 @@ static int launch_ws(const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& ar
   return check_launch("gemm_i8_ws_kernel");
 }
 
-template <int MODE, bool CHECKED>
+template <int TB, int MODE, bool CHECKED>
 static int launch_cl(const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& args, cudaStream_t st) {
-  using Cfg = ClCfg;
+  using Cfg = ClCfg<TB>;
   CUtensorMap tmA, tmW;
   int rc = make_tmap_2d_u8(&tmA, A, args.K, args.M, lda, BK, Cfg::TB, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
@@ -795,14 +813,14 @@ static int launch_cl(const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& ar
   args.stages = Cfg::STAGES;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_i8_cl_kernel<MODE, CHECKED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>(Cfg::SMEM));
+    cudaError_t e = cudaFuncSetAttribute(gemm_i8_cl_kernel<TB, MODE, CHECKED>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(Cfg::SMEM));
     if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
     attr_set = true;
   }
   const int ntiles = ((args.M + Cfg::TB - 1) / Cfg::TB) * ((args.N + Cfg::CB - 1) / Cfg::CB);
   const int grid = ntiles < sm_count() ? ntiles : sm_count();
-  gemm_i8_cl_kernel<MODE, CHECKED><<<grid, Cfg::THREADS, Cfg::SMEM, st>>>(tmA, tmW, args);
+  gemm_i8_cl_kernel<TB, MODE, CHECKED><<<grid, Cfg::THREADS, Cfg::SMEM, st>>>(tmA, tmW, args);
   return check_launch("gemm_i8_cl_kernel");
 }
 
@@ -848,10 +866,12 @@ extern "C" int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M
   const bool checked = epi->z_bound_ok == 0;
   // Hot shapes: channels-on-lanes kernel (per-channel constants in registers).  Needs 4-byte
   // aligned output / identity rows and no row remap.
-  if (mode != 0 && epi->group <= 0 && N % 4 == 0 && ldo % 4 == 0 && (mode == 1 || epi->ld_id % 4 == 0) &&
-      channels_on_lanes_enabled()) {
-    if (mode == 1) return checked ? launch_cl<1, true>(A, lda, W, args, st) : launch_cl<1, false>(A, lda, W, args, st);
-    return checked ? launch_cl<2, true>(A, lda, W, args, st) : launch_cl<2, false>(A, lda, W, args, st);
+  const int64_t span_o = static_cast<int64_t>(M) * ldo + N, span_i = static_cast<int64_t>(M) * epi->ld_id + N;
+  if (mode != 0 && epi->group <= 0 && N % 4 == 0 && ldo % 4 == 0 && span_o < (1ll << 31) &&
+      (mode == 1 || (epi->ld_id % 4 == 0 && span_i < (1ll << 31))) && channels_on_lanes_enabled()) {
+    // REQUANT: 256-token tiles, 16 epilogue warps (fits 96 registers); RESIDUAL: 192 tokens, 12 warps
+    if (mode == 1) return checked ? launch_cl<256, 1, true>(A, lda, W, args, st) : launch_cl<256, 1, false>(A, lda, W, args, st);
+    return checked ? launch_cl<192, 2, true>(A, lda, W, args, st) : launch_cl<192, 2, false>(A, lda, W, args, st);
   }
   // BN = 192 divides every DeiT/ViT width (3C, C, 4C for C = 192/384/768); 128 otherwise
   if (N % 192 == 0 || N > 512) return launch_mode<192>(mode, checked, A, lda, W, args, st);
