@@ -142,10 +142,18 @@ typedef struct {
   /* optional device table [256][256] float32 built by ivit_softmax_table_build from the SAME
    * params: exp term indexed [row-max code + 128][code + 128].  NULL: computed per element. */
   const float* exp_table;
+  /* optional device table [256] float32 from ivit_softmax_table_collapse: the same term indexed
+   * [row-max code - code]; only valid when that call reported the 2-D table collapsible.  Takes
+   * precedence over exp_table (the kernel keeps 16 copies in shared memory instead of gathering). */
+  const float* exp_table_1d;
 } ivit_attention_params_t;
 /* The integer-exp term of IntSoftmax depends only on (code, row-max code) of qact_attn1's int8
  * output: tabulate it once per frozen layer with the kernel's own arithmetic. */
 int ivit_softmax_table_build(const ivit_attention_params_t* p, float* table65536, void* stream);
+/* table256[d] = table65536[127+128][127-d+128]; *collapsible (device int) = 1 iff every valid
+ * entry satisfies table65536[m][c] == table256[m - c] bit for bit, i.e. the exp term depends on
+ * the difference of the two codes only (x/s recovers every int8 code exactly), else 0. */
+int ivit_softmax_table_collapse(const float* table65536, float* table256, int* collapsible, void* stream);
 int ivit_attention_i8(const int8_t* qkv, int8_t* out, int B, int N, int H, int hd,
                       const ivit_attention_params_t* p, void* stream);
 /* Debug taps of the same kernel: softmax codes [B,H,N,N] uint8 (what int_softmax emits). */

@@ -47,6 +47,7 @@ class AttentionParams(C.Structure):
         ("mult_exp16", C.c_double),
         ("s_exp16", C.c_float),
         ("exp_table", C.c_void_p),
+        ("exp_table_1d", C.c_void_p),
     ]
 
 
@@ -78,6 +79,7 @@ _SIGS = {
     "ivit_attention_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.POINTER(AttentionParams), C.c_void_p]),
     "ivit_softmax_table_build": (C.c_int, [C.POINTER(AttentionParams), C.c_void_p, C.c_void_p]),
+    "ivit_softmax_table_collapse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ivit_attention_probs_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                           C.POINTER(AttentionParams), C.c_void_p]),
 }

@@ -30,6 +30,7 @@ struct AttnArgs {
   int8_t* out;
   uint8_t* probs;  // optional debug tap [B,H,N,N]
   const float* exp_table;  // optional [256][256]: softmax_term(c, cmax) tabulated (bit-identical)
+  const float* exp_table_1d;   // optional [256]: the same over cmax - c, when the 2-D table collapses
   ivit_attention_params_t p;
   // derived on the host with float32 arithmetic, mirroring the reference's scalar ops
   float x0, nx0;              // ivit: floor(-1/s), 15*x0 ; ibert: floor(-0.6931/s), 30*x0
@@ -74,12 +75,25 @@ __global__ void softmax_table_kernel(float* __restrict__ table, const AttnArgs a
   table[idx] = (c <= mx) ? softmax_term(c, x_eff(static_cast<float>(mx), a.p.s_attn), a) : 0.f;
 }
 
+// Does table[cmax][c] depend on cmax - c only?  (True whenever fl(fl(c*s)/s) == c for every code,
+// i.e. almost always.)  t1[d] = table[127][127 - d]; *ok is cleared on the first mismatch.
+__global__ void softmax_table_collapse_init(const float* __restrict__ table, float* __restrict__ t1, int* ok) {
+  t1[threadIdx.x] = table[255 * 256 + 255 - threadIdx.x];
+  if (threadIdx.x == 0) *ok = 1;
+}
+__global__ void softmax_table_collapse_check(const float* __restrict__ table, const float* __restrict__ t1, int* ok) {
+  const int m = blockIdx.x, j = threadIdx.x;
+  if (j <= m && __float_as_uint(table[m * 256 + j]) != __float_as_uint(t1[m - j])) *ok = 0;
+}
+
 // 256 threads = two threads per query row: thread A (warps 0-3) owns columns [32i, 32i+16) of
 // every 32-column chunk, thread B (warps 4-7) columns [32i+16, 32i+32).  That split keeps torch's
 // float32 summation order (accumulator e % 32 lives in exactly one thread) while doubling the
-// warps that hide the TMEM / table-gather latency.  TABLE: exp term from the (row max, code)
-// table; TAP: also dump the softmax codes (tests).
-template <bool TABLE, bool TAP>
+// warps that hide the TMEM / table-gather latency.  TABLE 1: exp term gathered from the global
+// (row max, code) table (32 sectors per warp load); TABLE 2: from the 256-entry (row max - code)
+// table replicated 16x in shared memory (copy lane % 16: at most 2 lanes per bank); TABLE 0:
+// computed.  TAP: also dump the softmax codes (tests).
+template <int TABLE, bool TAP>
 __global__ void __launch_bounds__(256, 2)
 attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
@@ -94,6 +108,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   float* sFac = reinterpret_cast<float*>(sMax + 256);          // [128]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sFac + 128);    // qk, v, s, o
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+  float* sT = reinterpret_cast<float*>(bars + 8);              // TABLE 2: [256][16]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int half = warp >> 2;               // 0: thread A, 1: thread B
@@ -138,6 +153,11 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     tc_commit(&bars[2]);
   }
   __syncwarp();
+  if (TABLE == 2) {
+    // replicate while the TMA loads and the S MMA run; visible after the barrier that ends pass 1
+#pragma unroll
+    for (int i = 0; i < 16; ++i) sT[i * 256 + threadIdx.x] = __ldg(a.exp_table_1d + i * 16 + (threadIdx.x >> 4));
+  }
 
   // ---------------------------------------------------------------- softmax
   mbar_wait(&bars[2], 0);
@@ -186,9 +206,14 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   if (warp_active) {
     cmax = max(sMax[r_loc], sMax[128 + r_loc]);
     xmax = x_eff(static_cast<float>(cmax), a.p.s_attn);   // max of un-rounded x/s (monotone in code)
-    if (TABLE) trow = a.exp_table + (cmax + 128) * 256 + 128;
+    if (TABLE == 1) trow = a.exp_table + (cmax + 128) * 256 + 128;
+    if (TABLE == 2) trow = sT + cmax * 16 + (lane & 15);           // entry (cmax - c) of copy lane % 16
   }
-  auto term = [&](int c) -> float { return TABLE ? __ldg(trow + c) : softmax_term(c, xmax, a); };
+  auto term = [&](int c) -> float {
+    if (TABLE == 1) return __ldg(trow + c);
+    if (TABLE == 2) return trow[-16 * c];
+    return softmax_term(c, xmax, a);
+  };
 
   // pass 2: exp terms -> TMEM; float32 row sum in torch's CPU order: accumulator (col % 32) is
   // acc[col % 16] of thread (col % 32) / 16, fed in ascending column order.
@@ -367,7 +392,7 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
   a.B = B; a.N = N; a.H = H;
   a.NKP = (N + 15) / 16 * 16;
   a.KP2 = (N + 31) / 32 * 32;
-  a.out = out; a.probs = probs; a.exp_table = p->exp_table;
+  a.out = out; a.probs = probs; a.exp_table = p->exp_table; a.exp_table_1d = p->exp_table_1d;
   derive_softmax_consts(a, p);
   const int C = H * hd;
   CUtensorMap tq, tk, tv;
@@ -376,24 +401,21 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
   if ((rc = make_tmap_2d_u8(&tq, qkv, cols, rows, cols, HD, 128, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   if ((rc = make_tmap_2d_u8(&tk, qkv, cols, rows, cols, HD, a.NKP, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   if ((rc = make_tmap_2d_u8(&tv, qkv, cols, rows, cols, HD, a.KP2, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
-  const size_t smem = 1024 + 32768 + 8192 + 16384 + 16384 + 16 * 128 * 4 + 256 * 4 + 128 * 4 + 64;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaSuccess;
-    const int sm = static_cast<int>(smem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_i8_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_i8_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_i8_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_i8_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  const int table = a.exp_table_1d != nullptr ? 2 : (a.exp_table != nullptr ? 1 : 0);
+  const bool tap = probs != nullptr;
+  const size_t smem = 1024 + 32768 + 8192 + 16384 + 16384 + 16 * 128 * 4 + 256 * 4 + 128 * 4 + 64 +
+                      (table == 2 ? 256 * 16 * 4 : 0);
+  auto launch = [&](auto kernel) -> int {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
-    attr_set = true;
-  }
-  dim3 grid((N + 127) / 128, B * H);
-  const bool table = a.exp_table != nullptr, tap = probs != nullptr;
-  if (table && !tap) attention_i8_kernel<true, false><<<grid, 256, smem, st>>>(tq, tk, tv, a);
-  else if (table && tap) attention_i8_kernel<true, true><<<grid, 256, smem, st>>>(tq, tk, tv, a);
-  else if (!table && !tap) attention_i8_kernel<false, false><<<grid, 256, smem, st>>>(tq, tk, tv, a);
-  else attention_i8_kernel<false, true><<<grid, 256, smem, st>>>(tq, tk, tv, a);
+    dim3 grid((N + 127) / 128, B * H);
+    kernel<<<grid, 256, smem, st>>>(tq, tk, tv, a);
+    return 0;
+  };
+  if (table == 2) rc = tap ? launch(attention_i8_kernel<2, true>) : launch(attention_i8_kernel<2, false>);
+  else if (table == 1) rc = tap ? launch(attention_i8_kernel<1, true>) : launch(attention_i8_kernel<1, false>);
+  else rc = tap ? launch(attention_i8_kernel<0, true>) : launch(attention_i8_kernel<0, false>);
+  if (rc) return rc;
   return check_launch("attention_i8_kernel");
 }
 
@@ -412,6 +434,14 @@ extern "C" int ivit_softmax_table_build(const ivit_attention_params_t* p, float*
   derive_softmax_consts(a, p);
   softmax_table_kernel<<<256, 256, 0, static_cast<cudaStream_t>(stream)>>>(table65536, a);
   return check_launch("softmax_table_kernel");
+}
+
+extern "C" int ivit_softmax_table_collapse(const float* table65536, float* table256, int* collapsible, void* stream) {
+  if (!table65536 || !table256 || !collapsible) return fail(IVIT_ERR_BAD_ARG, "softmax table collapse: NULL argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  softmax_table_collapse_init<<<1, 256, 0, st>>>(table65536, table256, collapsible);
+  softmax_table_collapse_check<<<256, 256, 0, st>>>(table65536, table256, collapsible);
+  return check_launch("softmax_table_collapse");
 }
 
 extern "C" int ivit_attention_probs_i8(const int8_t* qkv, uint8_t* probs, int B, int N, int H, int hd,

@@ -152,14 +152,24 @@ def set_gemm_layout(layout: int) -> int:
     return _cabi.load().ivit_gemm_set_layout(int(layout))
 
 
-def softmax_table_build(params: AttentionParams, device) -> torch.Tensor:
-    """Tabulate the softmax exp term over (row-max code, code) and attach it to `params`.  The
-    returned tensor owns the memory: keep it alive as long as `params` is used."""
-    table = torch.empty((256, 256), dtype=torch.float32, device=device)
+def softmax_table_build(params: AttentionParams, device, collapse: bool = True) -> torch.Tensor:
+    """Tabulate the softmax exp term over (row-max code, code) and attach it to `params`; when the
+    table depends on the code difference only (checked on the device, bit for bit) also attach the
+    256-entry form the kernel keeps in shared memory.  The returned tensor owns the memory: keep
+    it alive as long as `params` is used.  Freeze-time call (reads one flag back)."""
+    lib = _cabi.load()
+    buf = torch.empty(65536 + 256, dtype=torch.float32, device=device)
     params.exp_table = None
-    check(_cabi.load().ivit_softmax_table_build(C.byref(params), ptr(table), stream()), "ivit_softmax_table_build")
-    params.exp_table = table.data_ptr()
-    return table
+    params.exp_table_1d = None
+    check(lib.ivit_softmax_table_build(C.byref(params), ptr(buf), stream()), "ivit_softmax_table_build")
+    params.exp_table = buf.data_ptr()
+    if collapse:
+        flag = torch.zeros(1, dtype=torch.int32, device=device)
+        check(lib.ivit_softmax_table_collapse(ptr(buf), buf.data_ptr() + 65536 * 4, ptr(flag), stream()),
+              "ivit_softmax_table_collapse")
+        if int(flag.item()) == 1:
+            params.exp_table_1d = buf.data_ptr() + 65536 * 4
+    return buf
 
 
 def attention(qkv: torch.Tensor, B: int, N: int, H: int, hd: int, params: AttentionParams,

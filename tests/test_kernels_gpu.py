@@ -280,17 +280,24 @@ def _attention_case(kind, B, N, H, seed, s_qkv=0.05):
     out, probs = ops.attention(_t(qkv.reshape(B, N, 3 * C), torch.int8), B, N, H, hd, p, want_probs=True)
     _cmp(probs.cpu().numpy(), sm_codes, f"attention probs kind={kind}")
     _cmp(out.cpu().numpy(), out_codes, f"attention out kind={kind}")
-    # same kernel with the exp term tabulated over (row-max code, code)
-    table = ops.softmax_table_build(p, DEV)
-    out, probs = ops.attention(_t(qkv.reshape(B, N, 3 * C), torch.int8), B, N, H, hd, p, want_probs=True)
-    _cmp(probs.cpu().numpy(), sm_codes, f"attention probs (table) kind={kind}")
-    _cmp(out.cpu().numpy(), out_codes, f"attention out (table) kind={kind}")
-    del table
+    # same kernel with the exp term tabulated: 2-D (row-max code, code) table gathered from global
+    # memory, then the collapsed (row-max - code) table replicated in shared memory
+    for collapse in (False, True):
+        table = ops.softmax_table_build(p, DEV, collapse=collapse)
+        assert p.exp_table and (collapse or not p.exp_table_1d)
+        tag = "1-D table" if p.exp_table_1d else "2-D table"
+        out, probs = ops.attention(_t(qkv.reshape(B, N, 3 * C), torch.int8), B, N, H, hd, p, want_probs=True)
+        _cmp(probs.cpu().numpy(), sm_codes, f"attention probs ({tag}) kind={kind}")
+        _cmp(out.cpu().numpy(), out_codes, f"attention out ({tag}) kind={kind}")
+        out = ops.attention(_t(qkv.reshape(B, N, 3 * C), torch.int8), B, N, H, hd, p)
+        _cmp(out.cpu().numpy(), out_codes, f"attention out, no tap ({tag}) kind={kind}")
+        del table
+    return bool(p.exp_table_1d)
 
 
 @pytest.mark.parametrize("N", [197, 64, 49, 256, 130])
 def test_attention_ivit(N):
-    _attention_case(0, 2, N, 3, seed=N)
+    assert _attention_case(0, 2, N, 3, seed=N), "the (row max, code) table of this scale should collapse"
 
 
 def test_attention_ivit_peaked():
