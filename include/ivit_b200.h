@@ -49,6 +49,9 @@ int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float inv_scale, i
 int ivit_layernorm_requant_i8(int kind, const int8_t* x, int64_t ldx, int8_t* out, int rows, int C, float s_in,
                               const float* bias_int, const float* sf, const double* mult, int qmin, int qmax,
                               float shift, int use_int_sqrt, void* stream);
+/* Two kernels for kind 0: packed lanes (C % 128 == 0, default) and strided lanes (any supported C).
+ * variant 0 = choose per call, 1 = always the second.  Returns the previous setting.  Process-wide. */
+int ivit_layernorm_set_variant(int variant);
 
 /* ---- GELU (+ mlp.qact1) as a per-layer table --------------------------------------------
  * kind 0: ivit_modules.py:89-126 (ShiftGELU, n = 23, output_bit), kind 1:

@@ -237,6 +237,178 @@ layernorm_ivit_requant_kernel(const int8_t* __restrict__ x, long long ldx, int8_
   }
 }
 
+// Same computation for C % 128 == 0 with a packed lane mapping: a lane owns the four consecutive
+// channels 128 j + 4 lane + {0..3} of every 128-channel group, so a row comes in as NJ 32-bit
+// shared-memory loads per lane and leaves as NJ coalesced 4-byte global stores per lane (no output
+// staging), codes are unpacked with one sign-replicating PRMT and packed with cvt.pack.sat.
+// The near-tie test is two FMAs: rint(ra (1 -+ 2^-18) + 1.5*2^23) must agree (the exact value lies
+// between them: float32(mult), z vs v and the product rounding are each < 2^-21.5 relative);
+// where they differ -- ~1e-3 of the elements -- the exact replay runs for that element.
+__device__ __forceinline__ int sext_byte(uint32_t w, int k) {
+  uint32_t d;
+  const uint32_t sel = 0x8880u + 0x1111u * static_cast<uint32_t>(k);
+  asm("prmt.b32 %0, %1, 0, %2;" : "=r"(d) : "r"(w), "r"(sel));
+  return static_cast<int>(d);
+}
+__device__ __forceinline__ uint32_t pack_sat_s8_ln(int a, int b, uint32_t hi16) {
+  uint32_t d;
+  asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(hi16));
+  return d;
+}
+
+template <int NJ, int R, int MINB>
+__global__ void __launch_bounds__(256, MINB)
+layernorm_ivit_requant4_kernel(const int8_t* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows,
+                               float s_in, const float* __restrict__ bias_int, const float* __restrict__ sf,
+                               const double* __restrict__ mult, int qmin, int qmax) {
+  constexpr int NPL = NJ * 4;
+  constexpr int C = NJ * 128;
+  constexpr int VPR = C / 16;
+  __shared__ __align__(16) int8_t stage[8][2][R][C];     // input rows, cp.async double buffer
+  __shared__ float lut_f[256];
+  __shared__ int lut_i[256];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  {
+    const float xe = x_eff(static_cast<float>(static_cast<int>(threadIdx.x) - 128), s_in);   // :36
+    lut_f[threadIdx.x] = xe;
+    lut_i[threadIdx.x] = static_cast<int>(xe);                                               // :38 trunc
+  }
+  const int* lut_i0 = lut_i + 128;                  // indexed by the signed code
+  float bia[NPL], mf[NPL];
+#pragma unroll
+  for (int j = 0; j < NJ; ++j)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int c = 128 * j + 4 * lane + b;
+      bia[4 * j + b] = __ldg(bias_int + c);
+      mf[4 * j + b] = static_cast<float>(__ldg(mult + c));
+    }
+  const bool fast_ok = qmin == -128 && qmax == 127;       // cvt.pack.sat clamps to exactly this range
+  const int ngroups = (rows + R - 1) / R;
+  auto prefetch = [&](int g, int buf) {
+    if (g < ngroups) {
+      const int row0 = g * R, nr = min(R, rows - row0);
+      for (int v = lane; v < R * VPR; v += 32) {
+        const int r = v / VPR, vv = v - r * VPR;
+        if (r < nr) {
+          const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(&stage[warp][buf][r][vv * 16]));
+          const int8_t* src = x + static_cast<long long>(row0 + r) * ldx + vv * 16;
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  prefetch(blockIdx.x * 8 + warp, 0);
+  __syncthreads();
+  int buf = 0;
+  for (int g = blockIdx.x * 8 + warp; g < ngroups; g += gridDim.x * 8, buf ^= 1) {
+    const int row0 = g * R;
+    const int nr = min(R, rows - row0);
+    prefetch(g + gridDim.x * 8, buf ^ 1);
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncwarp();
+    int y[R][NPL];
+    int S[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      S[r] = 0;
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        const uint32_t w = *reinterpret_cast<const uint32_t*>(&stage[warp][buf][r][128 * j + 4 * lane]);
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          y[r][4 * j + b] = sext_byte(w, b);
+          S[r] += y[r][4 * j + b];
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+      for (int r = 0; r < R; ++r) S[r] += __shfl_xor_sync(0xffffffffu, S[r], o);
+    int mean[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      // :37 mean = round(mean(x_int)); an exact tie S/C = k + 1/2 replays torch's float32 summation
+      // order over the un-rounded inputs (channel 32 i + lane, read back from the staged row)
+      float sum_f = static_cast<float>(S[r]);
+      if (((S[r] % C) + C) % C * 2 == C) {                      // warp-uniform, rare
+        float xe[NPL];
+#pragma unroll
+        for (int i = 0; i < NPL; ++i) xe[i] = lut_f[static_cast<int>(stage[warp][buf][r][32 * i + lane]) + 128];
+        sum_f = ln_torch_row_sum<NPL>(xe, lane);
+      }
+      mean[r] = static_cast<int>(rintf(__fdiv_rn(sum_f, static_cast<float>(C))));
+    }
+    int var[R];     // :41-42: |y| <= 258, so neither the int32 squares nor their sum over C <= 1024 channels wrap
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      int vr = 0;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        y[r][i] = lut_i0[y[r][i]] - mean[r];                        // :38-40 (trunc, int32)
+        vr += y[r][i] * y[r][i];
+      }
+      var[r] = vr;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+      for (int r = 0; r < R; ++r) var[r] += __shfl_xor_sync(0xffffffffu, var[r], o);
+    float factor[R];
+    {
+      int mv = var[0];
+#pragma unroll
+      for (int r = 1; r < R; ++r) mv = (lane == r) ? var[r] : mv;
+      const float var_f = static_cast<float>(mv);
+      float k = 65536.f;
+#pragma unroll
+      for (int it = 0; it < 10; ++it) k = floorf(__fmul_rn(__fadd_rn(k, floorf(__fdiv_rn(var_f, k))), 0.5f));   // :45-49
+      const float fct = floorf(__fdiv_rn(2147483648.f, k));        // :51 (2^31-1 -> 2^31 in float32)
+#pragma unroll
+      for (int r = 0; r < R; ++r) factor[r] = __shfl_sync(0xffffffffu, fct, r);
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      uint32_t slow = 0;
+      int code[NPL];
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        const float yf = __fsub_rn(__int_as_float(0x4B400000 + y[r][i]), 12582912.f);
+        float v = floorf(__fmul_rn(__fmul_rn(yf, factor[r]), 0.5f));                            // :52
+        v = __fadd_rn(v, bia[i]);                                                               // :61
+        const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -200.f), 200.f);   // beyond +-130 both paths clamp
+        const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);   // 1 - 2^-18
+        const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);   // 1 + 2^-18
+        slow = slow * 2u + ((__float_as_uint(lo) ^ __float_as_uint(hi)) & 1u);   // consecutive integers differ in bit 0
+        code[i] = __float_as_int(lo) - 0x4B400000;
+      }
+      if (!fast_ok) slow = 0xffffffffu;
+      if (slow != 0) {
+#pragma unroll
+        for (int i = 0; i < NPL; ++i) {
+          if ((slow >> (NPL - 1 - i)) & 1u) {
+            const int c = 128 * (i >> 2) + 4 * lane + (i & 3);
+            const float yf = static_cast<float>(y[r][i]);
+            float v = floorf(__fmul_rn(__fmul_rn(yf, factor[r]), 0.5f));                        // :52
+            v = __fadd_rn(v, bia[i]);                                                           // :61
+            code[i] = ln_requant_exact(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax);
+          }
+        }
+      }
+      if (r < nr) {
+        int8_t* orow = out + static_cast<long long>(row0 + r) * C + 4 * lane;
+#pragma unroll
+        for (int j = 0; j < NJ; ++j)
+          *reinterpret_cast<uint32_t*>(orow + 128 * j) =
+              pack_sat_s8_ln(code[4 * j + 1], code[4 * j], pack_sat_s8_ln(code[4 * j + 3], code[4 * j + 2], 0u));
+      }
+    }
+    __syncwarp();                 // the staged rows are overwritten by the prefetch two iterations on
+  }
+}
+
 // ibert_modules.py:112-158 followed by QuantAct.  shift_pow = 2^shift, inv_shift_pow = 2^-shift.
 template <int NPL>
 __global__ void __launch_bounds__(256)
@@ -478,6 +650,14 @@ extern "C" int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float i
   return check_launch("quantize_patches_kernel");
 }
 
+// 0: packed-lane kernel where C % 128 == 0 (default); 1: strided-lane kernel always (A/B, tests)
+static int g_ln_variant = 0;
+extern "C" int ivit_layernorm_set_variant(int variant) {
+  const int prev = g_ln_variant;
+  g_ln_variant = variant;
+  return prev;
+}
+
 template <int NPL>
 static int launch_ln(int kind, const int8_t* x, long long ldx, int8_t* out, int rows, float s_in, const float* bias_int,
                      const float* sf, const double* mult, int qmin, int qmax, float shift, int use_int_sqrt,
@@ -487,6 +667,13 @@ static int launch_ln(int kind, const int8_t* x, long long ldx, int8_t* out, int 
     constexpr int R = NPL <= 12 ? 4 : 2;
     const int groups = (rows + R - 1) / R;
     const int pgrid = min((groups + 7) / 8, 148 * 4);     // persistent: a few CTAs per SM
+    if constexpr (NPL % 4 == 0) {
+      if (g_ln_variant == 0) {
+        layernorm_ivit_requant4_kernel<NPL / 4, R, 2><<<pgrid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult,
+                                                                            qmin, qmax);
+        return check_launch("layernorm_requant4_kernel");
+      }
+    }
     layernorm_ivit_requant_kernel<NPL, R, 2><<<pgrid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin,
                                                                    qmax);
   } else {

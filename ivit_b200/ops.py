@@ -147,6 +147,11 @@ def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=Non
     return out
 
 
+def set_layernorm_variant(variant: int) -> int:
+    """0: packed-lane I-ViT LayerNorm kernel where C % 128 == 0; 1: strided-lane kernel always."""
+    return _cabi.load().ivit_layernorm_set_variant(int(variant))
+
+
 def set_gemm_layout(layout: int) -> int:
     """0: ivit_gemm_i8 picks its kernel per call; 1: tokens-on-lanes kernel only.  Returns the old value."""
     return _cabi.load().ivit_gemm_set_layout(int(layout))

@@ -73,13 +73,18 @@ def _ln_case(kind, C, rows, seed, s_in=0.0371, ties=True, neg=False, use_int_sqr
     p = hm.layernorm_params(w, b, C)
     assert np.array_equal(p["sf"], sf)
     mult = hm.dyadic_mult(p["sf"], s_out)
-    got = ops.layernorm_requant(kind, _t(q[0], torch.int8), float(s_in), _t(p["bias_int"], torch.float32),
-                                _t(p["sf"], torch.float32), _t(mult, torch.float64), -128, 127,
-                                use_int_sqrt=use_int_sqrt).cpu().numpy()
-    _cmp(got, codes[0], f"layernorm kind={kind} C={C}")
+    for variant in ((0, 1) if kind == 0 else (0,)):      # packed-lane / strided-lane I-ViT kernels
+        prev = ops.set_layernorm_variant(variant)
+        try:
+            got = ops.layernorm_requant(kind, _t(q[0], torch.int8), float(s_in), _t(p["bias_int"], torch.float32),
+                                        _t(p["sf"], torch.float32), _t(mult, torch.float64), -128, 127,
+                                        use_int_sqrt=use_int_sqrt).cpu().numpy()
+        finally:
+            ops.set_layernorm_variant(prev)
+        _cmp(got, codes[0], f"layernorm kind={kind} C={C} variant={variant}")
 
 
-@pytest.mark.parametrize("C", [192, 384, 768])
+@pytest.mark.parametrize("C", [128, 192, 384, 768, 1024])
 def test_layernorm_ivit(C):
     _ln_case(0, C, 301, seed=C)
     _ln_case(0, C, 64, seed=C + 1, s_in=0.0123, neg=True)
