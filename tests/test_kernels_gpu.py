@@ -242,7 +242,7 @@ def test_gemm_logits():
     _gemm_case(130, 1000, 384, seed=5, epilogue=_cabi.EPI_LOGITS)
 
 
-def _attention_case(kind, B, N, H, seed, s_qkv=0.05):
+def _attention_case(kind, B, N, H, seed, s_qkv=0.05, a_max=None):
     rng = np.random.default_rng(seed)
     hd = 64
     C = H * hd
@@ -255,7 +255,7 @@ def _attention_case(kind, B, N, H, seed, s_qkv=0.05):
     sc = f32(hd ** -0.5)
     attn = (attn * sc).astype(f32)
     s = (s * sc).astype(f32)
-    a_max = np.array([np.abs(attn).max() * 0.5], dtype=f32)
+    a_max = np.array([np.abs(attn).max() * 0.5 if a_max is None else a_max], dtype=f32)
     attn_q, s_a, attn_codes = O.quant_act(attn, 8, -a_max, a_max, pre_scale=s)
     p = _cabi.AttentionParams()
     p.kind, p.output_bit = kind, 8
@@ -302,7 +302,14 @@ def _attention_case(kind, B, N, H, seed, s_qkv=0.05):
 
 @pytest.mark.parametrize("N", [197, 64, 49, 256, 130])
 def test_attention_ivit(N):
-    assert _attention_case(0, 2, N, 3, seed=N), "the (row max, code) table of this scale should collapse"
+    _attention_case(0, 2, N, 3, seed=N)
+
+
+@pytest.mark.parametrize("N", [197, 100])
+def test_attention_ivit_collapsed_table(N):
+    """s_attn = 2^-4: x/s recovers every code exactly, the (row max, code) table depends on the
+    difference only and the kernel takes its shared-memory table path (most scales do not)."""
+    assert _attention_case(0, 2, N, 3, seed=N + 3, s_qkv=0.03, a_max=127.0 / 16.0)
 
 
 def test_attention_ivit_peaked():
