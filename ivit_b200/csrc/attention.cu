@@ -298,7 +298,9 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
           // :175 / :315 (terms past column N were stored as 0)
-          const uint32_t pc = static_cast<uint32_t>(__float2int_rd(__fmul_rn(__uint_as_float(v[j]), fs))) & 0xffu;
+          // floor of a value in [0, 2^22) through the 2^23 magic constant (round toward zero) instead of
+          // F2I: conversions run on the quarter-rate XU pipe
+          const uint32_t pc = __float_as_uint(__fadd_rz(__fmul_rn(__uint_as_float(v[j]), fs), 8388608.f)) & 0xffu;
           w[j >> 2] |= pc << (8 * (j & 3));
         }
         if (TAP && a.probs != nullptr && row < N) {
