@@ -1,8 +1,8 @@
 """Public inference call: host images in, host logits out.
 
 ``InferenceSession`` owns one ``FrozenVitPlan`` on one GPU and what a serving loop needs around
-it: CUDA-graph replays of the launch sequence, a copy stream, and two pinned-memory-fed staging
-slots so that the host->device copy of chunk i+1 overlaps the forward of chunk i.  This is the
+it: CUDA-graph replays of the launch sequence, a copy stream, and rotating staging slots so that
+the host->device copy of the next chunk (or the next call) overlaps the forward in flight.  This is the
 call ``bench.py`` times as ``e2e`` and the one ``scripts/inference.py:248`` (``model(imgs)`` per
 batch) maps to.  No CPU path: construction fails without a CUDA device and the in-tree library.
 """
@@ -15,33 +15,45 @@ from .synthetic import VitConfig
 
 
 class InferenceSession:
-    def __init__(self, cfg: VitConfig, state: dict, batch: int, device="cuda", chunks: int = 1):
+    def __init__(self, cfg: VitConfig, state: dict, batch: int, device="cuda", chunks: int = 1, slots: int = 2):
+        """batch images per call, processed as `chunks` equal forwards; `slots` staging slots (each a
+        captured graph with its own input buffer) rotate across chunks AND calls, so with slots >= 2
+        the host->device copy of the next chunk / next call overlaps the forward in flight."""
         if batch % chunks != 0:
             raise ValueError("batch must be divisible by chunks")
+        if slots < 1:
+            raise ValueError("slots must be >= 1")
         self.plan = FrozenVitPlan(cfg, state, device)
         self.device = self.plan.device
         self.batch, self.chunks, self.cb = batch, chunks, batch // chunks
         self.compute = torch.cuda.Stream(device=self.device)
         self.copy = torch.cuda.Stream(device=self.device)
         with torch.cuda.device(self.device):
-            self.slots = [self.plan.capture(self.cb, slot=s) for s in range(2 if chunks > 1 else 1)]
+            self.slots = [self.plan.capture(self.cb, slot=s) for s in range(slots)]
             self.ready = [torch.cuda.Event() for _ in self.slots]
             self.consumed = [torch.cuda.Event() for _ in self.slots]
-        self.out_host = torch.empty((batch, cfg.num_classes), dtype=torch.float32).pin_memory()
+        # two result buffers: the logits of call k stay valid while call k+1 is in flight
+        self.out_hosts = [torch.empty((batch, cfg.num_classes), dtype=torch.float32).pin_memory() for _ in range(2)]
         self.h2d_bytes = batch * cfg.in_chans * cfg.img_size * cfg.img_size * 4
         self.d2h_bytes = batch * cfg.num_classes * 4
-        self.launches_per_infer = sum(self.slots[c % len(self.slots)].launches for c in range(chunks))
+        self.launches_per_infer = chunks * self.slots[0].launches
+        self._seq = 0          # chunks enqueued so far (slot rotation)
+        self._calls = 0
 
     def infer_async(self, images: torch.Tensor) -> torch.Tensor:
         """Enqueue one batch.  images: float32 [batch,3,H,W] in HOST memory (pinned for an
-        asynchronous copy).  Returns the pinned host logits buffer; valid after ``synchronize()``."""
+        asynchronous copy; the caller keeps it unchanged until the copy has run).  Returns the pinned
+        host logits buffer of this call; valid after ``synchronize()``, reused two calls later."""
         if images.is_cuda:
             raise ValueError("infer() takes host images; use FrozenVitPlan.forward for device tensors")
         if images.shape[0] != self.batch:
             raise ValueError(f"session was built for batch {self.batch}")
+        out_host = self.out_hosts[self._calls % 2]
+        self._calls += 1
         ns = len(self.slots)
         for c in range(self.chunks):
-            s = c % ns
+            s = self._seq % ns
+            self._seq += 1
             g = self.slots[s]
             lo, hi = c * self.cb, (c + 1) * self.cb
             with torch.cuda.stream(self.copy):
@@ -52,8 +64,8 @@ class InferenceSession:
                 self.compute.wait_event(self.ready[s])
                 g.replay()
                 self.consumed[s].record(self.compute)
-                self.out_host[lo:hi].copy_(g.static_out, non_blocking=True)
-        return self.out_host
+                out_host[lo:hi].copy_(g.static_out, non_blocking=True)
+        return out_host
 
     def synchronize(self):
         self.compute.synchronize()

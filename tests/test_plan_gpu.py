@@ -93,3 +93,20 @@ def test_base_models_vs_reference_logits(case):
     ref = fix["logits"]
     assert np.array_equal(logits.argmax(1), ref.argmax(1))
     assert np.allclose(logits, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
+@pytest.mark.parametrize("chunks,slots", [(1, 2), (2, 2), (2, 3), (1, 1)])
+def test_session_slots_rotate_across_calls(chunks, slots):
+    """Back-to-back infer_async calls (no synchronisation in between) use different staging slots and
+    result buffers: every call must return the logits of ITS images."""
+    from ivit_b200.api import InferenceSession
+    cfg, state, _ = load_case("toy_ivit")
+    sess = InferenceSession(cfg, state, batch=4, chunks=chunks, slots=slots)
+    xs = [synth_images(4, cfg, seed=20 + i).pin_memory() for i in range(2)]
+    refs = [sess.plan.forward(x.cuda()).float().cpu() for x in xs]
+    assert not torch.equal(refs[0], refs[1])
+    for _ in range(2):
+        outs = [sess.infer_async(x) for x in xs]
+        sess.synchronize()
+        for o, r in zip(outs, refs):
+            assert torch.equal(o, r)
