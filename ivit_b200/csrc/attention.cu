@@ -86,6 +86,24 @@ __global__ void softmax_table_collapse_check(const float* __restrict__ table, co
   if (j <= m && __float_as_uint(table[m * 256 + j]) != __float_as_uint(t1[m - j])) *ok = 0;
 }
 
+// for ci in [0, n): body(ci, v) over this thread's 16 TMEM columns of 32-column chunk ci, with the
+// tcgen05.ld of chunk ci + 1 in flight while chunk ci is processed (two register buffers).
+template <class F>
+__device__ __forceinline__ void chunk_pipeline(uint32_t t_row, int n, F&& body) {
+  uint32_t v0[16], v1[16];
+  if (n > 0) tmem_ld16(t_row, v0);
+  for (int ci = 0; ci < n; ci += 2) {
+    tmem_ld_wait();
+    if (ci + 1 < n) tmem_ld16(t_row + (ci + 1) * 32, v1);
+    body(ci, v0);
+    if (ci + 1 < n) {
+      tmem_ld_wait();
+      if (ci + 2 < n) tmem_ld16(t_row + (ci + 2) * 32, v0);
+      body(ci + 1, v1);
+    }
+  }
+}
+
 // 256 threads = two threads per query row: thread A (warps 0-3) owns columns [32i, 32i+16) of
 // every 32-column chunk, thread B (warps 4-7) columns [32i+16, 32i+32).  That split keeps torch's
 // float32 summation order (accumulator e % 32 lives in exactly one thread) while doubling the
@@ -174,10 +192,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   // pass 1: qact_attn1 requant, row max; codes go back to TMEM
   int cmax = -(1 << 30);
   if (warp_active) {
-    for (int ci = 0; ci < nchunks; ++ci) {
-      uint32_t v[16];
-      tmem_ld16(t_row + ci * 32, v);
-      tmem_ld_wait();
+    chunk_pipeline(t_row, nchunks, [&](int ci, uint32_t (&v)[16]) {
       if (ci < nfull) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
@@ -194,7 +209,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
       }
       tmem_st16(t_row + ci * 32, v);
-    }
+    });
     tmem_st_wait();
     sMax[half * 128 + r_loc] = cmax;
   }
@@ -222,10 +237,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
   for (int j = 0; j < 16; ++j) acc[j] = 0.f;
   if (warp_active) {
-    for (int ci = 0; ci < size_ilp; ++ci) {
-      uint32_t v[16];
-      tmem_ld16(t_row + ci * 32, v);
-      tmem_ld_wait();
+    chunk_pipeline(t_row, size_ilp, [&](int ci, uint32_t (&v)[16]) {
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
         const float e = term(static_cast<int>(v[j]));
@@ -233,7 +245,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         v[j] = __float_as_uint(e);
       }
       tmem_st16(t_row + ci * 32, v);
-    }
+    });
     if (nchunks > size_ilp) {          // partial chunk: exp terms only; its sum is thread A's job below
       uint32_t v[16];
       tmem_ld16(t_row + size_ilp * 32, v);
@@ -289,31 +301,30 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   // pass 3: probabilities -> u8 operand tile in shared memory (K-major, SWIZZLE_128B)
   if (warp_active) {
     const float fs = sFac[r_loc];
-    for (int ci = 0; ci < pchunks; ++ci) {
-      uint32_t w[4] = {0, 0, 0, 0};
-      if (ci < nchunks) {
-        uint32_t v[16];
-        tmem_ld16(t_row + ci * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          // :175 / :315 (terms past column N were stored as 0)
-          // floor of a value in [0, 2^22) through the 2^23 magic constant (round toward zero) instead of
-          // F2I: conversions run on the quarter-rate XU pipe
-          const uint32_t pc = __float_as_uint(__fadd_rz(__fmul_rn(__uint_as_float(v[j]), fs), 8388608.f)) & 0xffu;
-          w[j >> 2] |= pc << (8 * (j & 3));
-        }
-        if (TAP && a.probs != nullptr && row < N) {
-          uint8_t* pr = a.probs + ((static_cast<long long>(blockIdx.y) * N + row) * N) + ci * 32 + cbase;
-          for (int j = 0; j < 16 && ci * 32 + cbase + j < N; ++j) pr[j] = static_cast<uint8_t>(w[j >> 2] >> (8 * (j & 3)));
-        }
-      }
+    auto store_p = [&](int ci, const uint32_t (&w)[4]) {
       // 16 bytes = one 16-byte unit of this row's 128-byte swizzle line
       const int col = ci * 32 + cbase;
       uint8_t* base = sP + (col >> 7) * 16384 + (r_loc >> 3) * 1024 + (r_loc & 7) * 128;
       const int u0 = (col & 127) >> 4;
       *reinterpret_cast<int4*>(base + ((u0 ^ (r_loc & 7)) << 4)) = make_int4(w[0], w[1], w[2], w[3]);
-    }
+    };
+    chunk_pipeline(t_row, nchunks, [&](int ci, uint32_t (&v)[16]) {
+      uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        // :175 / :315 (terms past column N were stored as 0).  floor of a value in [0, 2^22) through
+        // the 2^23 magic constant (round toward zero) instead of F2I (quarter-rate XU pipe)
+        const uint32_t pc = __float_as_uint(__fadd_rz(__fmul_rn(__uint_as_float(v[j]), fs), 8388608.f)) & 0xffu;
+        w[j >> 2] |= pc << (8 * (j & 3));
+      }
+      if (TAP && a.probs != nullptr && row < N) {
+        uint8_t* pr = a.probs + ((static_cast<long long>(blockIdx.y) * N + row) * N) + ci * 32 + cbase;
+        for (int j = 0; j < 16 && ci * 32 + cbase + j < N; ++j) pr[j] = static_cast<uint8_t>(w[j >> 2] >> (8 * (j & 3)));
+      }
+      store_p(ci, w);
+    });
+    const uint32_t zero[4] = {0, 0, 0, 0};
+    for (int ci = nchunks; ci < pchunks; ++ci) store_p(ci, zero);     // K padding of the P V product
   }
   fence_proxy_async_smem();     // generic-proxy smem writes -> visible to tcgen05.mma
   tc_fence_before();
