@@ -531,12 +531,19 @@ gelu_lut_apply_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, co
                max(static_cast<int8_t>(m >> 16), static_cast<int8_t>(m >> 24)));
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  const int8_t* trow = lut + (mx + 128) * 256 + 128;
+  // the row's 256-byte table line, staged per warp: byte gathers from shared memory (<= 2 lanes per
+  // bank on average) instead of 8-sector global gathers
+  __shared__ __align__(8) uint8_t srow[8][256];
+  *reinterpret_cast<uint2*>(&srow[warp][8 * lane]) =
+      __ldg(reinterpret_cast<const uint2*>(lut + (mx + 128) * 256) + lane);
+  __syncwarp();
+  const uint8_t* trow = srow[warp];            // indexed by the code as an unsigned byte ^ 0x80 (= code + 128)
   auto look4 = [&](uint32_t w) -> uint32_t {
-    const uint32_t b0 = static_cast<uint8_t>(__ldg(trow + static_cast<int8_t>(w)));
-    const uint32_t b1 = static_cast<uint8_t>(__ldg(trow + static_cast<int8_t>(w >> 8)));
-    const uint32_t b2 = static_cast<uint8_t>(__ldg(trow + static_cast<int8_t>(w >> 16)));
-    const uint32_t b3 = static_cast<uint8_t>(__ldg(trow + static_cast<int8_t>(w >> 24)));
+    w ^= 0x80808080u;
+    const uint32_t b0 = trow[w & 0xffu];
+    const uint32_t b1 = trow[(w >> 8) & 0xffu];
+    const uint32_t b2 = trow[(w >> 16) & 0xffu];
+    const uint32_t b3 = trow[w >> 24];
     return b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
   };
 #pragma unroll
