@@ -186,13 +186,16 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const int nfull = N / 32;                             // chunks with all 32 columns valid
   const int nchunks = (N + 31) / 32;
   const int pchunks = a.KP2 / 32;
+  // chunks in which THIS thread's 16-column segment holds a valid column (warp-uniform: a warp is all
+  // A or all B threads): for N = 197 thread B skips the 7th chunk entirely
+  const int my_chunks = (N - half * 16 + 31) / 32;
   const bool warp_active = mt * 128 + quarter * 32 < N; // warp-uniform: rows past the last token do no work
   const int cbase = half * 16;                          // this thread's first column inside a chunk
 
   // pass 1: qact_attn1 requant, row max; codes go back to TMEM
   int cmax = -(1 << 30);
   if (warp_active) {
-    chunk_pipeline(t_row, nchunks, [&](int ci, uint32_t (&v)[16]) {
+    chunk_pipeline(t_row, my_chunks, [&](int ci, uint32_t (&v)[16]) {
       if (ci < nfull) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
@@ -246,7 +249,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
       tmem_st16(t_row + ci * 32, v);
     });
-    if (nchunks > size_ilp) {          // partial chunk: exp terms only; its sum is thread A's job below
+    if (my_chunks > size_ilp) {        // partial chunk: exp terms only; its sum is thread A's job below
       uint32_t v[16];
       tmem_ld16(t_row + size_ilp * 32, v);
       tmem_ld_wait();
@@ -308,7 +311,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const int u0 = (col & 127) >> 4;
       *reinterpret_cast<int4*>(base + ((u0 ^ (r_loc & 7)) << 4)) = make_int4(w[0], w[1], w[2], w[3]);
     };
-    chunk_pipeline(t_row, nchunks, [&](int ci, uint32_t (&v)[16]) {
+    chunk_pipeline(t_row, my_chunks, [&](int ci, uint32_t (&v)[16]) {
       uint32_t w[4] = {0, 0, 0, 0};
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
@@ -324,7 +327,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       store_p(ci, w);
     });
     const uint32_t zero[4] = {0, 0, 0, 0};
-    for (int ci = nchunks; ci < pchunks; ++ci) store_p(ci, zero);     // K padding of the P V product
+    for (int ci = my_chunks; ci < pchunks; ++ci) store_p(ci, zero);   // K padding of the P V product
   }
   fence_proxy_async_smem();     // generic-proxy smem writes -> visible to tcgen05.mma
   tc_fence_before();
