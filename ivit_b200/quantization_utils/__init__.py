@@ -4,6 +4,7 @@ import torch
 import torch.nn.functional as F
 
 from .carrier import QTensor
+from .floatmods import FloatGELU, FloatLayerNorm, FloatSoftmax
 from .iostats import (attach_io_stat_hooks, clear_io_stats, disable_io_stats, enable_io_stats, get_io_stats_df,
                       save_io_stats_df)
 from .modules import (IBERTIntGELU, IBERTIntLayerNorm, IBERTIntSoftmax, IVITIntGELU, IVITIntLayerNorm,
@@ -23,4 +24,5 @@ def softmax(x, dim: int, onnx_trace: bool = False):
 __all__ = ["QuantLinear", "QuantAct", "QuantConv2d", "QuantMatMul", "attach_io_stat_hooks", "save_io_stats_df",
            "enable_io_stats", "disable_io_stats", "clear_io_stats", "softmax", "IVITIntGELU", "IVITIntSoftmax",
            "IVITIntLayerNorm", "IBERTIntGELU", "IBERTIntSoftmax", "IBERTIntLayerNorm", "get_gelu", "get_softmax",
-           "get_layernorm", "IntLayerNorm", "IntSoftmax", "IntGELU", "QTensor"]
+           "get_layernorm", "IntLayerNorm", "IntSoftmax", "IntGELU", "QTensor", "FloatGELU", "FloatSoftmax",
+           "FloatLayerNorm"]

@@ -162,8 +162,28 @@ class QuantAct(_FrozenCache, nn.Module):
             # quant_modules.py:374-377: no predecessor scale -> plain symmetric quantiser (deferred:
             # a following QuantConv2d fuses it with its im2col)
             if s_pre is not None:
-                raise _cabi.IvitKernelError("frozen QuantAct got a float carrier with a predecessor scale: every "
-                                            "module of the model must be frozen (model_utils.freeze_model)")
+                # a float module (the `float` registry entries) feeds this QuantAct: quant_utils.py:220
+                # z = round(x / s_pre) with torch ops (IEEE division + rint: same codes as on the CPU),
+                # then the integer requantisation kernel (identity branch included)
+                if self.activation_bit != 8:
+                    raise NotImplementedError("frozen QuantAct: 8-bit outputs only")
+                sp = s_pre.to(device).float()
+                z = torch.round(x.detach().float() / (sp.view(1, -1, 1, 1) if x.dim() == 4 and sp.numel() > 1 else sp))
+                z = z.to(torch.int32).contiguous()
+                s_in_h = fz.host_scale(sp)
+                mult, _ = self._mult(("req", s_in_h.tobytes()), s_in_h, device)
+                s_in_d = self._fz_get().setdefault(("s_in", s_in_h.tobytes()), _dev(s_in_h, torch.float32, device))
+                idc, mult_id = None, 0.0
+                if identity is not None:
+                    if not isinstance(identity, QTensor):
+                        raise _cabi.IvitKernelError("frozen QuantAct: identity must come from a frozen module")
+                    idc = identity.materialize().contiguous()
+                    _, mh = self._mult(("id", fz.eff_hscale(identity).tobytes()), fz.eff_hscale(identity), device)
+                    mult_id = float(mh[0])
+                z2 = z.reshape(-1, z.shape[-1])
+                out = ops.requant(z2, s_in_d, mult, qmin, qmax, idc.reshape(-1, z.shape[-1]) if idc is not None else None,
+                                  mult_id)
+                return self._wrap(out.reshape(z.shape), tuple(x.shape), device)
             inv = f32(1.0) / s_out_h[0]
             q = QTensor(pending=Pending("quantize", x=x.detach(), inv=inv, bits=self.activation_bit),
                         canon_shape=tuple(x.shape), scale=s_out, hscale=s_out_h, device=device)
@@ -410,7 +430,8 @@ class QuantMatMul(nn.Module):
     def forward(self, A, pre_act_scaling_factor_A, B, pre_act_scaling_factor_B):
         if isinstance(A, QTensor) or isinstance(B, QTensor):
             if not (isinstance(A, QTensor) and isinstance(B, QTensor)):
-                raise _cabi.IvitKernelError("QuantMatMul: both operands must come from frozen modules")
+                raise _cabi.IvitKernelError("QuantMatMul: both operands must come from frozen integer modules (the `float` "
+                                            "softmax entry runs in calibration mode only: its product is a float GEMM)")
             fz.require_cuda(A, "QuantMatMul")
             sA, sB = fz.eff_hscale(A), fz.eff_hscale(B)
             h = (sA * sB).astype(f32)

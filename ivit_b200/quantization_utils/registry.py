@@ -1,16 +1,18 @@
 """--gelu / --softmax / --layernorm selection (layer_selection.py:116-236): the `ivit` and `ibert`
 entries and the `base_arg_val_arg_val` name grammar that injects constructor keywords
-(`ibert_use-int-sqrt_true` -> IBERTIntLayerNorm(use_int_sqrt=True)).  The `float` / `ppoly` entries
-are outside this path and raise a clear error."""
+(`ibert_use-int-sqrt_true` -> IBERTIntLayerNorm(use_int_sqrt=True)), and the `float` diagnostics
+(true float op + quantised output, torch ops in every mode).  The `ppoly` entries are outside this
+path and raise a clear error."""
 from __future__ import annotations
 
+from .floatmods import FloatGELU, FloatLayerNorm, FloatSoftmax
 from .modules import (IBERTIntGELU, IBERTIntLayerNorm, IBERTIntSoftmax, IVITIntGELU, IVITIntLayerNorm,
                       IVITIntSoftmax)
 
-GELU_REGISTRY = {"ivit": IVITIntGELU, "ibert": IBERTIntGELU}
-SOFTMAX_REGISTRY = {"ivit": IVITIntSoftmax, "ibert": IBERTIntSoftmax}
-LN_REGISTRY = {"ivit": IVITIntLayerNorm, "ibert": IBERTIntLayerNorm}
-_NOT_BUILT = ("float", "ppoly")
+GELU_REGISTRY = {"float": FloatGELU, "ivit": IVITIntGELU, "ibert": IBERTIntGELU}
+SOFTMAX_REGISTRY = {"float": FloatSoftmax, "ivit": IVITIntSoftmax, "ibert": IBERTIntSoftmax}
+LN_REGISTRY = {"float": FloatLayerNorm, "ivit": IVITIntLayerNorm, "ibert": IBERTIntLayerNorm}
+_NOT_BUILT = ("ppoly",)
 
 
 def _coerce(text: str):
@@ -40,7 +42,7 @@ def _select(registry: dict, name: str, what: str):
     base, params = parse_layer_name(name)
     if base not in registry:
         if base in _NOT_BUILT or name.lower() in _NOT_BUILT:
-            raise NotImplementedError(f"{what} type '{name}': only the ivit|ibert entries are built on this path")
+            raise NotImplementedError(f"{what} type '{name}': only the float|ivit|ibert entries are built on this path")
         return registry[name.lower()]          # KeyError for unknown names, like the reference
     cls = registry[base]
     if not params:

@@ -31,6 +31,8 @@ def test_registry_grammar():
     assert qu.get_gelu("ivit") is qu.IVITIntGELU and qu.get_softmax("IBERT") is qu.IBERTIntSoftmax
     with pytest.raises(NotImplementedError):
         qu.get_gelu("ppoly_deg_2_seg_16")
+    assert qu.get_gelu("float") is qu.FloatGELU and qu.get_layernorm("FLOAT") is qu.FloatLayerNorm
+    assert qu.get_softmax("float_bitwidth_16")().bitwidth == 16
     with pytest.raises(KeyError):
         qu.get_gelu("nonsense")
 
@@ -87,3 +89,94 @@ def test_reference_vit_quant_runs_unchanged_and_calibrates_identically(case):
     assert model.qact_input.running_stat is False
     with pytest.raises(IvitKernelError):                    # frozen = integer kernels = CUDA only
         model(synth_images(1, cfg, seed=0))
+
+
+def _build_pair(case):
+    """The reference's VisionTransformer twice: on its own quantization_utils and on ours, same weights."""
+    from oracle.ref_shim import load_reference, load_reference_callers_on
+    import sys
+    ref = load_reference()
+    ref_vq = sys.modules[ref.__name__ + ".vit_quant"]
+    vq, mu = load_reference_callers_on(qu)
+    cfg, state, fix = load_case(case)
+    kw = dict(patch_size=cfg.patch_size, embed_dim=cfg.embed_dim, depth=cfg.depth, num_heads=cfg.num_heads,
+              mlp_ratio=cfg.mlp_ratio, qkv_bias=True, gelu_type=cfg.gelu_type, softmax_type=cfg.softmax_type,
+              layernorm_type=cfg.layernorm_type)
+    weights = {k: torch.as_tensor(v) for k, v in state.items() if not k.endswith((".x_min", ".x_max", ".shift"))}
+    models = []
+    for mod in (ref_vq, vq):
+        m = mod.VisionTransformer(**kw)
+        m.load_state_dict(weights, strict=False)
+        models.append(m.eval())
+    return cfg, models[0], models[1]
+
+
+@pytest.mark.reference
+@pytest.mark.parametrize("case", ["toy_ivit", "toy_ibert", "toy_mixed"])
+def test_state_dict_wire_format_equals_reference_after_calibration(case):
+    """same checkpoint keys, and after the calibration pass EVERY buffer the TVM
+    exporter and a later strict load read -- x_min/x_max, act/fc/conv/norm scaling factors,
+    weight_integer, bias_integer -- holds the reference's value bit for bit."""
+    from ivit_b200 import lifecycle
+    cfg, ref_model, our_model = _build_pair(case)
+    batches = [synth_images(4, cfg, seed=1), synth_images(2, cfg, seed=5)]     # two batches: EMA path too
+    with torch.no_grad():
+        for x in batches:
+            ref_model(x)
+    assert lifecycle.calibrate_model(our_model, batches) == 2
+    ref_sd, our_sd = ref_model.state_dict(), our_model.state_dict()
+    assert list(ref_sd.keys()) == list(our_sd.keys())
+    for k in ref_sd:
+        a, b = ref_sd[k], our_sd[k]
+        assert a.shape == b.shape and a.dtype == b.dtype, k
+        assert torch.equal(a, b) or (torch.isnan(a) == torch.isnan(b)).all() and torch.equal(
+            torch.nan_to_num(a), torch.nan_to_num(b)), k
+    params = lifecycle.tvm_params(our_model)
+    assert params["patch_embed.proj.weight_integer"].dtype == np.int8
+    assert params["head.bias_integer"].dtype == np.int32 and "blocks.0.norm1.norm_scaling_factor" in params or \
+        cfg.layernorm_type != "ivit"
+    # strict reload of our own state_dict (inference.py --strict-load path) and the 0-d buffer fix-up
+    cfg2, _, fresh = _build_pair(case)
+    sd = {k: (v.reshape(()) if v.numel() == 1 and k.endswith("act_scaling_factor") else v) for k, v in our_sd.items()}
+    missing, unexpected = lifecycle.load_checkpoint(fresh, {"model": sd, "epoch": 3}, strict=True)
+    assert not missing and not unexpected
+    lifecycle.freeze_model(fresh)
+    assert fresh.qact_input.running_stat is False
+    lifecycle.unfreeze_model(fresh)
+    assert fresh.qact_input.running_stat is True
+
+
+@pytest.mark.reference
+def test_float_registry_entries_equal_reference():
+    """SURVEY 8(f)-4, `float` part: same outputs and scales as layer_selection.py's Float* wrappers
+    (same torch ops, so bit-equal on the same device), and a whole model built on them calibrates to
+    the reference's logits and buffers."""
+    from oracle.ref_shim import load_reference
+    import sys
+    ref = load_reference()
+    ref_ls = sys.modules[ref.__name__ + ".quantization_utils.layer_selection"]
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(2, 7, 16, generator=g) * 2
+    s = torch.tensor(0.031)
+    for name, args in (("FloatGELU", ()), ("FloatSoftmax", ()), ("FloatLayerNorm", (16,))):
+        a, b = getattr(ref_ls, name)(*args), getattr(qu, name)(*args)
+        b.load_state_dict(a.state_dict())
+        (ya, sa), (yb, sb) = a(x, s), b(x, s)
+        assert torch.equal(ya, yb) and torch.equal(torch.as_tensor(sa), torch.as_tensor(sb)), name
+    from oracle.ref_shim import load_reference_callers_on
+    ref_vq = sys.modules[ref.__name__ + ".vit_quant"]
+    vq, mu = load_reference_callers_on(qu)
+    cfg, state, fix = load_case("toy_ivit")
+    kw = dict(patch_size=cfg.patch_size, embed_dim=cfg.embed_dim, depth=cfg.depth, num_heads=cfg.num_heads,
+              mlp_ratio=cfg.mlp_ratio, qkv_bias=True, gelu_type="float", softmax_type="float", layernorm_type="float")
+    torch.manual_seed(3)
+    m_ref = ref_vq.VisionTransformer(**kw).eval()
+    m_our = vq.VisionTransformer(**kw).eval()
+    assert list(m_ref.state_dict().keys()) == list(m_our.state_dict().keys())
+    m_our.load_state_dict(m_ref.state_dict())
+    xin = synth_images(3, cfg, seed=2)
+    with torch.no_grad():
+        la, lb = m_ref(xin), m_our(xin)
+    assert torch.equal(la, lb)
+    for k, v in m_ref.state_dict().items():
+        assert torch.equal(v, m_our.state_dict()[k]), k

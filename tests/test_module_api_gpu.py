@@ -86,3 +86,33 @@ def test_compile_frozen_equals_module_path():
     assert torch.equal(out, ref)
     sess2 = compile_frozen(model, batch=4, chunks=2)
     assert torch.equal(sess2.infer(x.pin_memory()), ref)
+
+
+def test_float_gelu_and_layernorm_under_frozen_quantacts():
+    """The `float` registry entries (diagnostics: true float op, quantised output) inside a frozen
+    model: their float outputs re-enter the integer path through round(x / scale) + the requant
+    kernel.  Against the same model in float-simulated mode on the same device (floating-point
+    modules: logits within 2 % of the logit range, same argmax)."""
+    import dataclasses
+    cfg, state, fix = load_case("toy_ivit")
+    cfg = dataclasses.replace(cfg, gelu_type="float", layernorm_type="float")
+    torch.manual_seed(1)
+    model = VisionTransformer(cfg)
+    sd = {k: torch.as_tensor(v).reshape(model.state_dict()[k].shape) for k, v in state.items()
+          if k in model.state_dict() and not k.endswith((".x_min", ".x_max"))}
+    model.load_state_dict(sd, strict=False)
+    model.cuda().eval()
+    x = synth_images(4, cfg, seed=0).cuda()
+    with torch.no_grad():
+        sim = model(synth_images(4, cfg, seed=1).cuda())       # calibration pass (running statistics)
+        for m in model.modules():
+            if hasattr(m, "running_stat"):
+                m.running_stat = False
+        sim = model(x).float()                                 # float-simulated, ranges fixed
+        freeze(model)
+        out = model(x)
+    out = (out.dequantize() if isinstance(out, QTensor) else out).float()
+    assert out.shape == sim.shape and torch.isfinite(out).all()
+    span = float(sim.max() - sim.min())
+    assert float((out - sim).abs().max()) <= 0.02 * span
+    assert torch.equal(out.argmax(-1), sim.argmax(-1))
