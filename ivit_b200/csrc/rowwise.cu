@@ -19,25 +19,49 @@ __device__ __forceinline__ int quant8(float x, float inv_s) {
 // fp32 image [B,Cin,H,W] -> int8 patch matrix [B*gh*gw, Cin*P*P] (k = c*P*P + i*P + j): the
 // im2col of a kernel=stride=P convolution is a pure re-indexing, so it is folded into the
 // quantiser's store layout.
-__global__ void quantize_patches_kernel(const float* __restrict__ x, int8_t* __restrict__ out, float inv_s, int B,
-                                        int Cin, int H, int W, int P) {
+// One CTA walks output rows (= patches); a thread owns 4 consecutive k of the row (one float4 of an
+// image row).  32-bit index arithmetic, and shifts instead of divisions when P is a power of two
+// (PLOG2 >= 0): the generic 64-bit div/mod version spent ~5x the memory time on index maths.
+template <int PLOG2>
+__global__ void __launch_bounds__(256)
+quantize_patches_kernel(const float* __restrict__ x, int8_t* __restrict__ out, float inv_s, int B, int Cin, int H, int W,
+                        int P) {
   const int gh = H / P, gw = W / P;
-  const int K = Cin * P * P;
-  const long long total4 = static_cast<long long>(B) * gh * gw * K / 4;
-  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total4;
-       t += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long o = t * 4;
-    const int k = static_cast<int>(o % K);
-    const long long row = o / K;
-    const int pw = static_cast<int>(row % gw);
-    const int ph = static_cast<int>((row / gw) % gh);
-    const int b = static_cast<int>(row / (static_cast<long long>(gw) * gh));
-    const int j = k % P, i = (k / P) % P, c = k / (P * P);
-    const float4 v = *reinterpret_cast<const float4*>(
-        x + ((static_cast<long long>(b) * Cin + c) * H + ph * P + i) * W + pw * P + j);
-    const int q0 = quant8(v.x, inv_s), q1 = quant8(v.y, inv_s), q2 = quant8(v.z, inv_s), q3 = quant8(v.w, inv_s);
-    const uint32_t packed = (q0 & 0xff) | ((q1 & 0xff) << 8) | ((q2 & 0xff) << 16) | (static_cast<uint32_t>(q3) << 24);
-    *reinterpret_cast<uint32_t*>(out + o) = packed;
+  const int K = Cin * P * P, K4 = K / 4;
+  const int rows = B * gh * gw;
+  // two rows per iteration: both float4 loads are in flight before the first store
+  for (int row0 = blockIdx.x; row0 < rows; row0 += 2 * gridDim.x) {
+    const float* img[2];
+    uint32_t* orow[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int row = min(row0 + u * static_cast<int>(gridDim.x), rows - 1);
+      const int pw = row % gw, t = row / gw;
+      const int ph = t % gh, b = t / gh;
+      img[u] = x + (static_cast<long long>(b) * Cin * H + ph * P) * W + pw * P;
+      orow[u] = reinterpret_cast<uint32_t*>(out + static_cast<long long>(row) * K);
+    }
+    const bool two = row0 + static_cast<int>(gridDim.x) < rows;
+    for (int k4 = threadIdx.x; k4 < K4; k4 += blockDim.x) {
+      const int k = k4 * 4;
+      int j, i, c;
+      if (PLOG2 >= 0) {
+        j = k & (P - 1); i = (k >> PLOG2) & (P - 1); c = k >> (2 * PLOG2);
+      } else {
+        j = k % P; i = (k / P) % P; c = k / (P * P);
+      }
+      const long long off = (static_cast<long long>(c) * H + i) * W + j;
+      float4 v[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) v[u] = __ldg(reinterpret_cast<const float4*>(img[u] + off));
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        if (u == 1 && !two) break;
+        const int q0 = quant8(v[u].x, inv_s), q1 = quant8(v[u].y, inv_s), q2 = quant8(v[u].z, inv_s),
+                  q3 = quant8(v[u].w, inv_s);
+        orow[u][k4] = (q0 & 0xff) | ((q1 & 0xff) << 8) | ((q2 & 0xff) << 16) | (static_cast<uint32_t>(q3) << 24);
+      }
+    }
   }
 }
 
@@ -650,10 +674,18 @@ extern "C" int ivit_quantize_f32_i8(const float* x, int8_t* out, float inv_scale
 extern "C" int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float inv_scale, int B, int Cin, int H,
                                             int W, int P, void* stream) {
   if (P % 4 != 0 || H % P != 0 || W % P != 0) return fail(IVIT_ERR_BAD_ARG, "patch size must divide H, W; P % 4 == 0");
-  const long long n4 = static_cast<long long>(B) * Cin * H * W / 4;
-  if (n4 <= 0) return 0;
-  quantize_patches_kernel<<<ew_grid(n4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, out, inv_scale, B, Cin,
-                                                                                         H, W, P);
+  const long long rows = static_cast<long long>(B) * (H / P) * (W / P);
+  if (rows <= 0) return 0;
+  if (rows > 0x7fffffffLL || static_cast<long long>(Cin) * P * P > 0x7fffffffLL)
+    return fail(IVIT_ERR_UNSUPPORTED, "quantize_patches: more than 2^31 patches");
+  const int grid = static_cast<int>(rows < 148LL * 32 ? rows : 148LL * 32);
+  const int k4 = Cin * P * P / 4;
+  const int threads = k4 >= 256 ? 256 : (k4 + 31) / 32 * 32;      // one pass over a row where it fits
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (P == 16) quantize_patches_kernel<4><<<grid, threads, 0, st>>>(x, out, inv_scale, B, Cin, H, W, P);
+  else if (P == 8) quantize_patches_kernel<3><<<grid, threads, 0, st>>>(x, out, inv_scale, B, Cin, H, W, P);
+  else if (P == 4) quantize_patches_kernel<2><<<grid, threads, 0, st>>>(x, out, inv_scale, B, Cin, H, W, P);
+  else quantize_patches_kernel<-1><<<grid, threads, 0, st>>>(x, out, inv_scale, B, Cin, H, W, P);
   return check_launch("quantize_patches_kernel");
 }
 

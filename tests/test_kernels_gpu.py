@@ -46,6 +46,14 @@ def test_quantize_patches():
     _cmp(got, exp, "quantize_patches")
     got2 = ops.quantize(_t(x, torch.float32), float(inv)).cpu().numpy()
     _cmp(got2, q, "quantize")
+    # other patch sizes: 4 (Swin's 4x4 stem: power-of-two path), 8, and 12 (generic division path)
+    for P, HW in ((4, 32), (8, 32), (12, 48)):
+        xs = rng.standard_normal((2, 3, HW, HW)).astype(f32)
+        qs = O.sym_quantize(xs, 8, s, is_weight=False)
+        g = HW // P
+        exps = qs.reshape(2, 3, g, P, g, P).transpose(0, 2, 4, 1, 3, 5).reshape(2 * g * g, 3 * P * P)
+        gots = ops.quantize_patches(_t(xs, torch.float32), float(inv), P).cpu().numpy()
+        _cmp(gots, exps, f"quantize_patches P={P}")
 
 
 def _ln_case(kind, C, rows, seed, s_in=0.0371, ties=True, neg=False, use_int_sqrt=False):
