@@ -159,6 +159,9 @@ int ivit_softmax_table_build(const ivit_attention_params_t* p, float* table65536
 int ivit_softmax_table_collapse(const float* table65536, float* table256, int* collapsible, void* stream);
 int ivit_attention_i8(const int8_t* qkv, int8_t* out, int B, int N, int H, int hd,
                       const ivit_attention_params_t* p, void* stream);
+/* The kernel runs 2 or 4 threads per query row (8 or 16 warps per CTA; default 2).  Returns the
+ * previous setting; other values are ignored.  Process-wide; for A/B timing and tests. */
+int ivit_attention_set_threads_per_row(int tpr);
 /* Debug taps of the same kernel: softmax codes [B,H,N,N] uint8 (what int_softmax emits). */
 int ivit_attention_probs_i8(const int8_t* qkv, uint8_t* probs, int B, int N, int H, int hd,
                             const ivit_attention_params_t* p, void* stream);

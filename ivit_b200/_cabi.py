@@ -74,6 +74,7 @@ _SIGS = {
     "ivit_gemm_i8": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                C.c_int64, C.POINTER(GemmEpilogue), C.c_void_p]),
     "ivit_gemm_set_layout": (C.c_int, [C.c_int]),
+    "ivit_attention_set_threads_per_row": (C.c_int, [C.c_int]),
     "ivit_layernorm_set_variant": (C.c_int, [C.c_int]),
     "ivit_gemm_i8_simple": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                       C.c_int64, C.POINTER(GemmEpilogue), C.c_void_p]),

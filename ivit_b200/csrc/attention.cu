@@ -86,50 +86,59 @@ __global__ void softmax_table_collapse_check(const float* __restrict__ table, co
   if (j <= m && __float_as_uint(table[m * 256 + j]) != __float_as_uint(t1[m - j])) *ok = 0;
 }
 
-// for ci in [0, n): body(ci, v) over this thread's 16 TMEM columns of 32-column chunk ci, with the
+__device__ __forceinline__ void tmem_ld_w(uint32_t t, uint32_t (&r)[8]) { tmem_ld8(t, r); }
+__device__ __forceinline__ void tmem_ld_w(uint32_t t, uint32_t (&r)[16]) { tmem_ld16(t, r); }
+__device__ __forceinline__ void tmem_ld_w(uint32_t t, uint32_t (&r)[32]) { tmem_ld32(t, r); }
+__device__ __forceinline__ void tmem_st_w(uint32_t t, const uint32_t (&r)[8]) { tmem_st8(t, r); }
+__device__ __forceinline__ void tmem_st_w(uint32_t t, const uint32_t (&r)[16]) { tmem_st16(t, r); }
+
+// for ci in [0, n): body(ci, v) over this thread's W TMEM columns of 32-column chunk ci, with the
 // tcgen05.ld of chunk ci + 1 in flight while chunk ci is processed (two register buffers).
-template <class F>
+template <int W, class F>
 __device__ __forceinline__ void chunk_pipeline(uint32_t t_row, int n, F&& body) {
-  uint32_t v0[16], v1[16];
-  if (n > 0) tmem_ld16(t_row, v0);
+  uint32_t v0[W], v1[W];
+  if (n > 0) tmem_ld_w(t_row, v0);
   for (int ci = 0; ci < n; ci += 2) {
     tmem_ld_wait();
-    if (ci + 1 < n) tmem_ld16(t_row + (ci + 1) * 32, v1);
+    if (ci + 1 < n) tmem_ld_w(t_row + (ci + 1) * 32, v1);
     body(ci, v0);
     if (ci + 1 < n) {
       tmem_ld_wait();
-      if (ci + 2 < n) tmem_ld16(t_row + (ci + 2) * 32, v0);
+      if (ci + 2 < n) tmem_ld_w(t_row + (ci + 2) * 32, v0);
       body(ci + 1, v1);
     }
   }
 }
 
-// 256 threads = two threads per query row: thread A (warps 0-3) owns columns [32i, 32i+16) of
-// every 32-column chunk, thread B (warps 4-7) columns [32i+16, 32i+32).  That split keeps torch's
-// float32 summation order (accumulator e % 32 lives in exactly one thread) while doubling the
-// warps that hide the TMEM / table-gather latency.  TABLE 1: exp term gathered from the global
+// CTA = one (image, head, 128-query tile); TPR threads per query row (2 or 4): thread q of a row
+// (warps 4q .. 4q+3) owns columns [32i + q W, 32i + (q+1) W), W = 32 / TPR, of every 32-column
+// chunk.  That split keeps torch's float32 summation order (accumulator e % 32 lives in exactly one
+// thread) while multiplying the warps that hide the TMEM / table-gather latency (the kernel is
+// occupancy-bound: TMEM allows two CTAs per SM).  TABLE 1: exp term gathered from the global
 // (row max, code) table (32 sectors per warp load); TABLE 2: from the 256-entry (row max - code)
 // table replicated 16x in shared memory (copy lane % 16: at most 2 lanes per bank); TABLE 0:
 // computed.  TAP: also dump the softmax codes (tests).
-template <int TABLE, bool TAP>
-__global__ void __launch_bounds__(256, 2)
+template <int TPR, int TABLE, bool TAP>
+__global__ void __launch_bounds__(128 * TPR, 2)
 attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
+  constexpr int W = 32 / TPR;               // columns per thread per 32-column chunk
+  constexpr int OW = HD / TPR;              // output head-dims per thread
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sP = smem;                       // 2 x [128 rows x 128 B], SWIZZLE_128B (written by threads)
   uint8_t* sQ = smem + 32768;               // [128 x 64 B]  SWIZZLE_64B (TMA)
   uint8_t* sK = sQ + 8192;                  // [<=256 x 64 B]
   uint8_t* sV = sK + 16384;                 // [<=256 x 64 B]
-  float* sAcc = reinterpret_cast<float*>(sV + 16384);          // [16][128] B's accumulators -> A
-  int* sMax = reinterpret_cast<int*>(sAcc + 16 * 128);         // [2][128]
-  float* sFac = reinterpret_cast<float*>(sMax + 256);          // [128]
+  float* sAcc = reinterpret_cast<float*>(sV + 16384);          // [32][128] accumulators of threads q > 0 -> thread 0
+  int* sMax = reinterpret_cast<int*>(sAcc + 32 * 128);         // [4][128]
+  float* sFac = reinterpret_cast<float*>(sMax + 512);          // [128]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sFac + 128);    // qk, v, s, o
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
   float* sT = reinterpret_cast<float*>(bars + 8);              // TABLE 2: [256][16]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int half = warp >> 2;               // 0: thread A, 1: thread B
+  const int q = warp >> 2;                  // which of the row's TPR threads
   const int quarter = warp & 3;             // TMEM lane quarter
   const int mt = blockIdx.x;
   const int b = blockIdx.y / a.H, h = blockIdx.y % a.H;
@@ -171,7 +180,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     tc_commit(&bars[2]);
   }
   __syncwarp();
-  if (TABLE == 2) {
+  if (TABLE == 2 && threadIdx.x < 256) {
     // replicate while the TMA loads and the S MMA run; visible after the barrier that ends pass 1
 #pragma unroll
     for (int i = 0; i < 16; ++i) sT[i * 256 + threadIdx.x] = __ldg(a.exp_table_1d + i * 16 + (threadIdx.x >> 4));
@@ -182,39 +191,39 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   tc_fence_after();
   const int r_loc = quarter * 32 + lane;
   const int row = mt * 128 + r_loc;                     // token index within the image
-  const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + half * 16;
+  const int cbase = q * W;                              // this thread's first column inside a chunk
+  const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + cbase;
   const int nfull = N / 32;                             // chunks with all 32 columns valid
   const int nchunks = (N + 31) / 32;
   const int pchunks = a.KP2 / 32;
-  // chunks in which THIS thread's 16-column segment holds a valid column (warp-uniform: a warp is all
-  // A or all B threads): for N = 197 thread B skips the 7th chunk entirely
-  const int my_chunks = (N - half * 16 + 31) / 32;
+  // chunks in which THIS thread's W-column segment holds a valid column (warp-uniform: all threads
+  // of a warp have the same q): for N = 197 the last segments skip the 7th chunk entirely
+  const int my_chunks = (N - cbase + 31) / 32;
   const bool warp_active = mt * 128 + quarter * 32 < N; // warp-uniform: rows past the last token do no work
-  const int cbase = half * 16;                          // this thread's first column inside a chunk
 
   // pass 1: qact_attn1 requant, row max; codes go back to TMEM
   int cmax = -(1 << 30);
   if (warp_active) {
-    chunk_pipeline(t_row, my_chunks, [&](int ci, uint32_t (&v)[16]) {
+    chunk_pipeline<W>(t_row, my_chunks, [&](int ci, uint32_t (&v)[W]) {
       if (ci < nfull) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
+        for (int j = 0; j < W; ++j) {
           const int c = clampi(requant_i32_fast(static_cast<int>(v[j]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
           cmax = max(cmax, c);
           v[j] = static_cast<uint32_t>(c);
         }
       } else {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
+        for (int j = 0; j < W; ++j) {
           const int c = clampi(requant_i32_fast(static_cast<int>(v[j]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
           if (ci * 32 + cbase + j < N) cmax = max(cmax, c);
           v[j] = static_cast<uint32_t>(c);
         }
       }
-      tmem_st16(t_row + ci * 32, v);
+      tmem_st_w(t_row + ci * 32, v);
     });
     tmem_st_wait();
-    sMax[half * 128 + r_loc] = cmax;
+    sMax[q * 128 + r_loc] = cmax;
   }
   tc_fence_before();
   __syncthreads();
@@ -222,7 +231,8 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   float xmax = 0.f;
   const float* trow = nullptr;
   if (warp_active) {
-    cmax = max(sMax[r_loc], sMax[128 + r_loc]);
+#pragma unroll
+    for (int t = 0; t < TPR; ++t) cmax = max(cmax, sMax[t * 128 + r_loc]);
     xmax = x_eff(static_cast<float>(cmax), a.p.s_attn);   // max of un-rounded x/s (monotone in code)
     if (TABLE == 1) trow = a.exp_table + (cmax + 128) * 256 + 128;
     if (TABLE == 2) trow = sT + cmax * 16 + (lane & 15);           // entry (cmax - c) of copy lane % 16
@@ -234,48 +244,51 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   };
 
   // pass 2: exp terms -> TMEM; float32 row sum in torch's CPU order: accumulator (col % 32) is
-  // acc[col % 16] of thread (col % 32) / 16, fed in ascending column order.
+  // acc[col % W] of thread (col % 32) / W, fed in ascending column order.
   const int nvec = N / 8, size_ilp = nvec / 4;           // size_ilp == nfull
-  float acc[16];
+  float acc[W];
 #pragma unroll
-  for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+  for (int j = 0; j < W; ++j) acc[j] = 0.f;
   if (warp_active) {
-    chunk_pipeline(t_row, size_ilp, [&](int ci, uint32_t (&v)[16]) {
+    chunk_pipeline<W>(t_row, size_ilp, [&](int ci, uint32_t (&v)[W]) {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
+      for (int j = 0; j < W; ++j) {
         const float e = term(static_cast<int>(v[j]));
         acc[j] = __fadd_rn(acc[j], e);
         v[j] = __float_as_uint(e);
       }
-      tmem_st16(t_row + ci * 32, v);
+      tmem_st_w(t_row + ci * 32, v);
     });
-    if (my_chunks > size_ilp) {        // partial chunk: exp terms only; its sum is thread A's job below
-      uint32_t v[16];
-      tmem_ld16(t_row + size_ilp * 32, v);
+    if (my_chunks > size_ilp) {        // partial chunk: exp terms only; its sum is thread 0's job below
+      uint32_t v[W];
+      tmem_ld_w(t_row + size_ilp * 32, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 16; ++j)
+      for (int j = 0; j < W; ++j)
         v[j] = (size_ilp * 32 + cbase + j < N) ? __float_as_uint(term(static_cast<int>(v[j]))) : 0u;
-      tmem_st16(t_row + size_ilp * 32, v);
+      tmem_st_w(t_row + size_ilp * 32, v);
     }
     tmem_st_wait();
-    if (half == 1) {
+    if (q > 0) {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) sAcc[j * 128 + r_loc] = acc[j];
+      for (int j = 0; j < W; ++j) sAcc[(cbase + j) * 128 + r_loc] = acc[j];
     }
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (warp_active && half == 0) {
-    // torch: ps[0] (lanes 0..7) += left-over whole vectors, THEN rows 1..3 are added, then the tail scalars
+  if (warp_active && q == 0) {
+    // torch keeps 4 rows of 8 accumulators (e % 32 = 8 k + l): ps[0] (row 0) += left-over whole
+    // vectors, THEN rows 1..3 are added, then the tail scalars.  Accumulator i lives in this thread
+    // for i < W, else in shared memory.
+    auto acc32 = [&](int i) -> float { return i < W ? acc[i < W ? i : 0] : sAcc[i * 128 + r_loc]; };
     float p8[8];
 #pragma unroll
     for (int l = 0; l < 8; ++l) p8[l] = acc[l];
     float tail = 0.f;
     if (nchunks > size_ilp) {
       uint32_t v[32];
-      tmem_ld32(t_row + size_ilp * 32, v);             // whole partial chunk (both halves' exp terms)
+      tmem_ld32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + size_ilp * 32, v);   // every thread's terms
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
@@ -286,11 +299,9 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
     }
 #pragma unroll
-    for (int l = 0; l < 8; ++l) p8[l] = __fadd_rn(p8[l], acc[8 + l]);
+    for (int k = 1; k < 4; ++k)
 #pragma unroll
-    for (int l = 0; l < 8; ++l) p8[l] = __fadd_rn(p8[l], sAcc[l * 128 + r_loc]);
-#pragma unroll
-    for (int l = 0; l < 8; ++l) p8[l] = __fadd_rn(p8[l], sAcc[(8 + l) * 128 + r_loc]);
+      for (int l = 0; l < 8; ++l) p8[l] = __fadd_rn(p8[l], acc32(8 * k + l));
     float sum = tail;
 #pragma unroll
     for (int l = 0; l < 8; ++l) sum = __fadd_rn(sum, p8[l]);
@@ -304,17 +315,21 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   // pass 3: probabilities -> u8 operand tile in shared memory (K-major, SWIZZLE_128B)
   if (warp_active) {
     const float fs = sFac[r_loc];
-    auto store_p = [&](int ci, const uint32_t (&w)[4]) {
-      // 16 bytes = one 16-byte unit of this row's 128-byte swizzle line
+    auto store_p = [&](int ci, const uint32_t (&w)[W / 4]) {
+      // W bytes inside one 16-byte unit of this row's 128-byte swizzle line
       const int col = ci * 32 + cbase;
       uint8_t* base = sP + (col >> 7) * 16384 + (r_loc >> 3) * 1024 + (r_loc & 7) * 128;
       const int u0 = (col & 127) >> 4;
-      *reinterpret_cast<int4*>(base + ((u0 ^ (r_loc & 7)) << 4)) = make_int4(w[0], w[1], w[2], w[3]);
+      uint8_t* dst = base + ((u0 ^ (r_loc & 7)) << 4) + (col & 15);
+      if (W == 16) *reinterpret_cast<int4*>(dst) = make_int4(w[0], w[1], w[W / 4 - 2], w[W / 4 - 1]);
+      else *reinterpret_cast<uint2*>(dst) = make_uint2(w[0], w[1]);
     };
-    chunk_pipeline(t_row, my_chunks, [&](int ci, uint32_t (&v)[16]) {
-      uint32_t w[4] = {0, 0, 0, 0};
+    chunk_pipeline<W>(t_row, my_chunks, [&](int ci, uint32_t (&v)[W]) {
+      uint32_t w[W / 4];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
+      for (int j = 0; j < W / 4; ++j) w[j] = 0;
+#pragma unroll
+      for (int j = 0; j < W; ++j) {
         // :175 / :315 (terms past column N were stored as 0).  floor of a value in [0, 2^22) through
         // the 2^23 magic constant (round toward zero) instead of F2I (quarter-rate XU pipe)
         const uint32_t pc = __float_as_uint(__fadd_rz(__fmul_rn(__uint_as_float(v[j]), fs), 8388608.f)) & 0xffu;
@@ -322,11 +337,13 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
       if (TAP && a.probs != nullptr && row < N) {
         uint8_t* pr = a.probs + ((static_cast<long long>(blockIdx.y) * N + row) * N) + ci * 32 + cbase;
-        for (int j = 0; j < 16 && ci * 32 + cbase + j < N; ++j) pr[j] = static_cast<uint8_t>(w[j >> 2] >> (8 * (j & 3)));
+        for (int j = 0; j < W && ci * 32 + cbase + j < N; ++j) pr[j] = static_cast<uint8_t>(w[j >> 2] >> (8 * (j & 3)));
       }
       store_p(ci, w);
     });
-    const uint32_t zero[4] = {0, 0, 0, 0};
+    uint32_t zero[W / 4];
+#pragma unroll
+    for (int j = 0; j < W / 4; ++j) zero[j] = 0;
     for (int ci = my_chunks; ci < pchunks; ++ci) store_p(ci, zero);   // K padding of the P V product
   }
   fence_proxy_async_smem();     // generic-proxy smem writes -> visible to tcgen05.mma
@@ -352,23 +369,24 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   mbar_wait(&bars[3], 0);
   tc_fence_after();
   if (warp_active) {
-    // O tile: columns [0,64); thread A stores head-dim 0..31, thread B 32..63.  The TMEM load is
+    // O tile: columns [0,64); thread q stores head-dims [q OW, (q+1) OW).  The TMEM load is
     // warp-collective (.sync.aligned): it must stay outside the per-lane row guard.
-    uint32_t o[32];
-    tmem_ld32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + half * 32, o);
+    uint32_t o[OW];
+    tmem_ld_w(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + q * OW, o);
     tmem_ld_wait();
     if (row < N && a.out != nullptr) {
-      uint32_t w[8];
+      uint32_t w[OW / 4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) w[j] = 0;
+      for (int j = 0; j < OW / 4; ++j) w[j] = 0;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
+      for (int j = 0; j < OW; ++j) {
         const int c = clampi(requant_i32_fast(static_cast<int>(o[j]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
         w[j >> 2] |= (static_cast<uint32_t>(c) & 0xffu) << (8 * (j & 3));
       }
-      int8_t* op = a.out + (static_cast<long long>(b) * N + row) * C + h * HD + half * 32;
-      *reinterpret_cast<int4*>(op) = make_int4(w[0], w[1], w[2], w[3]);
-      *reinterpret_cast<int4*>(op + 16) = make_int4(w[4], w[5], w[6], w[7]);
+      int8_t* op = a.out + (static_cast<long long>(b) * N + row) * C + h * HD + q * OW;
+#pragma unroll
+      for (int j = 0; j < OW / 16; ++j)
+        *reinterpret_cast<int4*>(op + 16 * j) = make_int4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
     }
   }
   tc_fence_before();
@@ -397,6 +415,10 @@ static void derive_softmax_consts(AttnArgs& a, const ivit_attention_params_t* p)
   }
 }
 
+// threads per query row: 2 (8 warps per CTA; default: measured 1.60 ms/step on DeiT-S) or 4 (16 warps
+// per CTA, 64 registers, no spills: 1.67 ms/step -- more warps do not help, the passes are throughput-bound)
+static int g_attn_tpr = 2;
+
 static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int N, int H, int hd,
                             const ivit_attention_params_t* p, cudaStream_t st) {
   if (!p) return fail(IVIT_ERR_BAD_ARG, "attention: params NULL");
@@ -419,18 +441,25 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
   if ((rc = make_tmap_2d_u8(&tv, qkv, cols, rows, cols, HD, a.KP2, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   const int table = a.exp_table_1d != nullptr ? 2 : (a.exp_table != nullptr ? 1 : 0);
   const bool tap = probs != nullptr;
-  const size_t smem = 1024 + 32768 + 8192 + 16384 + 16384 + 16 * 128 * 4 + 256 * 4 + 128 * 4 + 64 +
+  const size_t smem = 1024 + 32768 + 8192 + 16384 + 16384 + 32 * 128 * 4 + 512 * 4 + 128 * 4 + 64 +
                       (table == 2 ? 256 * 16 * 4 : 0);
+  const int tpr = g_attn_tpr;
   auto launch = [&](auto kernel) -> int {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
     dim3 grid((N + 127) / 128, B * H);
-    kernel<<<grid, 256, smem, st>>>(tq, tk, tv, a);
+    kernel<<<grid, 128 * tpr, smem, st>>>(tq, tk, tv, a);
     return 0;
   };
-  if (table == 2) rc = tap ? launch(attention_i8_kernel<2, true>) : launch(attention_i8_kernel<2, false>);
-  else if (table == 1) rc = tap ? launch(attention_i8_kernel<1, true>) : launch(attention_i8_kernel<1, false>);
-  else rc = tap ? launch(attention_i8_kernel<0, true>) : launch(attention_i8_kernel<0, false>);
+  if (tpr == 4) {
+    if (table == 2) rc = tap ? launch(attention_i8_kernel<4, 2, true>) : launch(attention_i8_kernel<4, 2, false>);
+    else if (table == 1) rc = tap ? launch(attention_i8_kernel<4, 1, true>) : launch(attention_i8_kernel<4, 1, false>);
+    else rc = tap ? launch(attention_i8_kernel<4, 0, true>) : launch(attention_i8_kernel<4, 0, false>);
+  } else {
+    if (table == 2) rc = tap ? launch(attention_i8_kernel<2, 2, true>) : launch(attention_i8_kernel<2, 2, false>);
+    else if (table == 1) rc = tap ? launch(attention_i8_kernel<2, 1, true>) : launch(attention_i8_kernel<2, 1, false>);
+    else rc = tap ? launch(attention_i8_kernel<2, 0, true>) : launch(attention_i8_kernel<2, 0, false>);
+  }
   if (rc) return rc;
   return check_launch("attention_i8_kernel");
 }
@@ -438,6 +467,12 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
 }  // namespace ivit
 
 using namespace ivit;
+
+extern "C" int ivit_attention_set_threads_per_row(int tpr) {
+  const int prev = g_attn_tpr;
+  if (tpr == 2 || tpr == 4) g_attn_tpr = tpr;
+  return prev;
+}
 
 extern "C" int ivit_attention_i8(const int8_t* qkv, int8_t* out, int B, int N, int H, int hd,
                                  const ivit_attention_params_t* p, void* stream) {

@@ -152,6 +152,11 @@ def set_layernorm_variant(variant: int) -> int:
     return _cabi.load().ivit_layernorm_set_variant(int(variant))
 
 
+def set_attention_threads_per_row(tpr: int) -> int:
+    """2 or 4 threads per query row in the attention kernel.  Returns the old value."""
+    return _cabi.load().ivit_attention_set_threads_per_row(int(tpr))
+
+
 def set_gemm_layout(layout: int) -> int:
     """0: ivit_gemm_i8 picks its kernel per call; 1: tokens-on-lanes kernel only.  Returns the old value."""
     return _cabi.load().ivit_gemm_set_layout(int(layout))

@@ -308,22 +308,30 @@ def _attention_case(kind, B, N, H, seed, s_qkv=0.05, a_max=None):
     return bool(p.exp_table_1d)
 
 
-@pytest.mark.parametrize("N", [197, 64, 49, 256, 130])
-def test_attention_ivit(N):
+@pytest.fixture(params=[4, 2], ids=["tpr4", "tpr2"])
+def threads_per_row(request):
+    """Both thread layouts of the attention kernel (4 or 2 threads per query row)."""
+    prev = ops.set_attention_threads_per_row(request.param)
+    yield request.param
+    ops.set_attention_threads_per_row(prev)
+
+
+@pytest.mark.parametrize("N", [197, 64, 49, 256, 130, 1, 33, 17])
+def test_attention_ivit(N, threads_per_row):
     _attention_case(0, 2, N, 3, seed=N)
 
 
 @pytest.mark.parametrize("N", [197, 100])
-def test_attention_ivit_collapsed_table(N):
+def test_attention_ivit_collapsed_table(N, threads_per_row):
     """s_attn = 2^-4: x/s recovers every code exactly, the (row max, code) table depends on the
     difference only and the kernel takes its shared-memory table path (most scales do not)."""
     assert _attention_case(0, 2, N, 3, seed=N + 3, s_qkv=0.03, a_max=127.0 / 16.0)
 
 
-def test_attention_ivit_peaked():
+def test_attention_ivit_peaked(threads_per_row):
     _attention_case(0, 2, 197, 2, seed=7, s_qkv=0.2)
 
 
 @pytest.mark.parametrize("N", [197, 49])
-def test_attention_ibert(N):
+def test_attention_ibert(N, threads_per_row):
     _attention_case(1, 2, N, 3, seed=N + 1)
