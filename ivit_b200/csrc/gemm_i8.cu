@@ -557,10 +557,12 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int qc = (lane >> 2) * 4;          //                      and its first channel within the warp's 32
     int pb = 0;
     double pm = 0.0;
+    float ps = 0.f;                          // MODE 3: dequantisation scale of the channel
     auto fetch_params = [&](int cb) {
       const int n = cb * Cfg::CB + quarter * 32 + lane;
       pb = (e.bias != nullptr && n < args.N) ? __ldg(e.bias + n) : 0;
-      pm = n < args.N ? __ldg(e.mult + n) : 0.0;
+      if (MODE == 3) ps = n < args.N ? __ldg(e.scale_out + n) : 0.f;
+      else pm = n < args.N ? __ldg(e.mult + n) : 0.0;
     };
     TileWalk tw(blockIdx.x, gridDim.x, ncb), tw_next = tw;
     if (blockIdx.x < ntiles) fetch_params(tw.cb);
@@ -575,6 +577,8 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       const int tok_w = tw.tb * Cfg::TB + part * Cfg::PART;    // the warp's first token
       const int n = c0 + lane;
       const double mult = pm;
+      const float scale = ps;
+      const int bias_now = pb;
       const double kb = kMagicInt - static_cast<double>(pb);
       const int brange = pb + (1 << 22);                       // CHECKED: 0 <= acc + brange < 2^23
       if (t + gridDim.x < ntiles) fetch_params(tw_next.cb);
@@ -626,6 +630,19 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             if (lane == 0) mbar_arrive(&tempty_bar[a]);
           }
           const uint32_t(&z)[16] = acc[ch & 1];        // rows past M are TMA zero fill: harmless, stores are guarded
+          if (MODE == 3) {
+            // LOGITS (head, vit_quant.py:311): float32(acc + bias) * scale[n]; lane = channel, so a
+            // token's 32 values leave as one 128-byte row segment
+            float* const outf = static_cast<float*>(args.out);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int tok = tok_w + ch * 16 + j;
+              if (n < args.N && tok < args.M)
+                outf[static_cast<uint32_t>(tok) * ldo + n] =
+                    __fmul_rn(static_cast<float>(static_cast<int>(z[j]) + bias_now), scale);
+            }
+            continue;
+          }
           int c[16];
           bool fast = true;
           if (CHECKED) {
@@ -668,7 +685,7 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
           for (int g = 0; g < 4; ++g) packed[g] = pack4_sat_s8(c[4 * g], c[4 * g + 1], c[4 * g + 2], c[4 * g + 3]);
         }
-        store_chunk(Cfg::NCH - 1, packed);
+        if (MODE != 3) store_chunk(Cfg::NCH - 1, packed);
       };
       if (all_ok) process(std::true_type{});
       else process(std::false_type{});
@@ -863,6 +880,11 @@ extern "C" int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M
              fabs(epi->mult_id) < 65536.0)
       mode = 2;
   }
+  // LOGITS without a row remap: channels-on-lanes too (coalesced float rows; the tokens-on-lanes
+  // epilogue scatters one 4-byte store per lane per row)
+  if (epi->epilogue == IVIT_EPI_LOGITS && epi->group <= 0 && channels_on_lanes_enabled() &&
+      static_cast<int64_t>(M) * ldo + N < (1ll << 31))
+    return launch_cl<192, 3, false>(A, lda, W, args, st);
   const bool checked = epi->z_bound_ok == 0;
   // Hot shapes: channels-on-lanes kernel (per-channel constants in registers).  Needs 4-byte
   // aligned output / identity rows and no row remap.

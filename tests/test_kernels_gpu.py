@@ -246,8 +246,9 @@ def test_gemm_patch_embed_remap():
     _gemm_case(196 * 3, 192, 768, seed=4, epilogue=_cabi.EPI_RESIDUAL, group=196)
 
 
-def test_gemm_logits():
-    _gemm_case(130, 1000, 384, seed=5, epilogue=_cabi.EPI_LOGITS)
+@pytest.mark.parametrize("shape", [(130, 1000, 384), (256, 1000, 384), (500, 10, 192), (193, 129, 64)])
+def test_gemm_logits(shape):
+    _gemm_case(*shape, seed=5, epilogue=_cabi.EPI_LOGITS)
 
 
 def _attention_case(kind, B, N, H, seed, s_qkv=0.05, a_max=None):
