@@ -140,8 +140,10 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = warp >> 2;                  // which of the row's TPR threads
   const int quarter = warp & 3;             // TMEM lane quarter
-  const int mt = blockIdx.x;
-  const int b = blockIdx.y / a.H, h = blockIdx.y % a.H;
+  // grid (image*head, query tile): every full 128-query tile is dispatched before the ragged last
+  // tiles (69 of 197 rows), so the short CTAs fill the tail of the launch
+  const int mt = blockIdx.y;
+  const int b = blockIdx.x / a.H, h = blockIdx.x % a.H;
   const int C = a.H * HD;
   const int N = a.N;
 
@@ -336,7 +338,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         w[j >> 2] |= pc << (8 * (j & 3));
       }
       if (TAP && a.probs != nullptr && row < N) {
-        uint8_t* pr = a.probs + ((static_cast<long long>(blockIdx.y) * N + row) * N) + ci * 32 + cbase;
+        uint8_t* pr = a.probs + ((static_cast<long long>(blockIdx.x) * N + row) * N) + ci * 32 + cbase;
         for (int j = 0; j < W && ci * 32 + cbase + j < N; ++j) pr[j] = static_cast<uint8_t>(w[j >> 2] >> (8 * (j & 3)));
       }
       store_p(ci, w);
@@ -447,7 +449,7 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
   auto launch = [&](auto kernel) -> int {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
-    dim3 grid((N + 127) / 128, B * H);
+    dim3 grid(B * H, (N + 127) / 128);
     kernel<<<grid, 128 * tpr, smem, st>>>(tq, tk, tv, a);
     return 0;
   };
