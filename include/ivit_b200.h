@@ -77,6 +77,19 @@ int ivit_requant_i8_i8(const int8_t* z, const float* s_in, const double* mult, i
 int ivit_dequant_i8_f32(const int8_t* q, float scale, float* out, int64_t n, void* stream);
 int ivit_fill_cls_rows_i8(int8_t* out, const int8_t* cls_row, int B, int N, int C, void* stream);
 
+/* ---- 16-bit activation locations (vit_quant.py:180-187 `*_bw = 16`; scripts/inference.py:297 --bitwidth 16)
+ * The residual stream then carries int16 codes.  Same LayerNorm + QuantAct as above on int16 rows
+ * (row stride ldx in ELEMENTS; the int32 square of ivit_modules.py:41 wraps as in the reference),
+ * the class-token row fill, and the stand-alone QuantAct over any of int32 / int16 / int8 inputs
+ * (z_bits), int8 / int16 identity (id_bits) and int8 / int16 output (out_bits). */
+int ivit_layernorm_requant_i16_i8(int kind, const int16_t* x, int64_t ldx, int8_t* out, int rows, int C, float s_in,
+                                  const float* bias_int, const float* sf, const double* mult, int qmin, int qmax,
+                                  float shift, int use_int_sqrt, void* stream);
+int ivit_fill_cls_rows_i16(int16_t* out, const int16_t* cls_row, int B, int N, int C, void* stream);
+int ivit_requant_codes(const void* z, int z_bits, const float* s_in, const double* mult, int per_channel,
+                       const void* identity, int id_bits, int64_t id_rows, double mult_id, void* out, int out_bits,
+                       int64_t rows, int C, int qmin, int qmax, void* stream);
+
 /* ---- QuantLinear / QuantConv2d(im2col) GEMM with fused QuantAct epilogues ---------------
  * quant_modules.py:186-226 (QuantLinear.forward: F.linear on integer-valued floats) and the
  * QuantAct(s) that follow it in vit_quant.py / layers_quant.py.  tcgen05 kind::i8 MMA, INT32
@@ -114,6 +127,11 @@ typedef struct {
   int force_slow;            /* 1: always take the general requant path (|mult| >= 256 or huge codes) */
   int z_bound_ok;            /* 1: caller proved |acc + bias| < 2^22 for every output (weights-only bound):
                               * the epilogue skips its per-element range check */
+  /* 16-bit activation locations (vit_quant.py:180-187 *_bw = 16; quant_utils.py:247-251 clamp for k = 16):
+   * out_bits 16 -> REQUANT / RESIDUAL store int16 codes (ldo in int16 elements); id_bits 16 -> the
+   * RESIDUAL identity is int16 (ld_id in int16 elements).  0 or 8 = int8.  RESIDUAL's first clamp
+   * (qmin, qmax) may then be a 16-bit range too (attention_out_bw / mlp_out_bw / patch_embed_bw). */
+  int out_bits, id_bits;
 } ivit_gemm_epilogue_t;
 int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M, int N, int K, void* out, int64_t ldo,
                  const ivit_gemm_epilogue_t* epi, void* stream);
@@ -133,7 +151,8 @@ int ivit_gemm_i8_simple(const int8_t* A, int64_t lda, const int8_t* W, int M, in
  * qkv int8 [B, N, 3, H, hd] (the layout QuantLinear(qkv)+qact1 produce); out int8 [B, N, H*hd]. */
 typedef struct {
   int kind;                  /* 0 ivit, 1 ibert */
-  int output_bit;            /* softmax output bits (8) */
+  int output_bit;            /* softmax output bits: 8, or 16 (softmax_bw = 16: codes up to 32768, u16 operand
+                              * split into two u8 planes, two MMAs) */
   double mult_attn;          /* qact_attn1: m*2^-e of (s_q*s_k*scale)/s_attn */
   int qmin_attn, qmax_attn;
   float s_attn;              /* scale of qact_attn1 output = softmax input */
@@ -149,6 +168,10 @@ typedef struct {
    * [row-max code - code]; only valid when that call reported the 2-D table collapsible.  Takes
    * precedence over exp_table (the kernel keeps 16 copies in shared memory instead of gathering). */
   const float* exp_table_1d;
+  /* output_bit 16 only: float32 scale of the P.V accumulator (s_softmax * s_v, quant_modules.py:409);
+   * |acc| reaches 8e8 there, so attn.qact2 replays the float32 recovery round(fl32(acc*s)/s)
+   * (quant_utils.py:220) before the dyadic multiply. */
+  float s_pv;
 } ivit_attention_params_t;
 /* The integer-exp term of IntSoftmax depends only on (code, row-max code) of qact_attn1's int8
  * output: tabulate it once per frozen layer with the kernel's own arithmetic. */
@@ -162,7 +185,8 @@ int ivit_attention_i8(const int8_t* qkv, int8_t* out, int B, int N, int H, int h
 /* The kernel runs 2 or 4 threads per query row (8 or 16 warps per CTA; default 2).  Returns the
  * previous setting; other values are ignored.  Process-wide; for A/B timing and tests. */
 int ivit_attention_set_threads_per_row(int tpr);
-/* Debug taps of the same kernel: softmax codes [B,H,N,N] uint8 (what int_softmax emits). */
+/* Debug taps of the same kernel: softmax codes [B,H,N,N] (what int_softmax emits): uint8, or
+ * uint16 when output_bit = 16 (`probs` then points to uint16 storage). */
 int ivit_attention_probs_i8(const int8_t* qkv, uint8_t* probs, int B, int N, int H, int hd,
                             const ivit_attention_params_t* p, void* stream);
 

@@ -32,6 +32,7 @@ class GemmEpilogue(C.Structure):
         ("group", C.c_int), ("out_group_stride", C.c_int), ("out_row_off", C.c_int), ("id_broadcast", C.c_int),
         ("force_slow", C.c_int),
         ("z_bound_ok", C.c_int),
+        ("out_bits", C.c_int), ("id_bits", C.c_int),
     ]
 
 
@@ -48,6 +49,7 @@ class AttentionParams(C.Structure):
         ("s_exp16", C.c_float),
         ("exp_table", C.c_void_p),
         ("exp_table_1d", C.c_void_p),
+        ("s_pv", C.c_float),
     ]
 
 
@@ -71,6 +73,13 @@ _SIGS = {
                                      C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "ivit_dequant_i8_f32": (C.c_int, [C.c_void_p, C.c_float, C.c_void_p, C.c_int64, C.c_void_p]),
     "ivit_fill_cls_rows_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "ivit_layernorm_requant_i16_i8": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_float,
+                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
+                                                C.c_int, C.c_void_p]),
+    "ivit_fill_cls_rows_i16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "ivit_requant_codes": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
+                                     C.c_int64, C.c_double, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int,
+                                     C.c_void_p]),
     "ivit_gemm_i8": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                C.c_int64, C.POINTER(GemmEpilogue), C.c_void_p]),
     "ivit_gemm_set_layout": (C.c_int, [C.c_int]),

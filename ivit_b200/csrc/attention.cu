@@ -28,7 +28,8 @@ struct AttnArgs {
   int NKP;        // N rounded up to 16: columns of S (MMA1 N)
   int KP2;        // N rounded up to 32: K extent of P.V
   int8_t* out;
-  uint8_t* probs;  // optional debug tap [B,H,N,N]
+  uint8_t* probs;  // optional debug tap [B,H,N,N] (uint8, or uint16 for a 16-bit softmax)
+  float s_pv;      // 16-bit softmax: float32 scale of the P.V accumulator (s_softmax * s_v)
   const float* exp_table;  // optional [256][256]: softmax_term(c, cmax) tabulated (bit-identical)
   const float* exp_table_1d;   // optional [256]: the same over cmax - c, when the 2-D table collapses
   ivit_attention_params_t p;
@@ -118,8 +119,13 @@ __device__ __forceinline__ void chunk_pipeline(uint32_t t_row, int n, F&& body) 
 // (row max, code) table (32 sectors per warp load); TABLE 2: from the 256-entry (row max - code)
 // table replicated 16x in shared memory (copy lane % 16: at most 2 lanes per bank); TABLE 0:
 // computed.  TAP: also dump the softmax codes (tests).
-template <int TPR, int TABLE, bool TAP>
-__global__ void __launch_bounds__(128 * TPR, 2)
+// P16: 16-bit softmax output (softmax_bw = 16; codes up to 32767, I-BERT 32768): the u16 operand is
+// split into two u8 planes P = 256 Phi + Plo, each its own SWIZZLE_128B tile and its own MMA into
+// its own TMEM accumulator (O_lo columns [0,64), O_hi [64,128), both over the dead score tile);
+// O = 256 O_hi + O_lo reaches 8e8, so attn.qact2 takes the general requant path that replays the
+// float32 carrier of the reference (requant_any).  One CTA per SM (the two planes double sP).
+template <int TPR, int TABLE, bool TAP, bool P16 = false>
+__global__ void __launch_bounds__(128 * TPR, P16 ? 1 : 2)
 attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
   constexpr int W = 32 / TPR;               // columns per thread per 32-column chunk
@@ -127,7 +133,8 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sP = smem;                       // 2 x [128 rows x 128 B], SWIZZLE_128B (written by threads)
-  uint8_t* sQ = smem + 32768;               // [128 x 64 B]  SWIZZLE_64B (TMA)
+  constexpr int P_BYTES = P16 ? 65536 : 32768;   // P16: low-byte plane, then high-byte plane
+  uint8_t* sQ = smem + P_BYTES;             // [128 x 64 B]  SWIZZLE_64B (TMA)
   uint8_t* sK = sQ + 8192;                  // [<=256 x 64 B]
   uint8_t* sV = sK + 16384;                 // [<=256 x 64 B]
   float* sAcc = reinterpret_cast<float*>(sV + 16384);          // [32][128] accumulators of threads q > 0 -> thread 0
@@ -317,36 +324,46 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   // pass 3: probabilities -> u8 operand tile in shared memory (K-major, SWIZZLE_128B)
   if (warp_active) {
     const float fs = sFac[r_loc];
-    auto store_p = [&](int ci, const uint32_t (&w)[W / 4]) {
+    auto store_p = [&](uint8_t* plane, int ci, const uint32_t (&w)[W / 4]) {
       // W bytes inside one 16-byte unit of this row's 128-byte swizzle line
       const int col = ci * 32 + cbase;
-      uint8_t* base = sP + (col >> 7) * 16384 + (r_loc >> 3) * 1024 + (r_loc & 7) * 128;
+      uint8_t* base = plane + (col >> 7) * 16384 + (r_loc >> 3) * 1024 + (r_loc & 7) * 128;
       const int u0 = (col & 127) >> 4;
       uint8_t* dst = base + ((u0 ^ (r_loc & 7)) << 4) + (col & 15);
       if (W == 16) *reinterpret_cast<int4*>(dst) = make_int4(w[0], w[1], w[W / 4 - 2], w[W / 4 - 1]);
       else *reinterpret_cast<uint2*>(dst) = make_uint2(w[0], w[1]);
     };
     chunk_pipeline<W>(t_row, my_chunks, [&](int ci, uint32_t (&v)[W]) {
-      uint32_t w[W / 4];
+      uint32_t w[W / 4], wh[W / 4];
 #pragma unroll
-      for (int j = 0; j < W / 4; ++j) w[j] = 0;
+      for (int j = 0; j < W / 4; ++j) w[j] = wh[j] = 0;
 #pragma unroll
       for (int j = 0; j < W; ++j) {
         // :175 / :315 (terms past column N were stored as 0).  floor of a value in [0, 2^22) through
         // the 2^23 magic constant (round toward zero) instead of F2I (quarter-rate XU pipe)
-        const uint32_t pc = __float_as_uint(__fadd_rz(__fmul_rn(__uint_as_float(v[j]), fs), 8388608.f)) & 0xffu;
-        w[j >> 2] |= pc << (8 * (j & 3));
+        const uint32_t pc = __float_as_uint(__fadd_rz(__fmul_rn(__uint_as_float(v[j]), fs), 8388608.f)) &
+                            (P16 ? 0x1ffffu : 0xffu);
+        w[j >> 2] |= (pc & 0xffu) << (8 * (j & 3));
+        if (P16) wh[j >> 2] |= (pc >> 8) << (8 * (j & 3));
       }
       if (TAP && a.probs != nullptr && row < N) {
-        uint8_t* pr = a.probs + ((static_cast<long long>(blockIdx.x) * N + row) * N) + ci * 32 + cbase;
-        for (int j = 0; j < W && ci * 32 + cbase + j < N; ++j) pr[j] = static_cast<uint8_t>(w[j >> 2] >> (8 * (j & 3)));
+        const long long po = ((static_cast<long long>(blockIdx.x) * N + row) * N) + ci * 32 + cbase;
+        for (int j = 0; j < W && ci * 32 + cbase + j < N; ++j) {
+          const uint32_t lo = (w[j >> 2] >> (8 * (j & 3))) & 0xffu, hi = (wh[j >> 2] >> (8 * (j & 3))) & 0xffu;
+          if (P16) reinterpret_cast<uint16_t*>(a.probs)[po + j] = static_cast<uint16_t>(lo | (hi << 8));
+          else a.probs[po + j] = static_cast<uint8_t>(lo);
+        }
       }
-      store_p(ci, w);
+      store_p(sP, ci, w);
+      if (P16) store_p(sP + 32768, ci, wh);
     });
     uint32_t zero[W / 4];
 #pragma unroll
     for (int j = 0; j < W / 4; ++j) zero[j] = 0;
-    for (int ci = my_chunks; ci < pchunks; ++ci) store_p(ci, zero);   // K padding of the P V product
+    for (int ci = my_chunks; ci < pchunks; ++ci) {   // K padding of the P V product
+      store_p(sP, ci, zero);
+      if (P16) store_p(sP + 32768, ci, zero);
+    }
   }
   fence_proxy_async_smem();     // generic-proxy smem writes -> visible to tcgen05.mma
   tc_fence_before();
@@ -358,12 +375,14 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     tc_fence_after();
     const uint32_t idesc2 = make_idesc_i8(128, HD, false, true, false, true);   // A u8 K-major, B s8 MN-major
     const int ksteps = a.KP2 / 32;
-    for (int k = 0; k < ksteps; ++k) {
-      const uint32_t pa = smem_u32(sP) + (k >> 2) * 16384 + (k & 3) * 32;
-      const uint64_t da = make_smem_desc(pa, 16, 1024, kLayoutSW128);
-      // V tile [token][64 B]: MN-major, one 64-byte swizzle atom wide, 8-token groups 512 B apart
-      const uint64_t db = make_smem_desc(smem_u32(sV) + k * 32 * HD, 512, 512, kLayoutSW64);
-      mma_i8_ss(tmem_base, da, db, idesc2, k != 0 ? 1u : 0u);
+    for (int pl = 0; pl < (P16 ? 2 : 1); ++pl) {
+      for (int k = 0; k < ksteps; ++k) {
+        const uint32_t pa = smem_u32(sP) + pl * 32768 + (k >> 2) * 16384 + (k & 3) * 32;
+        const uint64_t da = make_smem_desc(pa, 16, 1024, kLayoutSW128);
+        // V tile [token][64 B]: MN-major, one 64-byte swizzle atom wide, 8-token groups 512 B apart
+        const uint64_t db = make_smem_desc(smem_u32(sV) + k * 32 * HD, 512, 512, kLayoutSW64);
+        mma_i8_ss(tmem_base + pl * HD, da, db, idesc2, k != 0 ? 1u : 0u);
+      }
     }
     tc_commit(&bars[3]);
   }
@@ -375,6 +394,13 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     // warp-collective (.sync.aligned): it must stay outside the per-lane row guard.
     uint32_t o[OW];
     tmem_ld_w(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + q * OW, o);
+    if (P16) {
+      uint32_t oh[OW];
+      tmem_ld_w(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + HD + q * OW, oh);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < OW; ++j) o[j] += oh[j] << 8;          // O = 256 O_hi + O_lo  (< 2^31)
+    }
     tmem_ld_wait();
     if (row < N && a.out != nullptr) {
       uint32_t w[OW / 4];
@@ -382,7 +408,13 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       for (int j = 0; j < OW / 4; ++j) w[j] = 0;
 #pragma unroll
       for (int j = 0; j < OW; ++j) {
-        const int c = clampi(requant_i32_fast(static_cast<int>(o[j]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
+        int c;
+        if (P16) {
+          const double r = requant_any(static_cast<int>(o[j]), a.s_pv, a.p.mult_out);
+          c = static_cast<int>(fmin(fmax(r, static_cast<double>(a.p.qmin_out)), static_cast<double>(a.p.qmax_out)));
+        } else {
+          c = clampi(requant_i32_fast(static_cast<int>(o[j]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
+        }
         w[j >> 2] |= (static_cast<uint32_t>(c) & 0xffu) << (8 * (j & 3));
       }
       int8_t* op = a.out + (static_cast<long long>(b) * N + row) * C + h * HD + q * OW;
@@ -426,7 +458,10 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
   if (!p) return fail(IVIT_ERR_BAD_ARG, "attention: params NULL");
   if (hd != HD) return fail(IVIT_ERR_UNSUPPORTED, "attention: head_dim must be 64");
   if (N < 1 || N > 256) return fail(IVIT_ERR_UNSUPPORTED, "attention: 1 <= N <= 256 tokens");
-  if (p->output_bit != 8) return fail(IVIT_ERR_UNSUPPORTED, "attention: 8-bit softmax output only");
+  if (p->output_bit < 2 || p->output_bit > 16)
+    return fail(IVIT_ERR_UNSUPPORTED, "attention: softmax output_bit must be in [2, 16]");
+  const bool p16 = p->output_bit > 8;
+  if (p16 && !(p->s_pv > 0.f)) return fail(IVIT_ERR_BAD_ARG, "attention: s_pv (scale of the P.V accumulator) required at 16 bit");
   if (B * H <= 0) return 0;
   AttnArgs a;
   a.B = B; a.N = N; a.H = H;
@@ -434,6 +469,7 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
   a.KP2 = (N + 31) / 32 * 32;
   a.out = out; a.probs = probs; a.exp_table = p->exp_table; a.exp_table_1d = p->exp_table_1d;
   derive_softmax_consts(a, p);
+  a.s_pv = p->s_pv;
   const int C = H * hd;
   CUtensorMap tq, tk, tv;
   int rc;
@@ -443,9 +479,9 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
   if ((rc = make_tmap_2d_u8(&tv, qkv, cols, rows, cols, HD, a.KP2, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   const int table = a.exp_table_1d != nullptr ? 2 : (a.exp_table != nullptr ? 1 : 0);
   const bool tap = probs != nullptr;
-  const size_t smem = 1024 + 32768 + 8192 + 16384 + 16384 + 32 * 128 * 4 + 512 * 4 + 128 * 4 + 64 +
+  const size_t smem = 1024 + (p16 ? 65536 : 32768) + 8192 + 16384 + 16384 + 32 * 128 * 4 + 512 * 4 + 128 * 4 + 64 +
                       (table == 2 ? 256 * 16 * 4 : 0);
-  const int tpr = g_attn_tpr;
+  const int tpr = p16 ? 2 : g_attn_tpr;
   auto launch = [&](auto kernel) -> int {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
@@ -453,7 +489,11 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
     kernel<<<grid, 128 * tpr, smem, st>>>(tq, tk, tv, a);
     return 0;
   };
-  if (tpr == 4) {
+  if (p16) {
+    if (table == 2) rc = tap ? launch(attention_i8_kernel<2, 2, true, true>) : launch(attention_i8_kernel<2, 2, false, true>);
+    else if (table == 1) rc = tap ? launch(attention_i8_kernel<2, 1, true, true>) : launch(attention_i8_kernel<2, 1, false, true>);
+    else rc = tap ? launch(attention_i8_kernel<2, 0, true, true>) : launch(attention_i8_kernel<2, 0, false, true>);
+  } else if (tpr == 4) {
     if (table == 2) rc = tap ? launch(attention_i8_kernel<4, 2, true>) : launch(attention_i8_kernel<4, 2, false>);
     else if (table == 1) rc = tap ? launch(attention_i8_kernel<4, 1, true>) : launch(attention_i8_kernel<4, 1, false>);
     else rc = tap ? launch(attention_i8_kernel<4, 0, true>) : launch(attention_i8_kernel<4, 0, false>);

@@ -142,20 +142,40 @@ __device__ __noinline__ void epilogue_chunk_generic(const uint32_t (&acc)[16], c
     for (int j = 0; j < 16; ++j) c[j] = (nb + j < args.N) ? epi_requant_elem(z[j], nb + j, e) : 0;
   }
   if (e.epilogue == IVIT_EPI_RESIDUAL) {
-    uint32_t idw[4] = {0, 0, 0, 0};
+    int idv[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) idv[j] = 0;
     if (row_ok) {
-      const int8_t* ip = e.identity + irow * e.ld_id + nb;
-      if (full_chunk) {
-        const int4 a = __ldg(reinterpret_cast<const int4*>(ip));
-        idw[0] = a.x; idw[1] = a.y; idw[2] = a.z; idw[3] = a.w;
+      if (e.id_bits == 16) {               // 16-bit residual stream: identity int16, ld_id in elements
+        const int16_t* ip = reinterpret_cast<const int16_t*>(e.identity) + irow * e.ld_id + nb;
+        if (full_chunk && (reinterpret_cast<uintptr_t>(ip) & 15) == 0) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int4 a = __ldg(reinterpret_cast<const int4*>(ip) + h);
+            const uint32_t w4[4] = {static_cast<uint32_t>(a.x), static_cast<uint32_t>(a.y), static_cast<uint32_t>(a.z),
+                                    static_cast<uint32_t>(a.w)};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) idv[8 * h + j] = static_cast<int16_t>(w4[j >> 1] >> (16 * (j & 1)));
+          }
+        } else {
+          for (int j = 0; j < 16 && nb + j < args.N; ++j) idv[j] = ip[j];
+        }
       } else {
-        for (int j = 0; j < 16 && nb + j < args.N; ++j)
-          idw[j >> 2] |= static_cast<uint32_t>(static_cast<uint8_t>(ip[j])) << (8 * (j & 3));
+        const int8_t* ip = e.identity + irow * e.ld_id + nb;
+        if (full_chunk && (reinterpret_cast<uintptr_t>(ip) & 15) == 0) {
+          const int4 a = __ldg(reinterpret_cast<const int4*>(ip));
+          const uint32_t w4[4] = {static_cast<uint32_t>(a.x), static_cast<uint32_t>(a.y), static_cast<uint32_t>(a.z),
+                                  static_cast<uint32_t>(a.w)};
+#pragma unroll
+          for (int j = 0; j < 16; ++j) idv[j] = static_cast<int8_t>(w4[j >> 2] >> (8 * (j & 3)));
+        } else {
+          for (int j = 0; j < 16 && nb + j < args.N; ++j) idv[j] = ip[j];
+        }
       }
     }
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-      const int id = static_cast<int8_t>(idw[j >> 2] >> (8 * (j & 3)));
+      const int id = idv[j];
       // second fixedpoint_mul (scalar ratio) + identity branch, rounded separately then added
       if (args.allow_fast) {
         c[j] = clampi(requant_i32_fast(c[j], e.mult2) + requant_i32_fast(id, e.mult_id), e.qmin2, e.qmax2);
@@ -164,9 +184,25 @@ __device__ __noinline__ void epilogue_chunk_generic(const uint32_t (&acc)[16], c
       }
     }
   }
+  if (row_ok && e.out_bits == 16) {        // 16-bit activation location: int16 codes, ldo in elements
+    int16_t* o = static_cast<int16_t*>(args.out) + orow * args.ldo + nb;
+    if (full_chunk && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint32_t w[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          w[j] = (static_cast<uint32_t>(c[8 * h + 2 * j]) & 0xffffu) | (static_cast<uint32_t>(c[8 * h + 2 * j + 1]) << 16);
+        reinterpret_cast<int4*>(o)[h] = make_int4(w[0], w[1], w[2], w[3]);
+      }
+    } else {
+      for (int j = 0; j < 16 && nb + j < args.N; ++j) o[j] = static_cast<int16_t>(c[j]);
+    }
+    return;
+  }
   if (row_ok) {
     int8_t* o = static_cast<int8_t*>(args.out) + orow * args.ldo + nb;
-    if (full_chunk) {
+    if (full_chunk && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
       uint32_t w[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j)
@@ -721,8 +757,14 @@ __global__ void gemm_i8_simple_kernel(const int8_t* __restrict__ A, long long ld
       static_cast<float*>(args.out)[orow * args.ldo + n] = __fmul_rn(static_cast<float>(z), e.scale_out[n]);
     } else {
       int c = epi_requant_elem(z, n, e);
-      if (e.epilogue == IVIT_EPI_RESIDUAL) c = epi_residual_elem(c, e.identity[id_row_of(r, e) * e.ld_id + n], e);
-      static_cast<int8_t*>(args.out)[orow * args.ldo + n] = static_cast<int8_t>(c);
+      if (e.epilogue == IVIT_EPI_RESIDUAL) {
+        const long long io = id_row_of(r, e) * e.ld_id + n;
+        const int id = e.id_bits == 16 ? static_cast<int>(reinterpret_cast<const int16_t*>(e.identity)[io])
+                                       : static_cast<int>(e.identity[io]);
+        c = epi_residual_elem(c, id, e);
+      }
+      if (e.out_bits == 16) static_cast<int16_t*>(args.out)[orow * args.ldo + n] = static_cast<int16_t>(c);
+      else static_cast<int8_t*>(args.out)[orow * args.ldo + n] = static_cast<int8_t>(c);
     }
   }
 }
@@ -774,10 +816,19 @@ static int fill_args(GemmArgs& a, int M, int N, int K, void* out, int64_t ldo, c
     return fail(IVIT_ERR_BAD_ARG, "gemm: mult / s_in required for requant epilogues");
   if (epi->epilogue == IVIT_EPI_RESIDUAL && !epi->identity) return fail(IVIT_ERR_BAD_ARG, "gemm: identity is NULL");
   if (epi->epilogue == IVIT_EPI_LOGITS && !epi->scale_out) return fail(IVIT_ERR_BAD_ARG, "gemm: scale_out is NULL");
+  if (epi->out_bits != 0 && epi->out_bits != 8 && epi->out_bits != 16)
+    return fail(IVIT_ERR_BAD_ARG, "gemm: out_bits must be 0/8 or 16");
+  if (epi->id_bits != 0 && epi->id_bits != 8 && epi->id_bits != 16)
+    return fail(IVIT_ERR_BAD_ARG, "gemm: id_bits must be 0/8 or 16");
   if (epi->epilogue == IVIT_EPI_REQUANT || epi->epilogue == IVIT_EPI_RESIDUAL) {
-    if (epi->qmin < -128 || epi->qmax > 127) return fail(IVIT_ERR_UNSUPPORTED, "gemm: int8 outputs only");
-    if (epi->epilogue == IVIT_EPI_RESIDUAL && (epi->qmin2 < -128 || epi->qmax2 > 127))
-      return fail(IVIT_ERR_UNSUPPORTED, "gemm: int8 outputs only");
+    // the stored codes must fit the output type; RESIDUAL's first clamp (qmin, qmax) is an in-register
+    // intermediate of up to 16 bits
+    const int lim = epi->out_bits == 16 ? 32768 : 128;
+    const bool res = epi->epilogue == IVIT_EPI_RESIDUAL;
+    const int lo = res ? epi->qmin2 : epi->qmin, hi = res ? epi->qmax2 : epi->qmax;
+    if (lo < -lim || hi > lim - 1) return fail(IVIT_ERR_UNSUPPORTED, "gemm: output clamp range exceeds the output type");
+    if (res && (epi->qmin < -32768 || epi->qmax > 32767))
+      return fail(IVIT_ERR_UNSUPPORTED, "gemm: intermediate clamp range exceeds 16 bits");
   }
   return 0;
 }
@@ -872,7 +923,8 @@ extern "C" int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M
   // sum_k |W[n,k]| * 128 + |bias| bound) or checked per chunk with the general path behind it.
   int mode = 0;
   const bool req = epi->epilogue == IVIT_EPI_REQUANT, res = epi->epilogue == IVIT_EPI_RESIDUAL;
-  if ((req || res) && args.allow_fast && epi->qmin == -128 && epi->qmax == 127 && ldo % 16 == 0 &&
+  const bool wide = epi->out_bits == 16 || (res && epi->id_bits == 16);
+  if (!wide && (req || res) && args.allow_fast && epi->qmin == -128 && epi->qmax == 127 && ldo % 16 == 0 &&
       (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
     if (req) mode = 1;
     else if (epi->qmin2 == -128 && epi->qmax2 == 127 && epi->ld_id % 16 == 0 &&

@@ -1,0 +1,225 @@
+// Row-wise kernels for the 16-bit activation locations (vit_quant.py:180-187 `*_bw = 16`, the
+// `--bitwidth 16` sweep of scripts/inference.py:297): the residual stream then carries int16 codes.
+//
+//   * IntLayerNorm (I-ViT ivit_modules.py:30-65 / I-BERT ibert_modules.py:112-158) on int16 rows,
+//     fused with the 8-bit QuantAct that follows it (Block.qact1 / qact3, final qact2).
+//   * class-token row fill and the stand-alone QuantAct with 16-bit inputs / identities / outputs.
+//
+// With 16-bit codes the shortcuts of the int8 kernels (rowwise.cu) no longer hold: x/s is off an
+// integer by up to 2^-9 per element, so the float32 row sum is replayed in torch's CPU order for
+// EVERY row (not just exact ties), and |y| exceeds 46340, so the int32 square wraps (hazard H9)
+// exactly as `y_int ** 2` does in the reference.  One warp per row; lane t owns elements 32 i + t
+// (torch's accumulator layout, intmath.cuh TorchSum32).
+#include "intmath.cuh"
+#include "ivit_b200.h"
+
+namespace ivit {
+int fail(int code, const char* msg);
+int check_launch(const char* what);
+
+// exact replay of the QuantAct behind the LayerNorm for one element (quant_utils.py:220-251)
+__device__ __forceinline__ int ln16_requant(float v, float sc, double mult, int qmin, int qmax) {
+  const float xo = __fmul_rn(v, sc);
+  const float z = rintf(__fdiv_rn(xo, sc));
+  const double rd = requant_d(static_cast<double>(z), mult);
+  return static_cast<int>(fmin(fmax(rd, static_cast<double>(qmin)), static_cast<double>(qmax)));
+}
+
+// kind 0: I-ViT, kind 1: I-BERT.  x int16 [rows, C] with row stride ldx ELEMENTS; out int8 [rows, C].
+template <int NPL>
+__global__ void __launch_bounds__(256)
+layernorm_x16_requant_kernel(int kind, const int16_t* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows,
+                             float s_in, const float* __restrict__ bias_int, const float* __restrict__ sf,
+                             const double* __restrict__ mult, int qmin, int qmax, float shift_pow, float inv_shift_pow,
+                             int use_int_sqrt) {
+  constexpr int C = NPL * 32;
+  __shared__ __align__(16) int8_t stage[8][C];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= rows) return;
+  const int16_t* xr = x + static_cast<long long>(row) * ldx;
+  float xe[NPL];
+  TorchSum32 acc;
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) {
+    xe[i] = x_eff(static_cast<float>(__ldg(xr + 32 * i + lane)), s_in);       // ivit :36 / ibert :129
+    acc.add(xe[i]);
+  }
+  const float sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+  const float mean = rintf(__fdiv_rn(sum_f, static_cast<float>(C)));          // ivit :37 / ibert :130
+  float y[NPL];
+  float factor;
+  if (kind == 0) {
+    const int mean_i = static_cast<int>(mean);
+    long long var = 0;
+#pragma unroll
+    for (int i = 0; i < NPL; ++i) {
+      const int yi = static_cast<int>(xe[i]) - mean_i;                        // :38 trunc, :40
+      const int sq = static_cast<int>(static_cast<uint32_t>(yi) * static_cast<uint32_t>(yi));   // :41 int32 wrap (H9)
+      var += static_cast<long long>(sq);                                      // :42 int64 sum
+      y[i] = static_cast<float>(yi);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) var += __shfl_xor_sync(0xffffffffu, var, o);
+    const float var_f = static_cast<float>(var);
+    float k = 65536.f;
+#pragma unroll
+    for (int it = 0; it < 10; ++it) k = floorf(__fmul_rn(__fadd_rn(k, floorf(__fdiv_rn(var_f, k))), 0.5f));   // :45-49
+    factor = floorf(__fdiv_rn(2147483648.f, k));                              // :51 (2^31-1 -> 2^31 in float32)
+  } else {
+    TorchSum32 vacc;
+#pragma unroll
+    for (int i = 0; i < NPL; ++i) {
+      y[i] = __fsub_rn(xe[i], mean);                                          // :131
+      const float ys = floorf(__fmul_rn(y[i], inv_shift_pow));                // :132
+      vacc.add(__fmul_rn(ys, ys));                                            // :133
+    }
+    const float var_f = torch_sum_finish(vacc.level_sum(), 0.f, nullptr, 0, lane);   // :134
+    float std_i;
+    if (use_int_sqrt) {                                                       // :85-109
+      const float n = fmaxf(var_f, 0.f);
+      const float bits = floorf(log2f(fmaxf(n, 1.f))) + 1.f;
+      float xk = pow2i(static_cast<int>(ceilf(__fmul_rn(bits, 0.5f))));
+      for (int it = 0; it < 4; ++it) {
+        const float inv = floorf(__fdiv_rn(n, fmaxf(xk, 1.f)));
+        xk = floorf(__fmul_rn(__fadd_rn(xk, inv), 0.5f));
+      }
+      std_i = (var_f > 0.f) ? xk : 0.f;
+    } else {
+      std_i = floorf(__fsqrt_rn(var_f));                                      // :145
+    }
+    std_i = __fmul_rn(std_i, shift_pow);
+    factor = floorf(__fdiv_rn(2147483648.f, std_i));                          // :146 (2^31)
+  }
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) {
+    const int c = 32 * i + lane;
+    float v = floorf(__fmul_rn(__fmul_rn(y[i], factor), 0.5f));               // ivit :52 / ibert :147
+    v = __fadd_rn(v, __ldg(bias_int + c));                                    // :61 / :154
+    stage[warp][c] = static_cast<int8_t>(ln16_requant(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax));
+  }
+  __syncwarp();
+  int8_t* orow = out + static_cast<long long>(row) * C;
+  for (int v = lane; v < C / 16; v += 32)
+    *reinterpret_cast<int4*>(orow + v * 16) = *reinterpret_cast<const int4*>(&stage[warp][v * 16]);
+}
+
+__global__ void fill_cls_rows16_kernel(int16_t* __restrict__ out, const int16_t* __restrict__ cls_row, int B, int N,
+                                       int C) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= B * C) return;
+  const int b = t / C, c = t % C;
+  out[(static_cast<long long>(b) * N) * C + c] = cls_row[c];
+}
+
+// Stand-alone QuantAct, any of int32 / int16 / int8 codes in, int8 / int16 identity, int8 / int16 out.
+template <typename ZT, typename IT, typename OT>
+__global__ void requant_any_kernel(const ZT* __restrict__ z, const float* __restrict__ s_in,
+                                   const double* __restrict__ mult, int per_channel, const IT* __restrict__ id,
+                                   long long id_rows, double mult_id, OT* __restrict__ out, long long rows, int C,
+                                   int qmin, int qmax) {
+  const long long n = rows * C;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < n;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = per_channel ? static_cast<int>(t % C) : 0;
+    double r = requant_any(static_cast<int>(z[t]), s_in[c], mult[c]);
+    if (id != nullptr) {
+      const long long it = (id_rows > 0 && id_rows < rows) ? ((t / C) % id_rows) * C + t % C : t;
+      r += requant_d(static_cast<double>(id[it]), mult_id);
+    }
+    out[t] = static_cast<OT>(static_cast<int>(fmin(fmax(r, (double)qmin), (double)qmax)));
+  }
+}
+
+template <typename ZT, typename IT, typename OT>
+static int launch_requant(const void* z, const float* s_in, const double* mult, int per_channel, const void* id,
+                          long long id_rows, double mult_id, void* out, long long rows, int C, int qmin, int qmax,
+                          cudaStream_t st) {
+  const long long n = rows * C;
+  long long g = (n + 255) / 256;
+  if (g > 148LL * 16) g = 148LL * 16;
+  requant_any_kernel<ZT, IT, OT><<<static_cast<int>(g), 256, 0, st>>>(
+      static_cast<const ZT*>(z), s_in, mult, per_channel, static_cast<const IT*>(id), id_rows, mult_id,
+      static_cast<OT*>(out), rows, C, qmin, qmax);
+  return check_launch("requant_any_kernel");
+}
+
+template <typename ZT>
+static int dispatch_requant(int id_bits, int out_bits, const void* z, const float* s_in, const double* mult,
+                            int per_channel, const void* id, long long id_rows, double mult_id, void* out,
+                            long long rows, int C, int qmin, int qmax, cudaStream_t st) {
+  if (out_bits == 16) {
+    if (id_bits == 16)
+      return launch_requant<ZT, int16_t, int16_t>(z, s_in, mult, per_channel, id, id_rows, mult_id, out, rows, C, qmin, qmax, st);
+    return launch_requant<ZT, int8_t, int16_t>(z, s_in, mult, per_channel, id, id_rows, mult_id, out, rows, C, qmin, qmax, st);
+  }
+  if (id_bits == 16)
+    return launch_requant<ZT, int16_t, int8_t>(z, s_in, mult, per_channel, id, id_rows, mult_id, out, rows, C, qmin, qmax, st);
+  return launch_requant<ZT, int8_t, int8_t>(z, s_in, mult, per_channel, id, id_rows, mult_id, out, rows, C, qmin, qmax, st);
+}
+
+}  // namespace ivit
+
+using namespace ivit;
+
+extern "C" int ivit_layernorm_requant_i16_i8(int kind, const int16_t* x, int64_t ldx, int8_t* out, int rows, int C,
+                                             float s_in, const float* bias_int, const float* sf, const double* mult,
+                                             int qmin, int qmax, float shift, int use_int_sqrt, void* stream) {
+  if (rows <= 0) return 0;
+  if (kind != 0 && kind != 1) return fail(IVIT_ERR_BAD_ARG, "layernorm16: kind must be 0 (ivit) or 1 (ibert)");
+  if (ldx < C) return fail(IVIT_ERR_BAD_ARG, "layernorm16: row stride (elements) must be >= C");
+  if (qmin < -128 || qmax > 127) return fail(IVIT_ERR_UNSUPPORTED, "layernorm16: int8 outputs only");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const float sp = ldexpf(1.f, static_cast<int>(shift));
+  const int grid = (rows + 7) / 8;
+#define IVIT_LN16_CASE(c)                                                                                       \
+  case c:                                                                                                       \
+    layernorm_x16_requant_kernel<c / 32><<<grid, 256, 0, st>>>(kind, x, ldx, out, rows, s_in, bias_int, sf, mult, \
+                                                               qmin, qmax, sp, 1.f / sp, use_int_sqrt);         \
+    break;
+  switch (C) {
+    IVIT_LN16_CASE(96)
+    IVIT_LN16_CASE(128)
+    IVIT_LN16_CASE(192)
+    IVIT_LN16_CASE(384)
+    IVIT_LN16_CASE(768)
+    IVIT_LN16_CASE(1024)
+    default:
+      return fail(IVIT_ERR_UNSUPPORTED, "layernorm16: C must be one of 96,128,192,384,768,1024");
+  }
+#undef IVIT_LN16_CASE
+  return check_launch("layernorm_x16_requant_kernel");
+}
+
+extern "C" int ivit_fill_cls_rows_i16(int16_t* out, const int16_t* cls_row, int B, int N, int C, void* stream) {
+  if (B * C <= 0) return 0;
+  fill_cls_rows16_kernel<<<(B * C + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(out, cls_row, B, N, C);
+  return check_launch("fill_cls_rows16_kernel");
+}
+
+extern "C" int ivit_requant_codes(const void* z, int z_bits, const float* s_in, const double* mult, int per_channel,
+                                  const void* identity, int id_bits, int64_t id_rows, double mult_id, void* out,
+                                  int out_bits, int64_t rows, int C, int qmin, int qmax, void* stream) {
+  const long long n = rows * C;
+  if (n <= 0) return 0;
+  if (identity != nullptr && id_rows > 0 && rows % id_rows != 0)
+    return fail(IVIT_ERR_BAD_ARG, "requant: id_rows must divide rows");
+  if ((out_bits != 8 && out_bits != 16) || (identity != nullptr && id_bits != 8 && id_bits != 16))
+    return fail(IVIT_ERR_BAD_ARG, "requant: out_bits / id_bits must be 8 or 16");
+  const int lim = out_bits == 16 ? 32768 : 128;
+  if (qmin < -lim || qmax > lim - 1) return fail(IVIT_ERR_UNSUPPORTED, "requant: clamp range exceeds the output type");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (z_bits) {
+    case 32:
+      return dispatch_requant<int32_t>(id_bits, out_bits, z, s_in, mult, per_channel, identity, id_rows, mult_id, out, rows,
+                                       C, qmin, qmax, st);
+    case 16:
+      return dispatch_requant<int16_t>(id_bits, out_bits, z, s_in, mult, per_channel, identity, id_rows, mult_id, out, rows,
+                                       C, qmin, qmax, st);
+    case 8:
+      return dispatch_requant<int8_t>(id_bits, out_bits, z, s_in, mult, per_channel, identity, id_rows, mult_id, out, rows,
+                                      C, qmin, qmax, st);
+    default:
+      return fail(IVIT_ERR_BAD_ARG, "requant: z_bits must be 8, 16 or 32");
+  }
+}

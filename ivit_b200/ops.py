@@ -41,17 +41,19 @@ def quantize_patches(x: torch.Tensor, inv_scale: float, patch: int, out: torch.T
 def layernorm_requant(kind: int, x: torch.Tensor, s_in: float, bias_int: torch.Tensor, sf: torch.Tensor,
                       mult: torch.Tensor, qmin: int, qmax: int, shift: float = 0.0,
                       use_int_sqrt: bool = False, out: torch.Tensor | None = None) -> torch.Tensor:
-    """x: int8 [..., C] (last dim contiguous, uniform row stride), e.g. a [B, C] view of the class rows."""
-    assert x.dtype == torch.int8 and x.stride(-1) == 1
+    """x: int8 (or int16: 16-bit residual stream) [..., C] (last dim contiguous, uniform row stride), e.g. a
+    [B, C] view of the class rows."""
+    assert x.dtype in (torch.int8, torch.int16) and x.stride(-1) == 1
     Cdim = x.shape[-1]
     rows = x.numel() // Cdim
     ldx = x.stride(-2) if x.dim() >= 2 else Cdim
     assert x.dim() <= 2 or x.is_contiguous()
     if out is None:
         out = torch.empty(x.shape, dtype=torch.int8, device=x.device)
-    check(_cabi.load().ivit_layernorm_requant_i8(kind, ptr(x), ldx, ptr(out), rows, Cdim, C.c_float(s_in), ptr(bias_int),
-                                                 ptr(sf), ptr(mult), qmin, qmax, C.c_float(shift),
-                                                 int(use_int_sqrt), stream()), "ivit_layernorm_requant_i8")
+    lib = _cabi.load()
+    fn = lib.ivit_layernorm_requant_i8 if x.dtype == torch.int8 else lib.ivit_layernorm_requant_i16_i8
+    check(fn(kind, ptr(x), ldx, ptr(out), rows, Cdim, C.c_float(s_in), ptr(bias_int), ptr(sf), ptr(mult), qmin, qmax,
+             C.c_float(shift), int(use_int_sqrt), stream()), "ivit_layernorm_requant")
     return out
 
 
@@ -80,22 +82,34 @@ def gelu_lut_apply(x: torch.Tensor, lut: torch.Tensor, out: torch.Tensor | None 
     return out
 
 
+_BITS = {torch.int8: 8, torch.int16: 16, torch.int32: 32}
+
+
 def requant(z: torch.Tensor, s_in: torch.Tensor, mult: torch.Tensor, qmin: int, qmax: int,
-            identity: torch.Tensor | None = None, mult_id: float = 0.0, out: torch.Tensor | None = None) -> torch.Tensor:
-    """Stand-alone QuantAct on int32 or int8 codes [..., C]; identity int8 [id_rows, C] broadcast over rows."""
-    assert z.dtype in (torch.int32, torch.int8) and z.is_contiguous()
+            identity: torch.Tensor | None = None, mult_id: float = 0.0, out: torch.Tensor | None = None,
+            out_bits: int = 8) -> torch.Tensor:
+    """Stand-alone QuantAct on int32 / int16 / int8 codes [..., C]; identity int8 or int16 [id_rows, C]
+    broadcast over rows; int8 codes out, or int16 for a 16-bit location (out_bits = 16)."""
+    assert z.dtype in _BITS and z.is_contiguous()
     Cdim = z.shape[-1]
     rows = z.numel() // Cdim
+    odt = torch.int16 if out_bits == 16 else torch.int8
     if out is None:
-        out = torch.empty(z.shape, dtype=torch.int8, device=z.device)
+        out = torch.empty(z.shape, dtype=odt, device=z.device)
+    assert out.dtype == odt and out.is_contiguous()
     id_rows = 0
     if identity is not None:
-        assert identity.dtype == torch.int8 and identity.is_contiguous() and identity.shape[-1] == Cdim
+        assert identity.dtype in (torch.int8, torch.int16) and identity.is_contiguous() and identity.shape[-1] == Cdim
         id_rows = identity.numel() // Cdim
     lib = _cabi.load()
-    fn = lib.ivit_requant_i32_i8 if z.dtype == torch.int32 else lib.ivit_requant_i8_i8
-    check(fn(ptr(z), ptr(s_in), ptr(mult), int(mult.numel() > 1), ptr(identity), id_rows, C.c_double(mult_id),
-             ptr(out), rows, Cdim, qmin, qmax, stream()), "ivit_requant")
+    if z.dtype != torch.int16 and out_bits == 8 and (identity is None or identity.dtype == torch.int8):
+        fn = lib.ivit_requant_i32_i8 if z.dtype == torch.int32 else lib.ivit_requant_i8_i8
+        check(fn(ptr(z), ptr(s_in), ptr(mult), int(mult.numel() > 1), ptr(identity), id_rows, C.c_double(mult_id),
+                 ptr(out), rows, Cdim, qmin, qmax, stream()), "ivit_requant")
+        return out
+    check(lib.ivit_requant_codes(ptr(z), _BITS[z.dtype], ptr(s_in), ptr(mult), int(mult.numel() > 1), ptr(identity),
+                                 _BITS[identity.dtype] if identity is not None else 8, id_rows, C.c_double(mult_id),
+                                 ptr(out), out_bits, rows, Cdim, qmin, qmax, stream()), "ivit_requant_codes")
     return out
 
 
@@ -113,19 +127,26 @@ def dequant(q: torch.Tensor, scale: float) -> torch.Tensor:
 
 def fill_cls_rows(out: torch.Tensor, cls_row: torch.Tensor):
     B, N, Cdim = out.shape
-    check(_cabi.load().ivit_fill_cls_rows_i8(ptr(out), ptr(cls_row), B, N, Cdim, stream()), "ivit_fill_cls_rows_i8")
+    assert out.dtype == cls_row.dtype and out.is_contiguous()
+    lib = _cabi.load()
+    fn = lib.ivit_fill_cls_rows_i16 if out.dtype == torch.int16 else lib.ivit_fill_cls_rows_i8
+    check(fn(ptr(out), ptr(cls_row), B, N, Cdim, stream()), "ivit_fill_cls_rows")
 
 
 def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=None, s_in=None, qmin=-128, qmax=127,
          mult2=0.0, mult_id=0.0, qmin2=-128, qmax2=127, identity=None, scale_out=None, out=None, out_rows=None,
          group=0, out_group_stride=0, out_row_off=0, id_broadcast=False, force_slow=False,
-         z_bound_ok=False, simple=False) -> torch.Tensor:
-    """C = A[M,K] @ W[N,K]^T with a fused epilogue (see include/ivit_b200.h)."""
+         z_bound_ok=False, simple=False, out_bits=8) -> torch.Tensor:
+    """C = A[M,K] @ W[N,K]^T with a fused epilogue (see include/ivit_b200.h).  REQUANT / RESIDUAL store
+    int16 codes when `out` is int16 (or out_bits = 16); an int16 `identity` is the 16-bit residual stream."""
     assert A.dtype == torch.int8 and W.dtype == torch.int8 and A.dim() == 2 and W.dim() == 2
     assert A.stride(1) == 1 and W.is_contiguous()
     M, K = A.shape
     N = W.shape[0]
-    odt = {_cabi.EPI_ACC32: torch.int32, _cabi.EPI_LOGITS: torch.float32}.get(epilogue, torch.int8)
+    if out is not None and out.dtype == torch.int16:
+        out_bits = 16
+    odt = {_cabi.EPI_ACC32: torch.int32, _cabi.EPI_LOGITS: torch.float32}.get(
+        epilogue, torch.int16 if out_bits == 16 else torch.int8)
     if out is None:
         out = torch.empty((out_rows if out_rows is not None else M, N), dtype=odt, device=A.device)
     assert out.dtype == odt and out.stride(-1) == 1
@@ -139,6 +160,10 @@ def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=Non
     e.group, e.out_group_stride, e.out_row_off, e.id_broadcast = group, out_group_stride, out_row_off, int(id_broadcast)
     e.force_slow = int(force_slow)
     e.z_bound_ok = int(z_bound_ok)
+    e.out_bits = 16 if odt == torch.int16 else 8
+    e.id_bits = 16 if (identity is not None and identity.dtype == torch.int16) else 8
+    if identity is not None:
+        assert identity.dtype in (torch.int8, torch.int16) and identity.stride(-1) == 1
     lib = _cabi.load()
     fn = lib.ivit_gemm_i8_simple if simple else lib.ivit_gemm_i8
     ldo = out.stride(-2) if out.dim() >= 2 else N
@@ -184,7 +209,8 @@ def softmax_table_build(params: AttentionParams, device, collapse: bool = True) 
 
 def attention(qkv: torch.Tensor, B: int, N: int, H: int, hd: int, params: AttentionParams,
               want_probs: bool = False, out: torch.Tensor | None = None):
-    """qkv int8 [B,N,3*H*hd] -> out int8 [B,N,H*hd] (and optionally the softmax codes [B,H,N,N] u8)."""
+    """qkv int8 [B,N,3*H*hd] -> out int8 [B,N,H*hd] (and optionally the softmax codes [B,H,N,N]: uint8, or
+    int32 holding the uint16 codes of a 16-bit softmax)."""
     assert qkv.dtype == torch.int8 and qkv.is_contiguous()
     lib = _cabi.load()
     if out is None:
@@ -193,7 +219,10 @@ def attention(qkv: torch.Tensor, B: int, N: int, H: int, hd: int, params: Attent
     check(lib.ivit_attention_i8(ptr(qkv), ptr(out), B, N, H, hd, C.byref(params), stream()), "ivit_attention_i8")
     if not want_probs:
         return out
-    probs = torch.empty((B, H, N, N), dtype=torch.uint8, device=qkv.device)
+    wide = params.output_bit > 8
+    probs = torch.empty((B, H, N, N), dtype=torch.int16 if wide else torch.uint8, device=qkv.device)
     check(lib.ivit_attention_probs_i8(ptr(qkv), ptr(probs), B, N, H, hd, C.byref(params), stream()),
           "ivit_attention_probs_i8")
+    if wide:
+        probs = probs.to(torch.int32) & 0xffff
     return out, probs

@@ -117,8 +117,17 @@ class FrozenVitPlan:
         self.device = torch.device("cpu" if host_only else device)
         if not host_only and self.device.type != "cuda":
             raise _cabi.IvitKernelError("FrozenVitPlan needs a CUDA device (there is no CPU fallback)")
-        if any(b != 8 for b in cfg.bitwidths):
-            raise NotImplementedError("FrozenVitPlan: 8-bit activation locations only (16-bit: see DESIGN.md)")
+        if len(cfg.bitwidths) != 8 or any(not 2 <= int(b) <= 16 for b in cfg.bitwidths):
+            raise NotImplementedError("FrozenVitPlan: the 8 activation locations take 2..16 bits")
+        # vit_quant.py:180-187: patch_embed, pos_encoding, block_input, attention_out, softmax, mlp_out,
+        # norm2_in, att_block_out.  The residual stream (block_input / norm2_in / att_block_out) is stored
+        # as int16 codes as soon as one of its three locations is wider than 8 bits, the positional
+        # codes likewise; attention_out / mlp_out / patch_embed are in-register intermediates of a fused
+        # epilogue and only change its clamp range; softmax > 8 bits selects the two-plane P.V kernel.
+        (self.bw_patch, self.bw_pos, self.bw_block_in, self.bw_attn_out, self.bw_softmax, self.bw_mlp_out,
+         self.bw_norm2_in, self.bw_block_out) = (int(b) for b in cfg.bitwidths)
+        self.stream_dtype = torch.int16 if max(self.bw_block_in, self.bw_norm2_in, self.bw_block_out) > 8 else torch.int8
+        self.pos_dtype = torch.int16 if self.bw_pos > 8 else torch.int8
         if not host_only:
             _cabi.load()
         self.sd = {k: _np(v) for k, v in state.items() if not k.endswith(("weight_integer", "bias_integer"))}
@@ -185,7 +194,8 @@ class FrozenVitPlan:
     def _attention(self, p: str, s_qkv: np.ndarray) -> tuple:
         """vit_quant.py:72-85: scales of matmul_1, *scale, qact_attn1, int_softmax, matmul_2, qact2."""
         a = AttentionParams()
-        a.kind, a.output_bit = self.softmax_kind, 8
+        ob = self.bw_softmax
+        a.kind, a.output_bit = self.softmax_kind, ob
         s_mm1 = (s_qkv * s_qkv).astype(f32)                        # quant_modules.py:409
         s_scaled = (s_mm1 * f32(self.hd ** -0.5)).astype(f32)      # vit_quant.py:75
         s_attn = self._act_scale(p + "qact_attn1")
@@ -193,14 +203,15 @@ class FrozenVitPlan:
         a.qmin_attn, a.qmax_attn = -128, 127
         a.s_attn = float(s_attn[0])
         if self.softmax_kind == 0:
-            s_sm = np.array([1 / 2 ** 7], dtype=f32)               # ivit_modules.py:177
+            s_sm = np.array([1 / 2 ** (ob - 1)], dtype=f32)        # ivit_modules.py:177
         else:
-            s_sm = np.array([2 / 2 ** 8], dtype=f32)               # ibert_modules.py:317
+            s_sm = np.array([2 / 2 ** ob], dtype=f32)              # ibert_modules.py:317
             s16 = self._act_scale(p + "int_softmax.act", 16)       # inner QuantAct(16), :262,:310
             exp_scale = ((f32(0.35815147) * (s_attn * s_attn)) / f32(2 ** 30)).astype(f32)
             a.mult_exp16 = float(hm.dyadic_mult(exp_scale, s16).reshape(-1)[0])
             a.s_exp16 = float(s16[0])
         s_mm2 = (s_sm * s_qkv).astype(f32)
+        a.s_pv = float(s_mm2[0])
         s_out = self._act_scale(p + "qact2")
         a.mult_out = float(hm.dyadic_mult(s_mm2, s_out).reshape(-1)[0])
         a.qmin_out, a.qmax_out = -128, 127
@@ -214,18 +225,18 @@ class FrozenVitPlan:
         # ---- stem: qact_input -> patch_embed.proj -> patch_embed.qact -> cat(cls) -> qact1(+pos)
         self.s_input = self._act_scale("qact_input")
         self.inv_s_input = float(f32(1.0) / self.s_input[0])        # quant_utils.py:49 reciprocal
-        s_pe = self._act_scale("patch_embed.qact")
-        s_pos = self._act_scale("qact_pos")
-        s_x = self._act_scale("qact1")
-        pe = self._linear("patch_embed.proj", self.s_input, s_pe)
-        self.patch = self._residual(pe, s_pe, s_pos, s_x)
-        pos_codes = hm.quantize_tensor(sd["pos_embed"].reshape(self.N, C), 8, s_pos)      # qact_pos
-        self.pos_codes = self._dev(pos_codes, torch.int8)
+        s_pe = self._act_scale("patch_embed.qact", self.bw_patch)
+        s_pos = self._act_scale("qact_pos", self.bw_pos)
+        s_x = self._act_scale("qact1", self.bw_block_in)
+        pe = self._linear("patch_embed.proj", self.s_input, s_pe, self.bw_patch)
+        self.patch = self._residual(pe, s_pe, s_pos, s_x, self.bw_block_in)
+        pos_codes = hm.quantize_tensor(sd["pos_embed"].reshape(self.N, C), self.bw_pos, s_pos)      # qact_pos
+        self.pos_codes = self._dev(pos_codes, self.pos_dtype)
         # class-token row: the raw fp32 parameter enters qact1 un-quantised (vit_quant.py:290-296):
         # z = round(cls / s_pe) is NOT clamped to the patch_embed range.
         z_cls = hm.recover_codes(sd["cls_token"].reshape(1, C), s_pe)
-        cls_row = hm.requant_host(z_cls, s_pe, s_x, 8, identity_codes=pos_codes[:1], s_id=s_pos)
-        self.cls_row = self._dev(cls_row.reshape(C), torch.int8)
+        cls_row = hm.requant_host(z_cls, s_pe, s_x, self.bw_block_in, identity_codes=pos_codes[:1], s_id=s_pos)
+        self.cls_row = self._dev(cls_row.reshape(C), self.stream_dtype)
         # ---- blocks
         self.blocks = []
         for i in range(cfg.depth):
@@ -236,18 +247,20 @@ class FrozenVitPlan:
             s_qkv = self._act_scale(p + "attn.qact1")
             b.qkv = self._linear(p + "attn.qkv", s_n1, s_qkv)
             b.attn, s_ao = self._attention(p + "attn.", s_qkv)
-            s_q3 = self._act_scale(p + "attn.qact3")
-            s_mid = self._act_scale(p + "qact2")
-            b.proj = self._residual(self._linear(p + "attn.proj", s_ao, s_q3), s_q3, s_x, s_mid)
+            s_q3 = self._act_scale(p + "attn.qact3", self.bw_attn_out)
+            s_mid = self._act_scale(p + "qact2", self.bw_norm2_in)
+            b.proj = self._residual(self._linear(p + "attn.proj", s_ao, s_q3, self.bw_attn_out), s_q3, s_x, s_mid,
+                                    self.bw_norm2_in)
             s_n2 = self._act_scale(p + "qact3")
             b.norm2 = self._norm(p + "norm2", s_n2)
             s_g = self._act_scale(p + "mlp.qact_gelu")
             b.fc1 = self._linear(p + "mlp.fc1", s_n2, s_g)
             s_m1 = self._act_scale(p + "mlp.qact1")
             b.gelu_lut, b.scales["gelu_out"] = self._gelu_lut(s_g, s_m1)
-            s_m2 = self._act_scale(p + "mlp.qact2")
-            s_o = self._act_scale(p + "qact4")
-            b.fc2 = self._residual(self._linear(p + "mlp.fc2", s_m1, s_m2), s_m2, s_mid, s_o)
+            s_m2 = self._act_scale(p + "mlp.qact2", self.bw_mlp_out)
+            s_o = self._act_scale(p + "qact4", self.bw_block_out)
+            b.fc2 = self._residual(self._linear(p + "mlp.fc2", s_m1, s_m2, self.bw_mlp_out), s_m2, s_mid, s_o,
+                                   self.bw_block_out)
             b.s_mid, b.s_out = s_mid[0], s_o[0]
             b.scales.update(n1=s_n1[0], qkv=s_qkv[0], attn_out=s_ao[0], n2=s_n2[0], gelu_in=s_g[0], mlp1=s_m1[0])
             self.blocks.append(b)
@@ -292,8 +305,10 @@ class FrozenVitPlan:
         i8 = dict(dtype=torch.int8, device=dev)
         bufs = {
             "patches": torch.empty((B * self.cfg.num_patches, K0), **i8),
-            "x": torch.empty((M, C), **i8),          # residual stream (block input / output)
-            "x_mid": torch.empty((M, C), **i8),      # after Block.qact2
+            # residual stream (block input / output) and its value after Block.qact2: int16 codes when
+            # one of block_input_bw / norm2_in_bw / att_block_out_bw exceeds 8
+            "x": torch.empty((M, C), dtype=self.stream_dtype, device=dev),
+            "x_mid": torch.empty((M, C), dtype=self.stream_dtype, device=dev),
             "ln": torch.empty((M, C), **i8),         # LayerNorm + QuantAct output (GEMM A operand)
             "qkv": torch.empty((M, 3 * C), **i8),
             "attn": torch.empty((M, C), **i8),
@@ -322,14 +337,16 @@ class FrozenVitPlan:
                      out=out, force_slow=lin.force_slow, z_bound_ok=lin.z_bound_ok, **kw)
         M, K = A.shape
         Nn = lin.w.shape[0]
-        by = M * K + Nn * K + M * Nn * out.element_size() + (M * Nn if epilogue == EPI_RESIDUAL else 0) + Nn * 16
+        idn = kw.get("identity")
+        by = (M * K + Nn * K + M * Nn * out.element_size() + Nn * 16 +
+              (M * Nn * idn.element_size() if epilogue == EPI_RESIDUAL and idn is not None else 0))
         self._mark("gemm_i8_tc", 2.0 * M * Nn * K, by)
         return r
 
     def _ln(self, x, s_in, nm: _Norm, out):
         r = ops.layernorm_requant(nm.kind, x, float(s_in), nm.bias_int, nm.sf, nm.mult, nm.qmin, nm.qmax,
                                   shift=nm.shift, use_int_sqrt=nm.use_int_sqrt, out=out)
-        self._mark("layernorm_requant", 0, 2 * out.numel() + 16 * self.C)
+        self._mark("layernorm_requant", 0, (1 + x.element_size()) * out.numel() + 16 * self.C)
         return r
 
     def _enqueue(self, images: torch.Tensor, taps: dict | None = None, blocks: int | None = None) -> torch.Tensor:
@@ -354,7 +371,7 @@ class FrozenVitPlan:
         self._gemm(bufs["patches"], self.patch, EPI_RESIDUAL, x, identity=self.pos_codes, group=cfg.num_patches,
                    out_group_stride=N, out_row_off=1, id_broadcast=True)
         ops.fill_cls_rows(x.view(B, N, C), self.cls_row)
-        self._mark("fill_cls_rows", 0, B * C)
+        self._mark("fill_cls_rows", 0, B * C * x.element_size())
         tap("qact1", x, (B, N, C))
         s_x = self.blocks[0].s_in if self.blocks else f32(0)
         nblk = cfg.depth if blocks is None else blocks

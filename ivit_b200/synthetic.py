@@ -114,7 +114,7 @@ def synth_images(batch: int, cfg: VitConfig, seed: int = 0) -> torch.Tensor:
 # pass (scripts/inference.py:33-91, one forward of `synth_images(4, cfg, seed=1)` with
 # running_stat=True, then freeze_model) and are committed in tests/golden/vit_<case>.npz by
 # oracle/make_golden.py.  A real deployment reads the same buffers from a reference checkpoint.
-# name -> (config, gelu, softmax, layernorm, negate_ln_frac)
+# name -> (config, gelu, softmax, layernorm, negate_ln_frac[, bitwidths of the 8 activation locations])
 CASES = {
     "toy_ivit": ("toy", "ivit", "ivit", "ivit", 0.0),
     "toy_ibert": ("toy", "ibert", "ibert", "ibert", 0.0),
@@ -125,6 +125,13 @@ CASES = {
     "deit_small_ivit": ("deit_small", "ivit", "ivit", "ivit", 0.0),
     "vit_base_mixed": ("vit_base", "ivit", "ibert", "ivit", 0.0),
     "deit_base_ibert": ("deit_base", "ibert", "ibert", "ibert", 0.0),
+    # 16-bit activation locations (vit_quant.py:180-187)
+    "toy_ivit_w16": ("toy", "ivit", "ivit", "ivit", 0.0, (16,) * 8),
+    "toy_ibert_w16": ("toy", "ibert", "ibert", "ibert", 0.0, (16,) * 8),
+    "toy_mixed_bw": ("toy", "ivit", "ibert", "ivit", 0.05, (16, 8, 8, 16, 16, 8, 16, 8)),
+    "toy_ivit_sm16": ("toy", "ivit", "ivit", "ivit", 0.0, (8, 8, 8, 8, 16, 8, 8, 8)),
+    "deit_tiny_ibert_w16": ("deit_tiny", "ibert", "ibert", "ibert", 0.0, (16,) * 8),
+    "deit_tiny_ivit_w16": ("deit_tiny", "ivit", "ivit", "ivit", 0.0, (16,) * 8),
 }
 
 
@@ -139,8 +146,9 @@ def load_case(case: str):
     (``*.x_min``, ``*.x_max``, ``*.shift``) as float32 numpy arrays, keyed like the reference
     state_dict.  Also returns the raw fixture (reference logits, tap hashes) as third element."""
     import numpy as np
-    cfg_name, g, s, l, neg = CASES[case]
-    cfg = CONFIGS[cfg_name].with_layers(gelu=g, softmax=s, layernorm=l)
+    cfg_name, g, s, l, neg = CASES[case][:5]
+    bw = CASES[case][5] if len(CASES[case]) > 5 else None
+    cfg = CONFIGS[cfg_name].with_layers(gelu=g, softmax=s, layernorm=l, bitwidths=bw)
     state = {k: v.numpy() for k, v in synth_vit_state(cfg, seed=0, negate_ln_frac=neg).items()}
     fix = np.load(golden_path(case))
     for k in fix.files:

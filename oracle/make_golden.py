@@ -52,6 +52,15 @@ CASES = {
     # configs[2]: ViT-Base, mixed layer selection
     "vit_base_mixed": ("vit_base", "ivit", "ibert", "ivit", None, 2, 0.0, ("qact2",)),
     "deit_base_ibert": ("deit_base", "ibert", "ibert", "ibert", None, 2, 0.0, ("qact2",)),
+    # 16-bit activation locations (vit_quant.py:180-187; scripts/inference.py:297 --bitwidth 16): all eight
+    # at 16 bit, and a mix (patch_embed, pos, block_input, attention_out, softmax, mlp_out, norm2_in, block_out)
+    "toy_ivit_w16": ("toy", "ivit", "ivit", "ivit", (16,) * 8, 2, 0.0, ("blocks.0.attn.qact2", "blocks.1.qact4")),
+    "toy_ibert_w16": ("toy", "ibert", "ibert", "ibert", (16,) * 8, 2, 0.0, ("blocks.0.attn.qact2", "blocks.1.qact4")),
+    "toy_mixed_bw": ("toy", "ivit", "ibert", "ivit", (16, 8, 8, 16, 16, 8, 16, 8), 2, 0.05, ("blocks.1.qact4",)),
+    "toy_ivit_sm16": ("toy", "ivit", "ivit", "ivit", (8, 8, 8, 8, 16, 8, 8, 8), 2, 0.0, ("blocks.0.attn.qact2",)),
+    # BASELINE.json configs[4] family: 16-bit ibert layer types on a DeiT (tiny here: CPU-sized oracle run)
+    "deit_tiny_ibert_w16": ("deit_tiny", "ibert", "ibert", "ibert", (16,) * 8, 2, 0.0, ("qact2",)),
+    "deit_tiny_ivit_w16": ("deit_tiny", "ivit", "ivit", "ivit", (16,) * 8, 2, 0.0, ("qact2",)),
 }
 CALIB_BATCH = 4
 

@@ -251,7 +251,7 @@ def test_gemm_logits(shape):
     _gemm_case(*shape, seed=5, epilogue=_cabi.EPI_LOGITS)
 
 
-def _attention_case(kind, B, N, H, seed, s_qkv=0.05, a_max=None):
+def _attention_case(kind, B, N, H, seed, s_qkv=0.05, a_max=None, bits=8):
     rng = np.random.default_rng(seed)
     hd = 64
     C = H * hd
@@ -267,12 +267,12 @@ def _attention_case(kind, B, N, H, seed, s_qkv=0.05, a_max=None):
     a_max = np.array([np.abs(attn).max() * 0.5 if a_max is None else a_max], dtype=f32)
     attn_q, s_a, attn_codes = O.quant_act(attn, 8, -a_max, a_max, pre_scale=s)
     p = _cabi.AttentionParams()
-    p.kind, p.output_bit = kind, 8
+    p.kind, p.output_bit = kind, bits
     p.mult_attn = float(hm.dyadic_mult(s, s_a).reshape(-1)[0])
     p.qmin_attn, p.qmax_attn = -128, 127
     p.s_attn = float(s_a[0])
     if kind == 0:
-        sm, s_sm, sm_codes = O.ivit_softmax(attn_q, s_a, 8)
+        sm, s_sm, sm_codes = O.ivit_softmax(attn_q, s_a, bits)
     else:
         # calibrate the inner QuantAct(16) range the way the reference would: max of exp_int values
         xi = attn_q / s_a
@@ -280,7 +280,7 @@ def _attention_case(kind, B, N, H, seed, s_qkv=0.05, a_max=None):
         x0 = np.floor(f32(-0.6931) / s_a)
         e_max = f32(1.0 / 0.35815147) / (s_a * s_a) * f32(2.0 ** 30)
         amax = np.array([e_max[0]], dtype=f32)
-        sm, s_sm, sm_codes = O.ibert_softmax(attn_q, s_a, 8, -amax, amax)
+        sm, s_sm, sm_codes = O.ibert_softmax(attn_q, s_a, bits, -amax, amax)
         s16 = O.sym_scale(16, -amax, amax)
         exp_scale = (f32(0.35815147) * (s_a * s_a) / f32(2 ** 30)).astype(f32)
         p.mult_exp16 = float(hm.dyadic_mult(exp_scale, s16).reshape(-1)[0])
@@ -291,6 +291,7 @@ def _attention_case(kind, B, N, H, seed, s_qkv=0.05, a_max=None):
     _, s_out, out_codes = O.quant_act(o, 8, -o_max, o_max, pre_scale=s_o)
     p.mult_out = float(hm.dyadic_mult(s_o, s_out).reshape(-1)[0])
     p.qmin_out, p.qmax_out = -128, 127
+    p.s_pv = float(s_o.reshape(-1)[0])
     out, probs = ops.attention(_t(qkv.reshape(B, N, 3 * C), torch.int8), B, N, H, hd, p, want_probs=True)
     _cmp(probs.cpu().numpy(), sm_codes, f"attention probs kind={kind}")
     _cmp(out.cpu().numpy(), out_codes, f"attention out kind={kind}")
@@ -331,6 +332,20 @@ def test_attention_ivit_collapsed_table(N, threads_per_row):
 
 def test_attention_ivit_peaked(threads_per_row):
     _attention_case(0, 2, 197, 2, seed=7, s_qkv=0.2)
+
+
+@pytest.mark.parametrize("kind", [0, 1])
+@pytest.mark.parametrize("N", [197, 49, 130, 256, 33])
+def test_attention_softmax16(kind, N):
+    """softmax_bw = 16 (ivit codes up to 32767, ibert 32768): u16 operand as two u8 planes, two MMAs,
+    attn.qact2 through the float32-recovery path (|acc| up to 8e8)."""
+    _attention_case(kind, 2, N, 3, seed=N + 11 * kind, bits=16)
+
+
+def test_attention_softmax16_peaked_and_mid_bits():
+    _attention_case(0, 2, 197, 2, seed=7, s_qkv=0.2, bits=16)
+    _attention_case(1, 1, 197, 2, seed=9, bits=12)       # any width in (8, 16] takes the two-plane kernel
+    _attention_case(0, 1, 100, 2, seed=10, bits=4)       # and any width <= 8 the one-plane kernel
 
 
 @pytest.mark.parametrize("N", [197, 49])

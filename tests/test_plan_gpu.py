@@ -56,6 +56,24 @@ def test_deit_tiny_ibert():
     assert np.allclose(logits, fix["logits"], rtol=1e-6, atol=1e-6 * np.abs(fix["logits"]).max())
 
 
+@pytest.mark.parametrize("case", ["toy_ivit_w16", "toy_ibert_w16", "toy_mixed_bw", "toy_ivit_sm16",
+                                  "deit_tiny_ibert_w16", "deit_tiny_ivit_w16"])
+def test_16bit_locations_all_boundaries(case):
+    """16-bit activation locations (--bitwidth 16 and mixed 8/16): int16 residual stream, two-plane u16
+    softmax operand; every boundary bit-exact against the oracle, logits against the reference fixture."""
+    _, plan, _, logits, fix = _run_case(case, 2)
+    ref = fix["logits"]
+    assert np.array_equal(logits.argmax(1), ref.argmax(1))
+    assert np.allclose(logits, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
+def test_16bit_fresh_inputs_and_graph_replay():
+    cfg, plan, x, logits, _ = _run_case("toy_ibert_w16", 3, seed=11)
+    assert plan.stream_dtype == torch.int16
+    g = plan.capture(3)
+    assert np.array_equal(g(x.cuda()).cpu().numpy(), logits)
+
+
 def test_fresh_inputs_and_graph_replay():
     cfg, plan, x, logits, _ = _run_case("toy_ivit", 3, seed=11)
     g = plan.capture(3)
