@@ -85,6 +85,10 @@ int ivit_fill_cls_rows_i8(int8_t* out, const int8_t* cls_row, int B, int N, int 
 int ivit_layernorm_requant_i16_i8(int kind, const int16_t* x, int64_t ldx, int8_t* out, int rows, int C, float s_in,
                                   const float* bias_int, const float* sf, const double* mult, int qmin, int qmax,
                                   float shift, int use_int_sqrt, void* stream);
+/* QuantAct on a float tensor at any width up to 16 bits (quant_utils.py:49,93; e.g. qact_pos at 16 bit):
+ * out int8 (out_bits 8) or int16 (out_bits 16) = clamp(round(inv_scale * x), qmin, qmax). */
+int ivit_quantize_f32_codes(const float* x, void* out, int out_bits, float inv_scale, int64_t n, int qmin, int qmax,
+                            void* stream);
 int ivit_fill_cls_rows_i16(int16_t* out, const int16_t* cls_row, int B, int N, int C, void* stream);
 int ivit_requant_codes(const void* z, int z_bits, const float* s_in, const double* mult, int per_channel,
                        const void* identity, int id_bits, int64_t id_rows, double mult_id, void* out, int out_bits,

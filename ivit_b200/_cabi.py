@@ -76,6 +76,8 @@ _SIGS = {
     "ivit_layernorm_requant_i16_i8": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_float,
                                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
                                                 C.c_int, C.c_void_p]),
+    "ivit_quantize_f32_codes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_int, C.c_int,
+                                          C.c_void_p]),
     "ivit_fill_cls_rows_i16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "ivit_requant_codes": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
                                      C.c_int64, C.c_double, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int,

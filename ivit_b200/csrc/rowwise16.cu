@@ -131,6 +131,15 @@ __global__ void requant_any_kernel(const ZT* __restrict__ z, const float* __rest
   }
 }
 
+// QuantAct on a float tensor at any width up to 16 bits: quant_utils.py:49 + :93 (reciprocal multiply)
+template <typename OT>
+__global__ void quantize_codes_kernel(const float* __restrict__ x, OT* __restrict__ out, float inv_s, long long n,
+                                      float qmin, float qmax) {
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < n;
+       t += static_cast<long long>(gridDim.x) * blockDim.x)
+    out[t] = static_cast<OT>(static_cast<int>(fminf(fmaxf(rintf(__fmul_rn(inv_s, x[t])), qmin), qmax)));
+}
+
 template <typename ZT, typename IT, typename OT>
 static int launch_requant(const void* z, const float* s_in, const double* mult, int per_channel, const void* id,
                           long long id_rows, double mult_id, void* out, long long rows, int C, int qmin, int qmax,
@@ -195,6 +204,24 @@ extern "C" int ivit_fill_cls_rows_i16(int16_t* out, const int16_t* cls_row, int 
   if (B * C <= 0) return 0;
   fill_cls_rows16_kernel<<<(B * C + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(out, cls_row, B, N, C);
   return check_launch("fill_cls_rows16_kernel");
+}
+
+extern "C" int ivit_quantize_f32_codes(const float* x, void* out, int out_bits, float inv_scale, int64_t n, int qmin,
+                                       int qmax, void* stream) {
+  if (n <= 0) return 0;
+  if (out_bits != 8 && out_bits != 16) return fail(IVIT_ERR_BAD_ARG, "quantize: out_bits must be 8 or 16");
+  const int lim = out_bits == 16 ? 32768 : 128;
+  if (qmin < -lim || qmax > lim - 1) return fail(IVIT_ERR_UNSUPPORTED, "quantize: clamp range exceeds the output type");
+  long long g = (n + 255) / 256;
+  if (g > 148LL * 16) g = 148LL * 16;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (out_bits == 16)
+    quantize_codes_kernel<int16_t><<<static_cast<int>(g), 256, 0, st>>>(x, static_cast<int16_t*>(out), inv_scale, n,
+                                                                       static_cast<float>(qmin), static_cast<float>(qmax));
+  else
+    quantize_codes_kernel<int8_t><<<static_cast<int>(g), 256, 0, st>>>(x, static_cast<int8_t*>(out), inv_scale, n,
+                                                                      static_cast<float>(qmin), static_cast<float>(qmax));
+  return check_launch("quantize_codes_kernel");
 }
 
 extern "C" int ivit_requant_codes(const void* z, int z_bits, const float* s_in, const double* mult, int per_channel,

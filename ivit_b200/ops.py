@@ -19,11 +19,20 @@ def dev(a, dtype, device) -> torch.Tensor:
     return torch.from_numpy(np.ascontiguousarray(a)).to(dtype=dtype).to(device)
 
 
-def quantize(x: torch.Tensor, inv_scale: float) -> torch.Tensor:
+def quantize(x: torch.Tensor, inv_scale: float, bits: int = 8) -> torch.Tensor:
+    """QuantAct on a float tensor: int8 codes for bits <= 8, int16 codes for 9..16 bits."""
     x = x.contiguous()
-    out = torch.empty(x.shape, dtype=torch.int8, device=x.device)
-    check(_cabi.load().ivit_quantize_f32_i8(ptr(x), ptr(out), C.c_float(inv_scale), x.numel(), stream()),
-          "ivit_quantize_f32_i8")
+    lib = _cabi.load()
+    if bits <= 8:
+        out = torch.empty(x.shape, dtype=torch.int8, device=x.device)
+        if bits == 8:
+            check(lib.ivit_quantize_f32_i8(ptr(x), ptr(out), C.c_float(inv_scale), x.numel(), stream()),
+                  "ivit_quantize_f32_i8")
+            return out
+    else:
+        out = torch.empty(x.shape, dtype=torch.int16, device=x.device)
+    check(lib.ivit_quantize_f32_codes(ptr(x), ptr(out), 16 if bits > 8 else 8, C.c_float(inv_scale), x.numel(),
+                                      -(2 ** (bits - 1)), 2 ** (bits - 1) - 1, stream()), "ivit_quantize_f32_codes")
     return out
 
 

@@ -40,9 +40,7 @@ def run_pending(q: QTensor) -> torch.Tensor:
     """Launch a pending producer without fusing a consumer into it; returns canonical codes."""
     p = q.pending
     if p.kind == "quantize":
-        if p.bits != 8:
-            raise NotImplementedError("frozen QuantAct on a float tensor: 8-bit only")
-        return ops.quantize(p.x.contiguous(), float(p.inv))
+        return ops.quantize(p.x.contiguous(), float(p.inv), bits=p.bits)
     if p.kind == "gemm":
         return ops.gemm(p.A, p.lin["w"], _cabi.EPI_ACC32, bias=p.lin["bias"])
     if p.kind == "cat":

@@ -140,6 +140,12 @@ class QuantAct(_FrozenCache, nn.Module):
             c["q"] = hm.qrange(self.activation_bit)
         return c["s_out"], c["s_out_h"], c["q"]
 
+    def _store_bits(self) -> int:
+        """int8 codes up to 8 bits, int16 codes for the 16-bit locations (vit_quant.py:180-187)."""
+        if self.activation_bit > 16:
+            raise NotImplementedError("frozen QuantAct: at most 16-bit activations")
+        return 16 if self.activation_bit > 8 else 8
+
     def _wrap(self, codes, shape, device):
         s, h, _ = self._out_scale(device)
         q = QTensor(codes, scale=s, hscale=h)
@@ -165,8 +171,6 @@ class QuantAct(_FrozenCache, nn.Module):
                 # a float module (the `float` registry entries) feeds this QuantAct: quant_utils.py:220
                 # z = round(x / s_pre) with torch ops (IEEE division + rint: same codes as on the CPU),
                 # then the integer requantisation kernel (identity branch included)
-                if self.activation_bit != 8:
-                    raise NotImplementedError("frozen QuantAct: 8-bit outputs only")
                 sp = s_pre.to(device).float()
                 z = torch.round(x.detach().float() / (sp.view(1, -1, 1, 1) if x.dim() == 4 and sp.numel() > 1 else sp))
                 z = z.to(torch.int32).contiguous()
@@ -182,7 +186,7 @@ class QuantAct(_FrozenCache, nn.Module):
                     mult_id = float(mh[0])
                 z2 = z.reshape(-1, z.shape[-1])
                 out = ops.requant(z2, s_in_d, mult, qmin, qmax, idc.reshape(-1, z.shape[-1]) if idc is not None else None,
-                                  mult_id)
+                                  mult_id, out_bits=self._store_bits())
                 return self._wrap(out.reshape(z.shape), tuple(x.shape), device)
             inv = f32(1.0) / s_out_h[0]
             q = QTensor(pending=Pending("quantize", x=x.detach(), inv=inv, bits=self.activation_bit),
@@ -191,11 +195,12 @@ class QuantAct(_FrozenCache, nn.Module):
         p = x.pending if x.codes is None else None
         kind = p.kind if p is not None else None
         shape = tuple(x.shape)
-        if identity is None and kind == "gemm" and x.is_canonical() and self.activation_bit == 8:
+        if identity is None and kind == "gemm" and x.is_canonical() and self.activation_bit <= 16:
             # QuantLinear / QuantConv2d -> QuantAct: requantisation fused into the GEMM epilogue
-            mult, _ = self._mult(("gemm", id(p.lin)), p.lin["b_scale_h"], device)
+            mult, mh = self._mult(("gemm", id(p.lin)), p.lin["b_scale_h"], device)
             out = ops.gemm(p.A, p.lin["w"], _cabi.EPI_REQUANT, bias=p.lin["bias"], mult=mult, s_in=p.lin["b_scale"],
-                           qmin=qmin, qmax=qmax, z_bound_ok=p.lin["z_bound_ok"], force_slow=p.lin["force_slow"])
+                           qmin=qmin, qmax=qmax, z_bound_ok=p.lin["z_bound_ok"],
+                           force_slow=p.lin["force_slow"] or bool(np.abs(mh).max() >= 256.0), out_bits=self._store_bits())
             return self._wrap(out, shape, device)
         if identity is None and kind == "ln":
             return self._wrap(p.mod._frozen_ln_requant(p, x, self, device), shape, device)
@@ -212,7 +217,7 @@ class QuantAct(_FrozenCache, nn.Module):
         z = x.materialize()
         if not z.is_contiguous():
             z = z.contiguous()
-        if z.dtype not in (torch.int8, torch.int32):
+        if z.dtype not in (torch.int8, torch.int16, torch.int32):
             z = z.to(torch.int32)
         s_in_h = fz.eff_hscale(x)
         mult, _ = self._mult(("req", s_in_h.tobytes()), s_in_h, device)
@@ -222,17 +227,15 @@ class QuantAct(_FrozenCache, nn.Module):
             if not isinstance(identity, QTensor):
                 raise _cabi.IvitKernelError("frozen QuantAct: identity must come from a frozen module")
             idc = identity.materialize()
-            if idc.dtype != torch.int8:
-                raise NotImplementedError("identity branch wider than 8 bits")
+            if idc.dtype not in (torch.int8, torch.int16):
+                raise NotImplementedError("identity branch wider than 16 bits")
             if tuple(idc.shape) != tuple(z.shape):
                 if idc.shape[-1] != z.shape[-1] or z.numel() % idc.numel() != 0:
                     raise NotImplementedError("identity broadcast other than over leading dims")
             idc = idc.contiguous()
             _, mh = self._mult(("id", fz.eff_hscale(identity).tobytes()), fz.eff_hscale(identity), device)
             mult_id = float(mh[0])
-        if self.activation_bit != 8:
-            raise NotImplementedError("frozen QuantAct: 8-bit outputs only (16-bit locations: DESIGN.md section 7)")
-        out = ops.requant(z, s_in_d, mult, qmin, qmax, idc, mult_id)
+        out = ops.requant(z, s_in_d, mult, qmin, qmax, idc, mult_id, out_bits=self._store_bits())
         return self._wrap(out, shape, device)
 
     def forward(self, x, pre_act_scaling_factor=None, identity=None, identity_scaling_factor=None,
@@ -482,8 +485,8 @@ class _IntLayerNormBase(_FrozenCache):
     def _frozen_ln_requant(self, p, view: QTensor, qact: "QuantAct", device):
         c = self._fz_get()
         codes = p.x.materialize()
-        if codes.dtype != torch.int8:
-            raise NotImplementedError("frozen IntLayerNorm: 8-bit input codes (16-bit streams: DESIGN.md section 7)")
+        if codes.dtype not in (torch.int8, torch.int16):
+            raise NotImplementedError("frozen IntLayerNorm: int8 or int16 input codes")
         if not codes.is_contiguous():
             codes = codes.contiguous()
         C = codes.shape[-1]
@@ -691,8 +694,8 @@ class _IntSoftmaxBase(_FrozenCache):
         fz.require_cuda(x, type(self).__name__)
         if x.codes is not None or x.pending.kind != "qattn":
             raise NotImplementedError("frozen IntSoftmax outside the attention chain of vit_quant.py:72-82")
-        if self.output_bit != 8:
-            raise NotImplementedError("frozen IntSoftmax: 8-bit output (16-bit: DESIGN.md section 7)")
+        if not 2 <= self.output_bit <= 16:
+            raise NotImplementedError("frozen IntSoftmax: output_bit in [2, 16]")
         c = self._fz_get()
         if "s_out" not in c:
             v = 1 / 2 ** (self.output_bit - 1) if self._kind == 0 else 2 / 2 ** self.output_bit
@@ -787,7 +790,8 @@ def _frozen_attention(p, view: QTensor, qact2: QuantAct, device):
     key = ("attn", id(sm.mod))
     if key not in cache:
         a = _cabi.AttentionParams()
-        a.kind, a.output_bit = sm.mod._kind, 8
+        a.kind, a.output_bit = sm.mod._kind, int(sm.mod.output_bit)
+        a.s_pv = float(np.asarray(p.s_h, dtype=f32).reshape(-1)[0])
         qa = qattn.qact
         s_attn, s_attn_h, (lo, hi) = qa._out_scale(device)
         a.mult_attn = float(hm.dyadic_mult(qattn.s_in_h, s_attn_h).reshape(-1)[0])

@@ -132,6 +132,7 @@ CASES = {
     "toy_ivit_sm16": ("toy", "ivit", "ivit", "ivit", 0.0, (8, 8, 8, 8, 16, 8, 8, 8)),
     "deit_tiny_ibert_w16": ("deit_tiny", "ibert", "ibert", "ibert", 0.0, (16,) * 8),
     "deit_tiny_ivit_w16": ("deit_tiny", "ivit", "ivit", "ivit", 0.0, (16,) * 8),
+    "deit_base_ibert_w16": ("deit_base", "ibert", "ibert", "ibert", 0.0, (16,) * 8),    # BASELINE.json configs[4]
 }
 
 

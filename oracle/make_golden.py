@@ -61,6 +61,8 @@ CASES = {
     # BASELINE.json configs[4] family: 16-bit ibert layer types on a DeiT (tiny here: CPU-sized oracle run)
     "deit_tiny_ibert_w16": ("deit_tiny", "ibert", "ibert", "ibert", (16,) * 8, 2, 0.0, ("qact2",)),
     "deit_tiny_ivit_w16": ("deit_tiny", "ivit", "ivit", "ivit", (16,) * 8, 2, 0.0, ("qact2",)),
+    # configs[4]: DeiT-Base, ibert layer types, --bitwidth 16
+    "deit_base_ibert_w16": ("deit_base", "ibert", "ibert", "ibert", (16,) * 8, 2, 0.0, ("qact2",)),
 }
 CALIB_BATCH = 4
 

@@ -27,7 +27,8 @@ def _build(case):
     return cfg, state, fix, model
 
 
-@pytest.mark.parametrize("case", ["toy_ivit", "toy_ibert", "toy_mixed", "deit_tiny_ivit"])
+@pytest.mark.parametrize("case", ["toy_ivit", "toy_ibert", "toy_mixed", "deit_tiny_ivit", "toy_ivit_w16", "toy_ibert_w16",
+                                  "toy_mixed_bw", "toy_ivit_sm16"])
 def test_frozen_modules_match_oracle(case):
     cfg, state, fix, model = _build(case)
     x = synth_images(2, cfg, seed=0)
@@ -57,6 +58,18 @@ def test_frozen_modules_match_oracle(case):
     assert np.array_equal(logits, exp)
     assert np.array_equal(again, exp)
     assert np.array_equal(logits.argmax(1), fix["logits"][:2].argmax(1))
+
+
+def test_compile_frozen_16bit_equals_module_path():
+    from ivit_b200.api import compile_frozen, config_from_model
+    cfg, state, fix, model = _build("toy_ibert_w16")
+    assert tuple(config_from_model(model).bitwidths) == (16,) * 8
+    x = synth_images(4, cfg, seed=3)
+    with torch.no_grad():
+        ref = model(x.cuda()).float().cpu()
+    sess = compile_frozen(model, batch=4)
+    assert sess.plan.stream_dtype == torch.int16
+    assert torch.equal(sess.infer(x.pin_memory()), ref)
 
 
 def test_state_dict_exposes_integer_weights():
