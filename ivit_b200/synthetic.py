@@ -156,3 +156,105 @@ def load_case(case: str):
         if k.startswith("range/"):
             state[k[len("range/"):]] = fix[k].astype(np.float32)
     return cfg, state, fix
+
+
+# ---------------------------------------------------------------------------------------------
+# Swin (swin_quant.py): BASELINE.json configs[3].  The reference hard-codes the ivit layer types
+# (IntLayerNorm / IntSoftmax / IntGELU aliases) and the bit-widths (16-bit residual stream).
+@dataclass(frozen=True)
+class SwinConfig:
+    name: str
+    embed_dim: int = 96
+    depths: tuple = (2, 2, 6, 2)
+    num_heads: tuple = (3, 6, 12, 24)
+    window_size: int = 7
+    mlp_ratio: int = 4
+    img_size: int = 224
+    patch_size: int = 4
+    in_chans: int = 3
+    num_classes: int = 1000
+
+    @property
+    def grid(self) -> int:
+        return self.img_size // self.patch_size
+
+    def stage_dim(self, i: int) -> int:
+        return self.embed_dim * 2 ** i
+
+    def stage_res(self, i: int) -> int:
+        return self.grid // 2 ** i
+
+    def block_window_shift(self, i: int, j: int):
+        """swin_quant.py:200-203: no partition / shift when the resolution is not larger than the window."""
+        res, ws = self.stage_res(i), self.window_size
+        shift = 0 if j % 2 == 0 else ws // 2
+        if res <= ws:
+            return res, 0
+        return ws, shift
+
+
+SWIN_CONFIGS = {
+    "swin_tiny": SwinConfig("swin_tiny"),
+    # 2-stage toy: 56x56 image -> 14x14 tokens (4 windows, shifted block with mask) -> 7x7 (one window)
+    "swin_toy": SwinConfig("swin_toy", embed_dim=96, depths=(2, 2), num_heads=(3, 6), img_size=56, num_classes=100),
+}
+
+SWIN_CASES = {"swin_toy": "swin_toy", "swin_tiny": "swin_tiny"}
+
+
+def synth_swin_state(cfg: SwinConfig, seed: int = 0) -> dict:
+    """Deterministic fp32 weights keyed like swin_quant.SwinTransformer.state_dict() (weights only)."""
+    g = torch.Generator(device="cpu")
+    g.manual_seed(3000 + seed)
+
+    def normal(*shape, std):
+        return (torch.randn(*shape, generator=g) * std).clamp_(-2.5 * std, 2.5 * std)
+
+    def ln(prefix, C, sd):
+        sd[prefix + ".weight"] = torch.rand(C, generator=g) + 0.5
+        sd[prefix + ".bias"] = normal(C, std=0.1)
+
+    sd: dict = {}
+    C0, P = cfg.embed_dim, cfg.patch_size
+    sd["patch_embed.proj.weight"] = normal(C0, cfg.in_chans, P, P, std=0.1)
+    sd["patch_embed.proj.bias"] = normal(C0, std=0.1)
+    ln("patch_embed.norm", C0, sd)
+    ws = cfg.window_size
+    for i, depth in enumerate(cfg.depths):
+        C, nH = cfg.stage_dim(i), cfg.num_heads[i]
+        for j in range(depth):
+            b = f"layers.{i}.blocks.{j}."
+            w, _ = cfg.block_window_shift(i, j)
+            ln(b + "norm1", C, sd)
+            sd[b + "attn.qkv.weight"] = normal(3 * C, C, std=0.02) * 6.0
+            sd[b + "attn.qkv.bias"] = normal(3 * C, std=0.1)
+            sd[b + "attn.relative_position_bias_table"] = normal((2 * w - 1) ** 2, nH, std=0.5)
+            sd[b + "attn.proj.weight"] = normal(C, C, std=0.02)
+            sd[b + "attn.proj.bias"] = normal(C, std=0.1)
+            ln(b + "norm2", C, sd)
+            sd[b + "mlp.fc1.weight"] = normal(C * cfg.mlp_ratio, C, std=0.02)
+            sd[b + "mlp.fc1.bias"] = normal(C * cfg.mlp_ratio, std=0.1)
+            sd[b + "mlp.fc2.weight"] = normal(C, C * cfg.mlp_ratio, std=0.02)
+            sd[b + "mlp.fc2.bias"] = normal(C, std=0.1)
+        if i < len(cfg.depths) - 1:
+            d = f"layers.{i}.downsample."
+            ln(d + "norm", 4 * C, sd)
+            sd[d + "reduction.weight"] = normal(2 * C, 4 * C, std=0.02)
+    Cl = cfg.stage_dim(len(cfg.depths) - 1)
+    ln("norm", Cl, sd)
+    sd["head.weight"] = normal(cfg.num_classes, Cl, std=0.02)
+    sd["head.bias"] = normal(cfg.num_classes, std=0.1)
+    return sd
+
+
+def load_swin_case(case: str):
+    """(cfg, state incl. calibrated ranges, fixture) of a committed Swin case (tests/golden/swin_<case>.npz)."""
+    import os
+    import numpy as np
+    cfg = SWIN_CONFIGS[SWIN_CASES[case]]
+    state = {k: v.numpy() for k, v in synth_swin_state(cfg, seed=0).items()}
+    fix = np.load(os.path.join(os.path.dirname(golden_path("x")), f"swin_{case}.npz"))
+    for k in fix.files:
+        if k.startswith("range/"):
+            state[k[len("range/"):]] = fix[k].astype(np.float32)
+    return cfg, state, fix

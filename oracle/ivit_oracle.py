@@ -276,15 +276,76 @@ def torch_sum_lastdim(x):
     return final.reshape(*lead, 1).astype(np.float32)
 
 
-def ivit_layernorm(x, scale, weight, bias):
-    """ivit_modules.py:30-65 IVITIntLayerNorm.forward.  x: [B,N,C].
+def _cascade_rows(x2, n_steps, load):
+    """ATen multi_row_sum (SumKernel.cpp): `load(i)` -> [R, K] values of step i for K independent
+    accumulators; sequential over i, cascading into a higher level every 2^max(4, ceil_log2(n)/4) steps."""
+    lp = max(4, max(n_steps - 1, 0).bit_length() // 4)
+    step, mask = 1 << lp, (1 << lp) - 1
+    first = load(0) if n_steps > 0 else None
+    acc = [np.zeros_like(first) if first is not None else 0 for _ in range(4)]
+    i = 0
+    while i + step <= n_steps:
+        for _ in range(step):
+            acc[0] = acc[0] + load(i)
+            i += 1
+        for j in range(1, 4):
+            acc[j] = acc[j] + acc[j - 1]
+            acc[j - 1] = np.zeros_like(acc[j - 1])
+            if (i & (mask << (j * lp))) != 0:
+                break
+    while i < n_steps:
+        acc[0] = acc[0] + load(i)
+        i += 1
+    for j in range(1, 4):
+        acc[0] = acc[0] + acc[j]
+    return acc[0]
+
+
+def torch_outer_sum_lastdim(x):
+    """``torch.sum(x, dim=-1, keepdim=True)`` on CPU float32 for x [B, L, C] whose reduced dimension C is
+    STRIDED and whose token dimension L is the contiguous one (e.g. ``conv_out.flatten(2).transpose(1, 2)``,
+    a layout every elementwise op -- QuantAct included -- preserves).  ATen takes its outer-reduction
+    path (SumKernel.cpp ``vectorized_outer_sum``): tokens are processed in blocks of 32 (4 vectors of 8
+    floats; threads split the token range on 32-token boundaries), each summing its C elements
+    sequentially with a cascade every 16 (``multi_row_sum``); the tokens past the last whole block of 32
+    (whole vectors, then scalars) go through ``row_sum`` instead: 4 interleaved accumulators
+    (element e -> e % 4) cascaded the same way, left-overs into accumulator 0, then 1..3 added in order.
+    Verified against torch in tests/test_swin_oracle.py."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    assert x.ndim == 3
+    B, L, C = x.shape
+    out = np.zeros((B, L), dtype=np.float32)
+    nblk = (L // 32) * 32
+    if nblk:
+        xb = x[:, :nblk].reshape(-1, C)
+        out[:, :nblk] = _cascade_rows(xb, C, lambda i: xb[:, i]).reshape(B, nblk)
+    if nblk < L:
+        xt = x[:, nblk:].reshape(-1, C)
+        size_ilp = C // 4
+        ps = _cascade_rows(xt, size_ilp, lambda i: xt[:, 4 * i:4 * i + 4])     # [R, 4]
+        if size_ilp == 0:
+            ps = np.zeros((xt.shape[0], 4), dtype=np.float32)
+        p0 = ps[:, 0].copy()
+        for e in range(size_ilp * 4, C):
+            p0 = p0 + xt[:, e]
+        for k in range(1, 4):
+            p0 = p0 + ps[:, k]
+        out[:, nblk:] = p0.reshape(B, L - nblk)
+    return out[..., None].astype(np.float32)
+
+
+def ivit_layernorm(x, scale, weight, bias, strided_input: bool = False):
+    """ivit_modules.py:30-65 IVITIntLayerNorm.forward.  x: [B,N,C].  strided_input: the reference's
+    tensor is a transposed view (channel stride != 1), which changes torch's float32 summation order
+    of the mean (Swin's patch_embed.norm, layers_quant.py:198-201).
 
     Returns (y float32, scale float32[C], y_int float32 = integer output incl. bias_int)."""
     x = _f32(x)
     C = x.shape[2]
     dim_sqrt = np.sqrt(f32(C)).astype(f32)
     x_int = x / _f32(scale)                                   # :36 un-rounded
-    mean_int = np.rint(torch_sum_lastdim(x_int) / f32(C))     # :37 (mean = sum / C, torch sum order)
+    row_sum = torch_outer_sum_lastdim(x_int) if strided_input else torch_sum_lastdim(x_int)
+    mean_int = np.rint(row_sum / f32(C))                      # :37 (mean = sum / C, torch sum order)
     p = np.trunc(x_int).astype(np.int32)                      # :38 .to(int32) truncates
     mean_i = mean_int.astype(np.int32)
     y_int = p - mean_i                                        # :40

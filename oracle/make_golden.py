@@ -109,6 +109,40 @@ def make_vit_case(name: str) -> dict:
     return out
 
 
+# Swin (BASELINE.json configs[3]): name -> (config, batch, calibration batch, taps stored in full)
+SWIN_CASES = {
+    "swin_toy": ("swin_toy", 2, 4, ("layers.0.blocks.1.attn.qact3", "layers.1.blocks.1.qact4")),
+    "swin_tiny": ("swin_tiny", 2, 2, ("qact3",)),
+}
+
+
+def make_swin_case(name: str) -> dict:
+    """The reference's own swin_quant.SwinTransformer (shimmed import, oracle/ref_shim.load_reference_swin)
+    on the seeded weights: calibrate, freeze, forward with a hook on every quantisation module."""
+    from ivit_b200.synthetic import SWIN_CONFIGS, synth_swin_state
+    cfg_name, batch, calib, full = SWIN_CASES[name]
+    cfg = SWIN_CONFIGS[cfg_name]
+    model = RH.build_reference_swin(cfg, synth_swin_state(cfg, seed=0))
+    RH.calibrate_and_freeze(model, synth_images(calib, cfg, seed=1))
+    ranges = RH.act_ranges(model)
+    logits, taps = RH.run_swin_with_taps(model, synth_images(batch, cfg, seed=0))
+    out = {"logits": logits.astype(f32), "meta": np.array([name, cfg.name, str(batch)])}
+    for k, v in ranges.items():
+        out["range/" + k] = v
+    # memory layout of every LayerNorm input in the reference run (decides torch's float32 summation order)
+    names, code_sha, scale_sha = [], [], []
+    for k, (y, s) in taps.items():
+        names.append(k)
+        code_sha.append(sha(tap_codes(y, s)))
+        scale_sha.append(sha(np.asarray(s, dtype=f32)))
+        if k in full:
+            c = tap_codes(y, s)
+            out["codes/" + k] = c.astype(np.int8 if np.abs(c).max() < 128 else np.int32)
+            out["scale/" + k] = np.asarray(s, dtype=f32)
+    out["tap_names"], out["tap_code_sha"], out["tap_scale_sha"] = np.array(names), np.array(code_sha), np.array(scale_sha)
+    return out
+
+
 def make_modules() -> dict:
     """Known answers of the reference's module functions on seeded inputs."""
     ref = load_reference()
@@ -223,6 +257,13 @@ def main():
             continue
         d = make_vit_case(name)
         path = os.path.join(GOLDEN_DIR, f"vit_{name}.npz")
+        np.savez_compressed(path, **d)
+        print(path, os.path.getsize(path) // 1024, "KiB", len(d["tap_names"]), "taps")
+    for name in SWIN_CASES:
+        if args.only not in (None, name):
+            continue
+        d = make_swin_case(name)
+        path = os.path.join(GOLDEN_DIR, f"swin_{name}.npz")
         np.savez_compressed(path, **d)
         print(path, os.path.getsize(path) // 1024, "KiB", len(d["tap_names"]), "taps")
 

@@ -86,3 +86,48 @@ def run_with_taps(model, images: torch.Tensor, names=None):
     for h in handles:
         h.remove()
     return y.numpy(), taps
+
+
+def build_reference_swin(cfg, state: dict):
+    """The reference's own SwinTransformer (swin_quant.py:419) with our seeded weights."""
+    from functools import partial
+
+    from .ref_shim import give_biasless_linears_a_zero_bias, load_reference_swin
+
+    sw = load_reference_swin()
+    ref = load_reference()
+    import sys
+    qu = sys.modules[ref.__name__ + ".quantization_utils"]
+    model = sw.SwinTransformer(img_size=cfg.img_size, patch_size=cfg.patch_size, in_chans=cfg.in_chans,
+                               num_classes=cfg.num_classes, embed_dim=cfg.embed_dim, depths=cfg.depths,
+                               num_heads=cfg.num_heads, window_size=cfg.window_size, mlp_ratio=float(cfg.mlp_ratio),
+                               norm_layer=partial(qu.IntLayerNorm, eps=1e-6))
+    give_biasless_linears_a_zero_bias(model)
+    missing, unexpected = model.load_state_dict({k: torch.as_tensor(v) for k, v in state.items()}, strict=False)
+    assert not unexpected, unexpected
+    bad = [k for k in missing if k.endswith((".weight", "relative_position_bias_table")) or
+           (k.endswith(".bias") and "reduction" not in k)]
+    assert not bad, bad
+    model.eval()
+    return model
+
+
+def run_swin_with_taps(model, images: torch.Tensor):
+    """Forward with hooks on every leaf quantisation module; returns (logits, {name: (carrier, scale)})."""
+    taps, handles = {}, []
+
+    def mk(name):
+        def hook(mod, inp, out):
+            if isinstance(out, tuple) and len(out) == 2 and torch.is_tensor(out[1]):
+                taps[name] = (out[0].detach().numpy().copy(), out[1].detach().numpy().copy())
+        return hook
+
+    leaf = {"QuantAct", "QuantLinear", "QuantConv2d", "QuantMatMul", "IVITIntLayerNorm", "IVITIntGELU", "IVITIntSoftmax"}
+    for name, mod in model.named_modules():
+        if type(mod).__name__ in leaf:
+            handles.append(mod.register_forward_hook(mk(name)))
+    with torch.no_grad():
+        y = model(images)
+    for h in handles:
+        h.remove()
+    return y.numpy(), taps

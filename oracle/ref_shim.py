@@ -100,3 +100,43 @@ def load_reference_callers_on(qu_package, alias: str = "models_on_b200"):
     vq = importlib.import_module(alias + ".vit_quant")
     mu = importlib.import_module(alias + ".model_utils")
     return vq, mu
+
+
+_SWIN = None
+
+
+def load_reference_swin():
+    """The reference's `models.swin_quant`, importable only with the three fixes of SURVEY.md section 0-2
+    (none of them edits the source): the tkinter stub, the `IntLayerNorm / IntSoftmax / IntGELU` names
+    that `swin_quant.py:11` imports but `quantization_utils/__init__.py` never exported (= the IVIT
+    classes: the only ones whose constructors match the call sites), and -- applied by the caller to
+    each built model, see `give_biasless_linears_a_zero_bias` -- a bias for `PatchMerging.reduction`."""
+    global _SWIN
+    if _SWIN is not None:
+        return _SWIN
+    import importlib
+
+    ref = load_reference()
+    qu = sys.modules[ref.__name__ + ".quantization_utils"]
+    qu.IntLayerNorm, qu.IntSoftmax, qu.IntGELU = qu.IVITIntLayerNorm, qu.IVITIntSoftmax, qu.IVITIntGELU
+    sys.path.insert(0, REFERENCE_ROOT)
+    try:
+        _SWIN = importlib.import_module(ref.__name__ + ".swin_quant")
+    finally:
+        sys.path.remove(REFERENCE_ROOT)
+    return _SWIN
+
+
+def give_biasless_linears_a_zero_bias(model) -> int:
+    """`QuantLinear(..., bias=False)` (swin_quant.py:321-325) crashes in the reference's forward
+    (quant_modules.py:219-220 quantises `self.bias` unconditionally).  A zero bias is arithmetically
+    the upstream behaviour (F.linear without bias): bias_integer = 0 and x + 0.0 == x."""
+    import torch
+
+    n = 0
+    for m in model.modules():
+        if type(m).__name__ == "QuantLinear" and m.bias is None:
+            m.bias = torch.nn.Parameter(torch.zeros(m.out_features))
+            m.register_buffer("bias_integer", torch.zeros(m.out_features))
+            n += 1
+    return n
