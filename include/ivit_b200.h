@@ -89,6 +89,13 @@ int ivit_layernorm_requant_i16_i8(int kind, const int16_t* x, int64_t ldx, int8_
  * out int8 (out_bits 8) or int16 (out_bits 16) = clamp(round(inv_scale * x), qmin, qmax). */
 int ivit_quantize_f32_codes(const float* x, void* out, int out_bits, float inv_scale, int64_t n, int qmin, int qmax,
                             void* stream);
+/* The same LayerNorm + QuantAct when the reference's input tensor is CHANNEL-STRIDED (Swin stage 0: the
+ * layout of `conv.flatten(2).transpose(1, 2)`, layers_quant.py:198, survives every elementwise op up to the
+ * first PatchMerging): torch then sums the mean (ivit_modules.py:37) in its outer-reduction order, which
+ * depends on the token's index within its image (tokens_per_image).  x int8 (x_bits 8) or int16 (16). */
+int ivit_layernorm_requant_strided(int kind, const void* x, int x_bits, int64_t ldx, int8_t* out, int rows, int C,
+                                   float s_in, const float* bias_int, const float* sf, const double* mult, int qmin,
+                                   int qmax, float shift, int use_int_sqrt, int tokens_per_image, void* stream);
 int ivit_fill_cls_rows_i16(int16_t* out, const int16_t* cls_row, int B, int N, int C, void* stream);
 int ivit_requant_codes(const void* z, int z_bits, const float* s_in, const double* mult, int per_channel,
                        const void* identity, int id_bits, int64_t id_rows, double mult_id, void* out, int out_bits,
@@ -193,6 +200,34 @@ int ivit_attention_set_threads_per_row(int tpr);
  * uint16 when output_bit = 16 (`probs` then points to uint16 storage). */
 int ivit_attention_probs_i8(const int8_t* qkv, uint8_t* probs, int B, int N, int H, int hd,
                             const ivit_attention_params_t* p, void* stream);
+
+/* ---- Swin (swin_quant.py) ------------------------------------------------------------------
+ * WindowAttention.forward (:121-169) for every (image, window, head): matmul_1 -> * scale -> qact_attn1
+ * -> qact2 with the quantised relative-position bias as identity (:140-147) -> + shifted-window mask
+ * (0 / -100 added to the float carrier, :149-153; built on the device from :223-247) -> IntSoftmax
+ * (Shiftmax, ivit_modules.py:150-179) -> matmul_2 -> qact3.  Roll and window partition / reverse
+ * (:18-50, :258-289) are index maps inside the kernel: qkv int8 [B, res*res, 3, nH, hd] and out int8
+ * [B, res*res, nH*hd] are in image token order.  bias_codes int8 [nH, ws*ws, ws*ws] = qact_table codes
+ * gathered by relative_position_index.  probs (may be NULL): softmax codes [B*nW, nH, N, N] u8. */
+typedef struct {
+  double mult_attn;          /* qact_attn1: (s_q*s_k*scale) / s_attn1 */
+  int qmin_attn, qmax_attn;
+  double mult2, mult_bias;   /* qact2: s_attn1 / s2 and s_table / s2 (identity branch) */
+  int qmin2, qmax2;
+  float s2;                  /* scale of qact2's output = softmax input */
+  const int8_t* bias_codes;
+  int output_bit;            /* softmax output bits (<= 8) */
+  double mult_out;           /* qact3: (s_softmax*s_v) / s3 */
+  int qmin_out, qmax_out;
+} ivit_window_attention_params_t;
+int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int res, int ws, int shift, int nH,
+                             int hd, const ivit_window_attention_params_t* p, void* stream);
+/* PatchMerging.forward's strided slices + cat (:339-344): [B, res, res, C] -> [B, (res/2)^2, 4C]. */
+int ivit_patch_merge_gather(const void* x, void* out, int elem_bits, int B, int res, int C, void* stream);
+/* AdaptiveAvgPool1d(1) over the tokens of the float carrier + qact3 (:554-555), torch's summation order:
+ * x int8 [B, L, C] with scale s_in -> out int8 [B, C] = clamp(rint(rint(mean / s_in) * mult)). */
+int ivit_avgpool_requant_i8(const int8_t* x, int8_t* out, int B, int L, int C, float s_in, double mult, int qmin,
+                            int qmax, void* stream);
 
 #ifdef __cplusplus
 }

@@ -53,6 +53,20 @@ class AttentionParams(C.Structure):
     ]
 
 
+class WindowAttentionParams(C.Structure):
+    _fields_ = [
+        ("mult_attn", C.c_double),
+        ("qmin_attn", C.c_int), ("qmax_attn", C.c_int),
+        ("mult2", C.c_double), ("mult_bias", C.c_double),
+        ("qmin2", C.c_int), ("qmax2", C.c_int),
+        ("s2", C.c_float),
+        ("bias_codes", C.c_void_p),
+        ("output_bit", C.c_int),
+        ("mult_out", C.c_double),
+        ("qmin_out", C.c_int), ("qmax_out", C.c_int),
+    ]
+
+
 _SIGS = {
     "ivit_abi_version": (C.c_int, []),
     "ivit_device_sm": (C.c_int, [C.POINTER(C.c_int), C.POINTER(C.c_int)]),
@@ -78,6 +92,14 @@ _SIGS = {
                                                 C.c_int, C.c_void_p]),
     "ivit_quantize_f32_codes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_int, C.c_int,
                                           C.c_void_p]),
+    "ivit_layernorm_requant_strided": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_int, C.c_int,
+                                                 C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                                 C.c_float, C.c_int, C.c_int, C.c_void_p]),
+    "ivit_window_attention_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                           C.c_int, C.c_int, C.POINTER(WindowAttentionParams), C.c_void_p]),
+    "ivit_patch_merge_gather": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "ivit_avgpool_requant_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_double,
+                                          C.c_int, C.c_int, C.c_void_p]),
     "ivit_fill_cls_rows_i16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "ivit_requant_codes": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
                                      C.c_int64, C.c_double, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int,

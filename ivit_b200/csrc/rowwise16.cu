@@ -25,27 +25,94 @@ __device__ __forceinline__ int ln16_requant(float v, float sc, double mult, int 
   return static_cast<int>(fmin(fmax(rd, static_cast<double>(qmin)), static_cast<double>(qmax)));
 }
 
-// kind 0: I-ViT, kind 1: I-BERT.  x int16 [rows, C] with row stride ldx ELEMENTS; out int8 [rows, C].
-template <int NPL>
+// torch.sum over a channel-STRIDED row (ATen outer reduction, oracle/ivit_oracle.py::torch_outer_sum_lastdim),
+// evaluated by one lane over the row's x/s values in shared memory.  tail = false: the token lies in a
+// whole block of 32 tokens of its image -> sequential with a cascade every 2^lp elements
+// (multi_row_sum); tail = true: row_sum -> 4 interleaved accumulators cascaded the same way over
+// C/4 steps, left-overs into accumulator 0, then 1..3 added in order.
+__device__ __noinline__ float outer_order_sum(const float* xe, int C, bool tail) {
+  if (!tail) {
+    int cl = 0;
+    while ((1 << cl) < C) ++cl;
+    const int lp = cl / 4 > 4 ? cl / 4 : 4, step = 1 << lp, mask = step - 1;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    int i = 0;
+    while (i + step <= C) {
+      for (int u = 0; u < step; ++u, ++i) acc[0] = __fadd_rn(acc[0], xe[i]);
+      for (int j = 1; j < 4; ++j) {
+        acc[j] = __fadd_rn(acc[j], acc[j - 1]);
+        acc[j - 1] = 0.f;
+        if ((i & (mask << (j * lp))) != 0) break;
+      }
+    }
+    for (; i < C; ++i) acc[0] = __fadd_rn(acc[0], xe[i]);
+    for (int j = 1; j < 4; ++j) acc[0] = __fadd_rn(acc[0], acc[j]);
+    return acc[0];
+  }
+  const int n = C / 4;
+  int cl = 0;
+  while ((1 << cl) < n) ++cl;
+  const int lp = cl / 4 > 4 ? cl / 4 : 4, step = 1 << lp, mask = step - 1;
+  float acc[4][4];
+  for (int j = 0; j < 4; ++j)
+    for (int k = 0; k < 4; ++k) acc[j][k] = 0.f;
+  int i = 0;
+  while (i + step <= n) {
+    for (int u = 0; u < step; ++u, ++i)
+      for (int k = 0; k < 4; ++k) acc[0][k] = __fadd_rn(acc[0][k], xe[4 * i + k]);
+    for (int j = 1; j < 4; ++j) {
+      for (int k = 0; k < 4; ++k) {
+        acc[j][k] = __fadd_rn(acc[j][k], acc[j - 1][k]);
+        acc[j - 1][k] = 0.f;
+      }
+      if ((i & (mask << (j * lp))) != 0) break;
+    }
+  }
+  for (; i < n; ++i)
+    for (int k = 0; k < 4; ++k) acc[0][k] = __fadd_rn(acc[0][k], xe[4 * i + k]);
+  for (int j = 1; j < 4; ++j)
+    for (int k = 0; k < 4; ++k) acc[0][k] = __fadd_rn(acc[0][k], acc[j][k]);
+  float p0 = acc[0][0];
+  for (int e = 4 * n; e < C; ++e) p0 = __fadd_rn(p0, xe[e]);
+  for (int k = 1; k < 4; ++k) p0 = __fadd_rn(p0, acc[0][k]);
+  return p0;
+}
+
+// kind 0: I-ViT, kind 1: I-BERT.  x int16 (or int8) [rows, C] with row stride ldx ELEMENTS; out int8
+// [rows, C].  OUTER: the reference's tensor is channel-strided with `tokens` tokens per image (Swin
+// stage 0: the memory layout of the patch-embedding conv survives every elementwise op up to the
+// first PatchMerging), so torch sums the mean in its outer-reduction order (row % tokens decides
+// between its two forms).
+template <int NPL, typename XT, bool OUTER>
 __global__ void __launch_bounds__(256)
-layernorm_x16_requant_kernel(int kind, const int16_t* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows,
+layernorm_x16_requant_kernel(int kind, const XT* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows,
                              float s_in, const float* __restrict__ bias_int, const float* __restrict__ sf,
                              const double* __restrict__ mult, int qmin, int qmax, float shift_pow, float inv_shift_pow,
-                             int use_int_sqrt) {
+                             int use_int_sqrt, int tokens) {
   constexpr int C = NPL * 32;
   __shared__ __align__(16) int8_t stage[8][C];
+  __shared__ float srow[OUTER ? 8 : 1][OUTER ? C : 1];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= rows) return;
-  const int16_t* xr = x + static_cast<long long>(row) * ldx;
+  const XT* xr = x + static_cast<long long>(row) * ldx;
   float xe[NPL];
   TorchSum32 acc;
 #pragma unroll
   for (int i = 0; i < NPL; ++i) {
     xe[i] = x_eff(static_cast<float>(__ldg(xr + 32 * i + lane)), s_in);       // ivit :36 / ibert :129
     acc.add(xe[i]);
+    if (OUTER) srow[warp][32 * i + lane] = xe[i];
   }
-  const float sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+  float sum_f;
+  if (OUTER) {
+    __syncwarp();
+    float sv = 0.f;
+    if (lane == 0) sv = outer_order_sum(srow[warp], C, (row % tokens) >= (tokens / 32) * 32);
+    sum_f = __shfl_sync(0xffffffffu, sv, 0);
+  } else {
+    sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+  }
   const float mean = rintf(__fdiv_rn(sum_f, static_cast<float>(C)));          // ivit :37 / ibert :130
   float y[NPL];
   float factor;
@@ -171,33 +238,63 @@ static int dispatch_requant(int id_bits, int out_bits, const void* z, const floa
 
 using namespace ivit;
 
-extern "C" int ivit_layernorm_requant_i16_i8(int kind, const int16_t* x, int64_t ldx, int8_t* out, int rows, int C,
-                                             float s_in, const float* bias_int, const float* sf, const double* mult,
-                                             int qmin, int qmax, float shift, int use_int_sqrt, void* stream) {
+template <typename XT>
+static int launch_ln16(int kind, const XT* x, int64_t ldx, int8_t* out, int rows, int C, float s_in,
+                       const float* bias_int, const float* sf, const double* mult, int qmin, int qmax, float shift,
+                       int use_int_sqrt, int strided_tokens, cudaStream_t st) {
   if (rows <= 0) return 0;
   if (kind != 0 && kind != 1) return fail(IVIT_ERR_BAD_ARG, "layernorm16: kind must be 0 (ivit) or 1 (ibert)");
   if (ldx < C) return fail(IVIT_ERR_BAD_ARG, "layernorm16: row stride (elements) must be >= C");
   if (qmin < -128 || qmax > 127) return fail(IVIT_ERR_UNSUPPORTED, "layernorm16: int8 outputs only");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   const float sp = ldexpf(1.f, static_cast<int>(shift));
   const int grid = (rows + 7) / 8;
-#define IVIT_LN16_CASE(c)                                                                                       \
-  case c:                                                                                                       \
-    layernorm_x16_requant_kernel<c / 32><<<grid, 256, 0, st>>>(kind, x, ldx, out, rows, s_in, bias_int, sf, mult, \
-                                                               qmin, qmax, sp, 1.f / sp, use_int_sqrt);         \
+  const bool outer = strided_tokens > 0;
+#define IVIT_LN16_CASE(c, ALLOW_OUTER)                                                                            \
+  case c:                                                                                                         \
+    if (outer) {                                                                                                  \
+      if (!ALLOW_OUTER) return fail(IVIT_ERR_UNSUPPORTED, "layernorm16: channel-strided order for C <= 384 only");  \
+      layernorm_x16_requant_kernel<c / 32, XT, (ALLOW_OUTER)><<<grid, 256, 0, st>>>(                               \
+          kind, x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp, 1.f / sp, use_int_sqrt, strided_tokens); \
+    } else {                                                                                                      \
+      layernorm_x16_requant_kernel<c / 32, XT, false><<<grid, 256, 0, st>>>(                                       \
+          kind, x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp, 1.f / sp, use_int_sqrt, 1);          \
+    }                                                                                                             \
     break;
   switch (C) {
-    IVIT_LN16_CASE(96)
-    IVIT_LN16_CASE(128)
-    IVIT_LN16_CASE(192)
-    IVIT_LN16_CASE(384)
-    IVIT_LN16_CASE(768)
-    IVIT_LN16_CASE(1024)
+    IVIT_LN16_CASE(96, true)
+    IVIT_LN16_CASE(128, true)
+    IVIT_LN16_CASE(192, true)
+    IVIT_LN16_CASE(384, true)
+    IVIT_LN16_CASE(768, false)
+    IVIT_LN16_CASE(1024, false)
+    IVIT_LN16_CASE(1536, false)
     default:
-      return fail(IVIT_ERR_UNSUPPORTED, "layernorm16: C must be one of 96,128,192,384,768,1024");
+      return fail(IVIT_ERR_UNSUPPORTED, "layernorm16: C must be one of 96,128,192,384,768,1024,1536");
   }
 #undef IVIT_LN16_CASE
   return check_launch("layernorm_x16_requant_kernel");
+}
+
+extern "C" int ivit_layernorm_requant_i16_i8(int kind, const int16_t* x, int64_t ldx, int8_t* out, int rows, int C,
+                                             float s_in, const float* bias_int, const float* sf, const double* mult,
+                                             int qmin, int qmax, float shift, int use_int_sqrt, void* stream) {
+  return launch_ln16<int16_t>(kind, x, ldx, out, rows, C, s_in, bias_int, sf, mult, qmin, qmax, shift, use_int_sqrt, 0,
+                              static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ivit_layernorm_requant_strided(int kind, const void* x, int x_bits, int64_t ldx, int8_t* out, int rows,
+                                              int C, float s_in, const float* bias_int, const float* sf,
+                                              const double* mult, int qmin, int qmax, float shift, int use_int_sqrt,
+                                              int tokens_per_image, void* stream) {
+  if (tokens_per_image <= 0) return fail(IVIT_ERR_BAD_ARG, "layernorm (strided order): tokens_per_image must be > 0");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (x_bits == 16)
+    return launch_ln16<int16_t>(kind, static_cast<const int16_t*>(x), ldx, out, rows, C, s_in, bias_int, sf, mult, qmin,
+                                qmax, shift, use_int_sqrt, tokens_per_image, st);
+  if (x_bits == 8)
+    return launch_ln16<int8_t>(kind, static_cast<const int8_t*>(x), ldx, out, rows, C, s_in, bias_int, sf, mult, qmin,
+                               qmax, shift, use_int_sqrt, tokens_per_image, st);
+  return fail(IVIT_ERR_BAD_ARG, "layernorm (strided order): x_bits must be 8 or 16");
 }
 
 extern "C" int ivit_fill_cls_rows_i16(int16_t* out, const int16_t* cls_row, int B, int N, int C, void* stream) {

@@ -1,0 +1,234 @@
+// Swin-specific kernels of the I-ViT integer path (swin_quant.py): window attention with the
+// quantised relative-position bias and the float shifted-window mask, the PatchMerging gather and
+// the token average pool.  First correct version: the window attention runs on the CUDA cores
+// (dp4a) -- a 49 x 49 x 32 window is 0.15 MMAC, ~15 % of Swin-T's MACs; moving it onto tcgen05
+// (two windows per 128-row tile, hd = 32 operands) is the next step for this row.
+//
+// Roll and window partition / reverse (swin_quant.py:18-50, :258-289) are pure index maps: the
+// kernel reads q / k / v of window token (iy, ix) of window (wy, wx) at image token
+// ((wy ws + iy + shift) % res, (wx ws + ix + shift) % res) of the un-permuted [B, L, 3C] qkv
+// buffer and writes its output row to the same token, so no permuted copy ever exists in HBM.
+#include "intmath.cuh"
+#include "ivit_b200.h"
+
+namespace ivit {
+int fail(int code, const char* msg);
+int check_launch(const char* what);
+
+constexpr int WMAX = 64;      // tokens per window (7 x 7 = 49; up to 8 x 8)
+constexpr int HDMAX = 64;
+
+// torch.sum(x, -1) of a contiguous float32 row on CPU (ATen vectorized_inner_sum; see
+// oracle/ivit_oracle.py::torch_sum_lastdim) for n < 512, evaluated by one thread.
+__device__ float torch_row_sum_small(const float* e, int n) {
+  const int nvec = n >> 3, size_ilp = nvec >> 2;
+  float acc[32];
+#pragma unroll
+  for (int l = 0; l < 32; ++l) acc[l] = 0.f;
+  for (int i = 0; i < size_ilp; ++i)          // size_ilp < 16: no cascade step is reached
+#pragma unroll
+    for (int l = 0; l < 32; ++l) acc[l] = __fadd_rn(acc[l], e[32 * i + l]);
+  for (int v = size_ilp * 4; v < nvec; ++v)   // left-over whole vectors go to accumulator row 0
+#pragma unroll
+    for (int l = 0; l < 8; ++l) acc[l] = __fadd_rn(acc[l], e[8 * v + l]);
+#pragma unroll
+  for (int k = 1; k < 4; ++k)
+#pragma unroll
+    for (int l = 0; l < 8; ++l) acc[l] = __fadd_rn(acc[l], acc[8 * k + l]);
+  float fin = 0.f;
+  for (int t = nvec * 8; t < n; ++t) fin = __fadd_rn(fin, e[t]);
+#pragma unroll
+  for (int l = 0; l < 8; ++l) fin = __fadd_rn(fin, acc[l]);
+  return fin;
+}
+
+struct WinAttnArgs {
+  const int8_t* qkv;      // [B, L, 3, nH, hd]
+  int8_t* out;            // [B, L, nH * hd]
+  uint8_t* probs;         // optional tap [B * nW, nH, N, N]
+  int res, ws, shift, nH, hd;
+  ivit_window_attention_params_t p;
+  float x0, nx0, out_shift;
+};
+
+// region label of a rolled coordinate for the shifted-window mask (swin_quant.py:226-236)
+__device__ __forceinline__ int mask_region(int c, int res, int ws, int shift) {
+  return c < res - ws ? 0 : (c < res - shift ? 1 : 2);
+}
+
+__global__ void __launch_bounds__(256)
+window_attention_i8_kernel(const WinAttnArgs a) {
+  __shared__ __align__(16) int8_t sq[WMAX * HDMAX], sk[WMAX * HDMAX], sv[WMAX * HDMAX];
+  __shared__ float sx[WMAX][WMAX + 1];
+  __shared__ uint8_t sp[WMAX][WMAX + 4];
+  __shared__ int tok[WMAX];
+  __shared__ int lab[WMAX];
+  const int ws = a.ws, N = ws * ws, hd = a.hd, res = a.res, nWx = res / ws, nW = nWx * nWx;
+  const int h = blockIdx.x % a.nH;
+  const int w = (blockIdx.x / a.nH) % nW;
+  const int b = blockIdx.x / (a.nH * nW);
+  const int C = a.nH * hd, L = res * res;
+  const int wy = w / nWx, wx = w % nWx;
+  if (threadIdx.x < N) {
+    const int iy = threadIdx.x / ws, ix = threadIdx.x % ws;
+    const int ry = wy * ws + iy, rx = wx * ws + ix;                        // rolled coordinates
+    tok[threadIdx.x] = ((ry + a.shift) % res) * res + (rx + a.shift) % res;
+    lab[threadIdx.x] = 3 * mask_region(ry, res, ws, a.shift) + mask_region(rx, res, ws, a.shift);
+  }
+  __syncthreads();
+  // q, k, v rows of this (window, head): hd bytes each, 4-byte words
+  const int wpr = hd >> 2;
+  for (int t = threadIdx.x; t < 3 * N * wpr; t += blockDim.x) {
+    const int which = t / (N * wpr), r = (t / wpr) % N, c4 = t % wpr;
+    const int8_t* src = a.qkv + (static_cast<long long>(b) * L + tok[r]) * 3 * C + which * C + h * hd + 4 * c4;
+    int8_t* dst = (which == 0 ? sq : which == 1 ? sk : sv) + r * hd + 4 * c4;
+    *reinterpret_cast<int*>(dst) = __ldg(reinterpret_cast<const int*>(src));
+  }
+  __syncthreads();
+  // S = q k^T -> qact_attn1 -> qact2 (+ relative-position bias identity) -> (+ mask) -> x / s
+  const int8_t* bias = a.p.bias_codes + static_cast<long long>(h) * N * N;
+  for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
+    const int i = t / N, j = t % N;
+    int acc = 0;
+    const int* qi = reinterpret_cast<const int*>(sq + i * hd);
+    const int* kj = reinterpret_cast<const int*>(sk + j * hd);
+    for (int c = 0; c < wpr; ++c) acc = __dp4a(qi[c], kj[c], acc);
+    const int c1 = clampi(requant_i32_fast(acc, a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);        // qact_attn1
+    const int c2 = clampi(requant_i32_fast(c1, a.p.mult2) + requant_i32_fast(__ldg(bias + t), a.p.mult_bias),
+                          a.p.qmin2, a.p.qmax2);                                                      // qact2 (:147)
+    float x = __fmul_rn(static_cast<float>(c2), a.p.s2);                   // the float carrier
+    if (a.shift > 0) x = __fadd_rn(x, lab[i] != lab[j] ? -100.f : 0.f);    // attn + mask (:151)
+    sx[i][j] = __fdiv_rn(x, a.p.s2);                                       // ivit_modules.py:165
+  }
+  __syncthreads();
+  // Shiftmax per query row (ivit_modules.py:164-179)
+  if (threadIdx.x < N) {
+    const int i = threadIdx.x;
+    float* row = sx[i];
+    float mx = row[0];
+    for (int j = 1; j < N; ++j) mx = fmaxf(mx, row[j]);
+    ExpShiftParams ep;
+    ep.x0 = a.x0; ep.nx0 = a.nx0; ep.n = 15;
+    for (int j = 0; j < N; ++j) row[j] = exp_shift(__fsub_rn(row[j], mx), ep);
+    float sum = torch_row_sum_small(row, N);
+    sum = fminf(sum, 2147483648.f);                                        // :171-173
+    const float fs = __fmul_rn(floorf(__fdiv_rn(2147483648.f, sum)), a.out_shift);   // :174-175
+    for (int j = 0; j < N; ++j) sp[i][j] = static_cast<uint8_t>(static_cast<int>(floorf(__fmul_rn(row[j], fs))));
+  }
+  __syncthreads();
+  if (a.probs != nullptr) {
+    uint8_t* pr = a.probs + (static_cast<long long>(b * nW + w) * a.nH + h) * N * N;
+    for (int t = threadIdx.x; t < N * N; t += blockDim.x) pr[t] = sp[t / N][t % N];
+  }
+  // O = P v -> qact3, stored at the window token's image position (window_reverse + roll back)
+  if (a.out != nullptr) {
+    for (int t = threadIdx.x; t < N * hd; t += blockDim.x) {
+      const int i = t / hd, d = t % hd;
+      int acc = 0;
+      for (int j = 0; j < N; ++j) acc += static_cast<int>(sp[i][j]) * static_cast<int>(sv[j * hd + d]);
+      const int c = clampi(requant_i32_fast(acc, a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
+      a.out[(static_cast<long long>(b) * L + tok[i]) * C + h * hd + d] = static_cast<int8_t>(c);
+    }
+  }
+}
+
+// PatchMerging gather (swin_quant.py:339-344): [B, res, res, C] -> [B, (res/2)^2, 4C], channel block k
+// of output token (i, j) = input token (2 i + k % 2, 2 j + k / 2).
+template <typename T>
+__global__ void patch_merge_gather_kernel(const T* __restrict__ x, T* __restrict__ out, int B, int res, int C) {
+  const int r2 = res / 2;
+  const long long total = static_cast<long long>(B) * r2 * r2 * 4 * C;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % C);
+    const int k = static_cast<int>((t / C) % 4);
+    const long long tokq = t / (4LL * C);
+    const int j = static_cast<int>(tokq % r2), i = static_cast<int>((tokq / r2) % r2);
+    const int b = static_cast<int>(tokq / (r2 * r2));
+    const long long src = ((static_cast<long long>(b) * res + 2 * i + (k & 1)) * res + 2 * j + (k >> 1)) * C + c;
+    out[t] = x[src];
+  }
+}
+
+// nn.AdaptiveAvgPool1d(1) over the tokens of the float carrier (swin_quant.py:554) followed by qact3:
+// torch computes sum(dim) / L in its outer-reduction order (each output sums its L tokens
+// sequentially, cascading every 2^lp tokens; oracle/swin_oracle.py::avgpool_tokens).
+__global__ void avgpool_requant_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, int B, int L, int C,
+                                       float s_in, double mult, int qmin, int qmax, int lp) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= B * C) return;
+  const int b = t / C, c = t % C;
+  const int8_t* col = x + static_cast<long long>(b) * L * C + c;
+  const int step = 1 << lp, mask = step - 1;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  int i = 0;
+  while (i + step <= L) {
+    for (int u = 0; u < step; ++u, ++i)
+      acc[0] = __fadd_rn(acc[0], __fmul_rn(static_cast<float>(col[static_cast<long long>(i) * C]), s_in));
+    for (int j = 1; j < 4; ++j) {
+      acc[j] = __fadd_rn(acc[j], acc[j - 1]);
+      acc[j - 1] = 0.f;
+      if ((i & (mask << (j * lp))) != 0) break;
+    }
+  }
+  for (; i < L; ++i) acc[0] = __fadd_rn(acc[0], __fmul_rn(static_cast<float>(col[static_cast<long long>(i) * C]), s_in));
+  for (int j = 1; j < 4; ++j) acc[0] = __fadd_rn(acc[0], acc[j]);
+  const float mean = __fdiv_rn(acc[0], static_cast<float>(L));
+  const float z = rintf(__fdiv_rn(mean, s_in));                              // quant_utils.py:220
+  const double r = requant_d(static_cast<double>(z), mult);
+  out[t] = static_cast<int8_t>(static_cast<int>(fmin(fmax(r, static_cast<double>(qmin)), static_cast<double>(qmax))));
+}
+
+}  // namespace ivit
+
+using namespace ivit;
+
+extern "C" int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int res, int ws, int shift,
+                                        int nH, int hd, const ivit_window_attention_params_t* p, void* stream) {
+  if (!p || !p->bias_codes) return fail(IVIT_ERR_BAD_ARG, "window attention: params / bias codes NULL");
+  if (ws < 1 || ws * ws > WMAX || res % ws != 0) return fail(IVIT_ERR_UNSUPPORTED, "window attention: ws^2 <= 64, ws | res");
+  if (hd % 4 != 0 || hd > HDMAX) return fail(IVIT_ERR_UNSUPPORTED, "window attention: head_dim % 4 == 0, <= 64");
+  if (shift < 0 || shift >= ws) return fail(IVIT_ERR_BAD_ARG, "window attention: 0 <= shift < ws");
+  if (p->output_bit < 2 || p->output_bit > 8) return fail(IVIT_ERR_UNSUPPORTED, "window attention: softmax output_bit <= 8");
+  const long long ctas = static_cast<long long>(B) * (res / ws) * (res / ws) * nH;
+  if (ctas <= 0) return 0;
+  if (ctas > 0x7fffffffLL) return fail(IVIT_ERR_UNSUPPORTED, "window attention: too many windows");
+  WinAttnArgs a;
+  a.qkv = qkv; a.out = out; a.probs = probs;
+  a.res = res; a.ws = ws; a.shift = shift; a.nH = nH; a.hd = hd;
+  a.p = *p;
+  a.x0 = floorf(-1.0f / p->s2);                                              // ivit_modules.py:154
+  a.nx0 = 15.f * a.x0;                                                       // :155
+  a.out_shift = 1.f / ldexpf(1.f, 31 - p->output_bit + 1);
+  window_attention_i8_kernel<<<static_cast<int>(ctas), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  return check_launch("window_attention_i8_kernel");
+}
+
+extern "C" int ivit_patch_merge_gather(const void* x, void* out, int elem_bits, int B, int res, int C, void* stream) {
+  if (res % 2 != 0) return fail(IVIT_ERR_BAD_ARG, "patch merge: resolution must be even");
+  const long long total = static_cast<long long>(B) * res * res * C;
+  if (total <= 0) return 0;
+  long long g = (total + 255) / 256;
+  if (g > 148LL * 16) g = 148LL * 16;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (elem_bits == 16)
+    patch_merge_gather_kernel<int16_t><<<static_cast<int>(g), 256, 0, st>>>(static_cast<const int16_t*>(x),
+                                                                            static_cast<int16_t*>(out), B, res, C);
+  else if (elem_bits == 8)
+    patch_merge_gather_kernel<int8_t><<<static_cast<int>(g), 256, 0, st>>>(static_cast<const int8_t*>(x),
+                                                                           static_cast<int8_t*>(out), B, res, C);
+  else
+    return fail(IVIT_ERR_BAD_ARG, "patch merge: elem_bits must be 8 or 16");
+  return check_launch("patch_merge_gather_kernel");
+}
+
+extern "C" int ivit_avgpool_requant_i8(const int8_t* x, int8_t* out, int B, int L, int C, float s_in, double mult,
+                                       int qmin, int qmax, void* stream) {
+  if (B * C <= 0 || L <= 0) return 0;
+  int ceil_log2 = 0;
+  while ((1LL << ceil_log2) < L) ++ceil_log2;
+  const int lp = ceil_log2 / 4 > 4 ? ceil_log2 / 4 : 4;
+  avgpool_requant_kernel<<<(B * C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(x, out, B, L, C, s_in, mult,
+                                                                                          qmin, qmax, lp);
+  return check_launch("avgpool_requant_kernel");
+}

@@ -235,3 +235,57 @@ def attention(qkv: torch.Tensor, B: int, N: int, H: int, hd: int, params: Attent
     if wide:
         probs = probs.to(torch.int32) & 0xffff
     return out, probs
+
+
+def layernorm_requant_strided(kind: int, x: torch.Tensor, tokens_per_image: int, s_in: float, bias_int: torch.Tensor,
+                              sf: torch.Tensor, mult: torch.Tensor, qmin: int, qmax: int, shift: float = 0.0,
+                              use_int_sqrt: bool = False, out: torch.Tensor | None = None) -> torch.Tensor:
+    """LayerNorm + QuantAct whose reference input is channel-strided (Swin stage 0): x int8 / int16 [rows, C]."""
+    assert x.dtype in (torch.int8, torch.int16) and x.dim() == 2 and x.stride(-1) == 1
+    rows, Cdim = x.shape
+    if out is None:
+        out = torch.empty(x.shape, dtype=torch.int8, device=x.device)
+    check(_cabi.load().ivit_layernorm_requant_strided(kind, ptr(x), _BITS[x.dtype], x.stride(0), ptr(out), rows, Cdim,
+                                                      C.c_float(s_in), ptr(bias_int), ptr(sf), ptr(mult), qmin, qmax,
+                                                      C.c_float(shift), int(use_int_sqrt), int(tokens_per_image),
+                                                      stream()), "ivit_layernorm_requant_strided")
+    return out
+
+
+def window_attention(qkv: torch.Tensor, B: int, res: int, ws: int, shift: int, nH: int, hd: int, params,
+                     out: torch.Tensor | None = None, want_probs: bool = False):
+    """Swin window attention on qkv int8 [B, res*res, 3*nH*hd] in image token order (roll / window
+    partition / reverse are index maps inside the kernel) -> out int8 [B, res*res, nH*hd]."""
+    assert qkv.dtype == torch.int8 and qkv.is_contiguous() and qkv.numel() == B * res * res * 3 * nH * hd
+    if out is None:
+        out = torch.empty((B, res * res, nH * hd), dtype=torch.int8, device=qkv.device)
+    assert out.dtype == torch.int8 and out.is_contiguous() and out.numel() == B * res * res * nH * hd
+    probs = None
+    if want_probs:
+        N = ws * ws
+        probs = torch.empty((B * (res // ws) ** 2, nH, N, N), dtype=torch.uint8, device=qkv.device)
+    check(_cabi.load().ivit_window_attention_i8(ptr(qkv), ptr(out), ptr(probs), B, res, ws, shift, nH, hd,
+                                                C.byref(params), stream()), "ivit_window_attention_i8")
+    return (out, probs) if want_probs else out
+
+
+def patch_merge_gather(x: torch.Tensor, B: int, res: int, Cdim: int, out: torch.Tensor | None = None) -> torch.Tensor:
+    """[B, res, res, C] -> [B, (res/2)^2, 4C] (PatchMerging's strided slices + cat)."""
+    assert x.dtype in (torch.int8, torch.int16) and x.is_contiguous() and x.numel() == B * res * res * Cdim
+    if out is None:
+        out = torch.empty((B * (res // 2) ** 2, 4 * Cdim), dtype=x.dtype, device=x.device)
+    assert out.dtype == x.dtype and out.is_contiguous() and out.numel() == x.numel()
+    check(_cabi.load().ivit_patch_merge_gather(ptr(x), ptr(out), _BITS[x.dtype], B, res, Cdim, stream()),
+          "ivit_patch_merge_gather")
+    return out
+
+
+def avgpool_requant(x: torch.Tensor, B: int, L: int, Cdim: int, s_in: float, mult: float, qmin: int, qmax: int,
+                    out: torch.Tensor | None = None) -> torch.Tensor:
+    """Token average pool of the float carrier + QuantAct: x int8 [B, L, C] -> int8 [B, C]."""
+    assert x.dtype == torch.int8 and x.is_contiguous() and x.numel() == B * L * Cdim
+    if out is None:
+        out = torch.empty((B, Cdim), dtype=torch.int8, device=x.device)
+    check(_cabi.load().ivit_avgpool_requant_i8(ptr(x), ptr(out), B, L, Cdim, C.c_float(s_in), C.c_double(mult), qmin,
+                                               qmax, stream()), "ivit_avgpool_requant_i8")
+    return out

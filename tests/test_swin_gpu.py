@@ -1,0 +1,131 @@
+"""GPU parity of the frozen Swin forward (FrozenSwinPlan -> C ABI -> sm_100a kernels) against the numpy
+oracle at every materialised module boundary, and against the committed logits of the unmodified
+reference (tests/golden/swin_*.npz).  Bar: bit-exact integer codes, logits == oracle exactly and within
+1e-6 relative of the reference's float32-carried logits."""
+import numpy as np
+import pytest
+import torch
+
+from ivit_b200 import _cabi, hostmath as hm, ops
+from ivit_b200.swin_plan import FrozenSwinPlan
+from ivit_b200.synthetic import load_swin_case, synth_images
+from oracle import ivit_oracle as O
+from oracle import swin_oracle as SO
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+
+
+def _to_image_order(codes, cfg, i, j, B):
+    """oracle tap of attn.qact3 [B*nW, N, C] (window order) -> [B, L, C] (image token order)."""
+    res, C = cfg.stage_res(i), cfg.stage_dim(i)
+    ws, shift = cfg.block_window_shift(i, j)
+    x = SO.window_reverse(codes.reshape(-1, ws, ws, C), ws, res, res)
+    if shift > 0:
+        x = np.roll(x, (shift, shift), axis=(1, 2))
+    return x.reshape(B, res * res, C)
+
+
+def _run_case(case, batch, seed=0):
+    cfg, state, fix = load_swin_case(case)
+    x = synth_images(batch, cfg, seed=seed)
+    plan = FrozenSwinPlan(cfg, state, "cuda")
+    taps = {}
+    logits = plan.forward(x.cuda(), taps=taps).cpu().numpy()
+    o = SO.SwinOracle(cfg, state)
+    exp_logits = o.forward(x.numpy(), record=True)
+    bad = []
+    for name, t in taps.items():
+        got = t.cpu().numpy().astype(np.int64)
+        if name.endswith(".imgorder"):
+            base = name[:-len(".imgorder")]
+            i, j = int(base.split(".")[1]), int(base.split(".")[3])
+            exp = _to_image_order(SO.codes_of(o.taps[base]), cfg, i, j, batch).astype(np.int64)
+        else:
+            exp = SO.codes_of(o.taps[name]).astype(np.int64).reshape(got.shape)
+        n = int((got != exp).sum())
+        if n:
+            idx = tuple(np.argwhere(got != exp)[0])
+            bad.append(f"{name}: {n}/{got.size} (first {idx}: got {got[idx]} exp {exp[idx]})")
+    assert not bad, f"{case}: {len(bad)}/{len(taps)} boundaries differ:\n" + "\n".join(bad[:12])
+    assert np.array_equal(logits, exp_logits), np.abs(logits - exp_logits).max()
+    return cfg, plan, logits, fix, len(taps)
+
+
+def test_swin_toy_all_boundaries():
+    """Two stages: 14x14 tokens in four 7x7 windows (block 1 shifted, masked), PatchMerging, one 7x7 window."""
+    _, _, logits, fix, ntaps = _run_case("swin_toy", 2)
+    assert ntaps >= 30
+    ref = fix["logits"]
+    assert np.array_equal(logits.argmax(1), ref.argmax(1))
+    assert np.allclose(logits, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
+def test_swin_toy_fresh_inputs_batch3():
+    _run_case("swin_toy", 3, seed=5)
+
+
+def test_swin_tiny_configs3():
+    """BASELINE.json configs[3]: Swin-Tiny INT8 window attention (shifted windows), 224x224."""
+    _, _, logits, fix, ntaps = _run_case("swin_tiny", 2)
+    assert ntaps >= 90
+    ref = fix["logits"]
+    assert np.array_equal(logits.argmax(1), ref.argmax(1))
+    assert np.allclose(logits, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
+def test_swin_tiny_batch_invariance():
+    cfg, state, _ = load_swin_case("swin_tiny")
+    plan = FrozenSwinPlan(cfg, state, "cuda")
+    x = synth_images(8, cfg, seed=3).cuda()
+    full = plan.forward(x).clone()
+    assert torch.equal(plan.forward(x[2:5].contiguous()), full[2:5])
+
+
+def test_patch_merge_gather_and_avgpool():
+    rng = np.random.default_rng(0)
+    B, res, C = 3, 8, 96
+    x = rng.integers(-32768, 32768, size=(B, res, res, C)).astype(np.int16)
+    exp = np.concatenate([x[:, 0::2, 0::2], x[:, 1::2, 0::2], x[:, 0::2, 1::2], x[:, 1::2, 1::2]], axis=-1)
+    got = ops.patch_merge_gather(torch.from_numpy(x).cuda(), B, res, C).cpu().numpy()
+    assert np.array_equal(got.reshape(exp.shape), exp)
+    for L, Cc in ((49, 768), (196, 192), (7, 96)):
+        q = rng.integers(-128, 128, size=(B, L, Cc)).astype(np.int8)
+        s = np.array([f32(0.0371)])
+        xin = (q.astype(f32) * s).astype(f32)
+        pooled = SO.avgpool_tokens(xin)
+        x_max = np.array([np.abs(pooled).max() * 0.8], dtype=f32)
+        _, s_out, codes = O.quant_act(pooled[:, :, None], 8, -x_max, x_max, pre_scale=s)
+        mult = float(hm.dyadic_mult(s, s_out).reshape(-1)[0])
+        got = ops.avgpool_requant(torch.from_numpy(q).cuda(), B, L, Cc, float(s[0]), mult, -128, 127).cpu().numpy()
+        assert np.array_equal(got.astype(np.int64), codes[:, :, 0].astype(np.int64)), (L, Cc)
+
+
+@pytest.mark.parametrize("C,tokens,bits", [(96, 196, 16), (96, 64, 16), (128, 49, 16), (96, 196, 8), (192, 100, 16)])
+def test_layernorm_strided_order(C, tokens, bits):
+    """LayerNorm whose reference input is channel-strided: torch's outer-reduction order of the mean, both
+    forms (whole 32-token blocks / tail tokens).  16-bit codes make the order matter on ordinary rows."""
+    rng = np.random.default_rng(C + tokens)
+    B = 2
+    lim = 2 ** (bits - 1)
+    q = np.clip(np.rint(rng.standard_normal((B, tokens, C)) * lim / 3.5), -lim, lim - 1).astype(np.int64)
+    for r in range(0, tokens, 2):            # exact mean ties on half of the rows
+        d = int(rng.integers(-3, 4)) * C + C // 2 - int(q[0, r].sum())
+        np.add.at(q[0, r], rng.integers(0, C, size=abs(d)), np.sign(d))
+        q[0, r] = np.clip(q[0, r], -lim, lim - 1)
+    s_in = f32(3.1e-4 if bits == 16 else 0.0371)
+    w = (rng.random(C) + 0.5).astype(f32)
+    b = (rng.standard_normal(C) * 0.1).astype(f32)
+    y, sf, _ = O.ivit_layernorm((q.astype(f32) * s_in).astype(f32), np.array([s_in]), w, b, strided_input=True)
+    y_in, _, _ = O.ivit_layernorm((q.astype(f32) * s_in).astype(f32), np.array([s_in]), w, b, strided_input=False)
+    x_max = np.array([np.abs(y).max() * 0.7], dtype=f32)
+    _, s_out, codes = O.quant_act(y, 8, -x_max, x_max, pre_scale=sf)
+    p = hm.layernorm_params(w, b, C)
+    mult = hm.dyadic_mult(p["sf"], s_out)
+    dt = torch.int16 if bits == 16 else torch.int8
+    xt = torch.from_numpy(q.reshape(B * tokens, C)).to(dt).cuda()
+    dev = lambda a, d: torch.from_numpy(np.ascontiguousarray(a)).to(d).cuda()
+    got = ops.layernorm_requant_strided(0, xt, tokens, float(s_in), dev(p["bias_int"], torch.float32),
+                                        dev(p["sf"], torch.float32), dev(mult, torch.float64), -128, 127).cpu().numpy()
+    assert np.array_equal(got.astype(np.int64), codes.reshape(B * tokens, C).astype(np.int64))
+    assert not np.array_equal(y, y_in) or bits == 8     # the two orders really differ on this input
