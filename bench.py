@@ -27,7 +27,36 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 CASE = "deit_small_ivit"           # BASELINE.json configs[1]
-GOP_PER_IMAGE = {"deit_small": 9.198, "deit_tiny": 2.507, "deit_base": 35.128, "vit_base": 35.128, "toy": 0.0}
+GOP_PER_IMAGE = {"deit_small": 9.198, "deit_tiny": 2.507, "deit_base": 35.128, "vit_base": 35.128, "toy": 0.0,
+                 "swin_tiny": 8.981, "swin_toy": 0.0}
+
+
+def load_any_case(case: str):
+    """(cfg, state, oracle class) of a committed ViT/DeiT or Swin case."""
+    if case.startswith("swin"):
+        from ivit_b200.synthetic import load_swin_case
+        from oracle import swin_oracle as SO
+        cfg, state, _ = load_swin_case(case)
+        return cfg, state, SO.SwinOracle
+    from ivit_b200.synthetic import load_case
+    from oracle import vit_oracle as VO
+    cfg, state, _ = load_case(case)
+    return cfg, state, VO.VitOracle
+
+
+def metric_name(case: str) -> str:
+    if case == CASE:
+        return "images/sec DeiT-S INT8 (I-ViT integer forward)"
+    return f"images/sec {case} (I-ViT integer forward)"
+
+
+def describe(case: str, cfg) -> str:
+    if case.startswith("swin"):
+        return (f"{case}: Swin {cfg.img_size}x{cfg.img_size}, depths {cfg.depths}, window {cfg.window_size}, ivit layers, "
+                f"8-bit with the 16-bit residual stream of swin_quant.py, frozen")
+    bw = "8-bit" if all(b == 8 for b in cfg.bitwidths) else f"bit-widths {tuple(cfg.bitwidths)}"
+    return (f"{case}: {cfg.name} {cfg.img_size}x{cfg.img_size}, --gelu {cfg.gelu_type} --softmax {cfg.softmax_type} "
+            f"--layernorm {cfg.layernorm_type}, {bw}, frozen")
 
 
 def parse():
@@ -114,10 +143,9 @@ def cpu_reference_images_per_s(case: str, sample: int, repeats: int = 1):
     reference itself is Python/PyTorch source that cannot travel to the GPU box (no /root/reference
     there), so kind = "port"."""
     import numpy as np
-    from ivit_b200.synthetic import load_case, synth_images
-    from oracle import vit_oracle as VO
-    cfg, state, _ = load_case(case)
-    o = VO.VitOracle(cfg, state)
+    from ivit_b200.synthetic import synth_images
+    cfg, state, Oracle = load_any_case(case)
+    o = Oracle(cfg, state)
     x = synth_images(sample, cfg, seed=0).numpy()
     best = None
     for _ in range(repeats):
@@ -146,12 +174,12 @@ def run_reference(args):
     tot_t = sum(d for _, d in vals)
     value = tot_img / tot_t
     line = {
-        "impl": "reference", "metric": "images/sec DeiT-S INT8 (I-ViT integer forward)", "value": value,
+        "impl": "reference", "metric": metric_name(args.case), "value": value,
         "unit": "images/s", "n_gpus": args.gpus, "steps": len(vals), "warmup": warm,
         "ms_per_step": 1e3 * tot_t / len(vals), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int8", "data": "synthetic",
-        "config": {"workload": f"{args.case}: DeiT-S 224x224 ivit layers, frozen; each step = {args.cpu_sample} "
-                               f"images (bounded sample of the batch-256 workload)", "batch_per_step": args.cpu_sample},
+        "config": {"workload": f"{describe(args.case, cfg)}; each step = {args.cpu_sample} "
+                               f"images (bounded sample of the batch-{args.batch} workload)", "batch_per_step": args.cpu_sample},
         "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": "port",
                          "sample": f"{args.cpu_sample} images/step x {len(vals)} steps, numpy oracle "
                                    f"(float64 BLAS on {cores} threads + float32 elementwise)"},
@@ -192,7 +220,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     from ivit_b200.api import InferenceSession
-    from ivit_b200.synthetic import load_case, synth_images
+    from ivit_b200.synthetic import synth_images
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -204,7 +232,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B = args.batch
-    cfg, state, _ = load_case(args.case)
+    cfg, state, _ = load_any_case(args.case)
     sess = InferenceSession(cfg, state, B, dev, chunks=1)
     plan = sess.plan
     host = synth_images(B, cfg, seed=rank).pin_memory()      # every rank owns a different shard
@@ -311,14 +339,15 @@ def run_ours(args):
     value = world * B * args.steps / (ms * 1e-3)
     gop = GOP_PER_IMAGE.get(cfg.name, 0.0)
     line = {
-        "metric": "images/sec DeiT-S INT8 (I-ViT integer forward)", "value": value, "unit": "images/s",
+        "metric": metric_name(args.case), "value": value, "unit": "images/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
-        "config": {"workload": f"{args.case}: DeiT-S 224x224, --gelu/--softmax/--layernorm ivit, 8-bit, frozen, "
-                               f"batch {B} per GPU", "batch_per_gpu": B, "global_batch": world * B,
+        "config": {"workload": f"{describe(args.case, cfg)}, batch {B} per GPU", "batch_per_gpu": B,
+                   "global_batch": world * B,
                    "parallelism": f"batch-sharded x{world}, logits all-gather only",
-                   "l2": "inputs (154 MB fp32 images) and per-layer activations (19-77 MB each, ~1 GB/step) exceed "
-                         "the 126 MB L2 between iterations",
+                   "l2": f"inputs ({B * 3 * cfg.img_size ** 2 * 4 / 1e6:.0f} MB fp32 images) and the per-layer activations "
+                         f"of the step are streamed between iterations" + (" (19-77 MB each, ~1 GB/step: well beyond the "
+                         "126 MB L2)" if args.case == "deit_small_ivit" and B == 256 else ""),
                    "launch": "CUDA graph replay"},
         "images_per_s_per_gpu": value / world,
         "tensor_frac_whole_step": value / world * gop * 1e9 / (int8_peak * 1e12),

@@ -1,6 +1,6 @@
 """Public inference call: host images in, host logits out.
 
-``InferenceSession`` owns one ``FrozenVitPlan`` on one GPU and what a serving loop needs around
+``InferenceSession`` owns one ``FrozenVitPlan`` (or ``FrozenSwinPlan``) on one GPU and what a serving loop needs around
 it: CUDA-graph replays of the launch sequence, a copy stream, and rotating staging slots so that
 the host->device copy of the next chunk (or the next call) overlaps the forward in flight.  This is the
 call ``bench.py`` times as ``e2e`` and the one ``scripts/inference.py:248`` (``model(imgs)`` per
@@ -11,11 +11,12 @@ from __future__ import annotations
 import torch
 
 from .plan import FrozenVitPlan
-from .synthetic import VitConfig
+from .swin_plan import FrozenSwinPlan
+from .synthetic import SwinConfig, VitConfig
 
 
 class InferenceSession:
-    def __init__(self, cfg: VitConfig, state: dict, batch: int, device="cuda", chunks: int = 1, slots: int = 2):
+    def __init__(self, cfg: "VitConfig | SwinConfig", state: dict, batch: int, device="cuda", chunks: int = 1, slots: int = 2):
         """batch images per call, processed as `chunks` equal forwards; `slots` staging slots (each a
         captured graph with its own input buffer) rotate across chunks AND calls, so with slots >= 2
         the host->device copy of the next chunk / next call overlaps the forward in flight."""
@@ -23,7 +24,7 @@ class InferenceSession:
             raise ValueError("batch must be divisible by chunks")
         if slots < 1:
             raise ValueError("slots must be >= 1")
-        self.plan = FrozenVitPlan(cfg, state, device)
+        self.plan = FrozenSwinPlan(cfg, state, device) if isinstance(cfg, SwinConfig) else FrozenVitPlan(cfg, state, device)
         self.device = self.plan.device
         self.batch, self.chunks, self.cb = batch, chunks, batch // chunks
         self.compute = torch.cuda.Stream(device=self.device)

@@ -102,7 +102,46 @@ def _layer_kind(name: str) -> int:
     raise NotImplementedError(f"layer type {name!r}: this plan covers the ivit|ibert registry entries")
 
 
-class FrozenVitPlan:
+class GraphCaptureMixin:
+    """Launch accounting and CUDA-graph capture shared by the frozen plans (`_enqueue(images)` enqueues one
+    forward on torch's current stream)."""
+
+    def _mark(self, kernel: str, ops_: float, bytes_: float):
+        """One kernel launched.  With ``self.trace`` set (bench.py's per-kernel pass) a CUDA event is
+        recorded after it, with the launch's ALGORITHMIC work: integer ops (1 MAC = 2) and the bytes
+        of every operand read once + every result written once."""
+        self.launches_per_forward += 1
+        if self.trace is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self.trace.append((kernel, float(ops_), float(bytes_), ev))
+
+    def capture(self, B: int, slot: int = 0) -> "GraphedForward":
+        """Capture the launch sequence for batch B into a CUDA graph over a static input buffer.
+        Graphs of different ``slot`` have their own input buffer but share the activation buffers
+        (replay them on one stream)."""
+        if (B, slot) in self._graphs:
+            return self._graphs[(B, slot)]
+        cfg = self.cfg
+        static_in = torch.zeros((B, cfg.in_chans, cfg.img_size, cfg.img_size), dtype=torch.float32,
+                                device=self.device)
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):           # warm-up: cudaFuncSetAttribute etc. outside capture
+            self._enqueue(static_in)
+            self._enqueue(static_in)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            out = self._enqueue(static_in)
+        gf = GraphedForward(g, static_in, out, self.launches_per_forward)
+        self._graphs[(B, slot)] = gf
+        return gf
+
+
+
+class FrozenVitPlan(GraphCaptureMixin):
     """Host-side constants + launch sequence of one frozen ViT/DeiT model.
 
     cfg: ``VitConfig``; state: reference ``state_dict`` names -> arrays (weights, biases,
@@ -321,16 +360,6 @@ class FrozenVitPlan:
         return bufs
 
     # ------------------------------------------------------------------ launch sequence
-    def _mark(self, kernel: str, ops_: float, bytes_: float):
-        """One kernel launched.  With ``self.trace`` set (bench.py's per-kernel pass) a CUDA event is
-        recorded after it, with the launch's ALGORITHMIC work: integer ops (1 MAC = 2) and the bytes
-        of every operand read once + every result written once."""
-        self.launches_per_forward += 1
-        if self.trace is not None:
-            ev = torch.cuda.Event(enable_timing=True)
-            ev.record()
-            self.trace.append((kernel, float(ops_), float(bytes_), ev))
-
     def _gemm(self, A, lin: _Linear, epilogue, out, name="gemm", **kw):
         r = ops.gemm(A, lin.w, epilogue, bias=lin.bias, mult=lin.mult, s_in=lin.b_scale, qmin=lin.qmin,
                      qmax=lin.qmax, mult2=lin.mult2, mult_id=lin.mult_id, qmin2=lin.qmin2, qmax2=lin.qmax2,
@@ -407,30 +436,6 @@ class FrozenVitPlan:
         return self._enqueue(images, taps, blocks)
 
     __call__ = forward
-
-    # ------------------------------------------------------------------ CUDA graph
-    def capture(self, B: int, slot: int = 0) -> "GraphedForward":
-        """Capture the launch sequence for batch B into a CUDA graph over a static input buffer.
-        Graphs of different ``slot`` have their own input buffer but share the activation buffers
-        (replay them on one stream)."""
-        if (B, slot) in self._graphs:
-            return self._graphs[(B, slot)]
-        cfg = self.cfg
-        static_in = torch.zeros((B, cfg.in_chans, cfg.img_size, cfg.img_size), dtype=torch.float32,
-                                device=self.device)
-        side = torch.cuda.Stream(device=self.device)
-        side.wait_stream(torch.cuda.current_stream(self.device))
-        with torch.cuda.stream(side):           # warm-up: cudaFuncSetAttribute etc. outside capture
-            self._enqueue(static_in)
-            self._enqueue(static_in)
-        torch.cuda.current_stream(self.device).wait_stream(side)
-        torch.cuda.synchronize(self.device)
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            out = self._enqueue(static_in)
-        gf = GraphedForward(g, static_in, out, self.launches_per_forward)
-        self._graphs[(B, slot)] = gf
-        return gf
 
 
 class GraphedForward:

@@ -31,7 +31,7 @@ import torch
 
 from . import _cabi, hostmath as hm, ops
 from ._cabi import EPI_LOGITS, EPI_REQUANT, EPI_RESIDUAL, WindowAttentionParams
-from .plan import _Linear, _Norm, _np
+from .plan import GraphCaptureMixin, _Linear, _Norm, _np
 from .synthetic import SwinConfig
 
 f32 = np.float32
@@ -47,7 +47,7 @@ def relative_position_index(ws: int) -> np.ndarray:
     return rel.sum(-1)
 
 
-class FrozenSwinPlan:
+class FrozenSwinPlan(GraphCaptureMixin):
     def __init__(self, cfg: SwinConfig, state: dict, device="cuda", host_only: bool = False):
         self.cfg, self.host_only = cfg, host_only
         self.device = torch.device("cpu" if host_only else device)
@@ -56,8 +56,9 @@ class FrozenSwinPlan:
         if not host_only:
             _cabi.load()
         self.sd = {k: _np(v) for k, v in state.items() if not k.endswith(("weight_integer", "bias_integer"))}
-        self._bufs, self._keep = {}, []
+        self._bufs, self._keep, self._graphs = {}, [], {}
         self.launches_per_forward = 0
+        self.trace = None
         self._build()
 
     # ------------------------------------------------------------------ host constants
@@ -222,19 +223,33 @@ class FrozenSwinPlan:
 
     # ------------------------------------------------------------------ launch sequence
     def _gemm(self, A, lin: _Linear, epilogue, out, **kw):
-        self.launches_per_forward += 1
-        return ops.gemm(A, lin.w, epilogue, bias=lin.bias, mult=lin.mult, s_in=lin.b_scale, qmin=lin.qmin, qmax=lin.qmax,
-                        mult2=lin.mult2, mult_id=lin.mult_id, qmin2=lin.qmin2, qmax2=lin.qmax2, out=out,
-                        force_slow=lin.force_slow, z_bound_ok=lin.z_bound_ok, **kw)
+        r = ops.gemm(A, lin.w, epilogue, bias=lin.bias, mult=lin.mult, s_in=lin.b_scale, qmin=lin.qmin, qmax=lin.qmax,
+                     mult2=lin.mult2, mult_id=lin.mult_id, qmin2=lin.qmin2, qmax2=lin.qmax2, out=out,
+                     force_slow=lin.force_slow, z_bound_ok=lin.z_bound_ok, **kw)
+        M, K = A.shape
+        Nn = lin.w.shape[0]
+        idn = kw.get("identity")
+        by = (M * K + Nn * K + M * Nn * out.element_size() + Nn * 16 +
+              (M * Nn * idn.element_size() if idn is not None else 0))
+        self._mark("gemm_i8_tc", 2.0 * M * Nn * K, by)
+        return r
 
     def _ln(self, x, s_in, nm: _Norm, out, strided_tokens=0):
-        self.launches_per_forward += 1
         if strided_tokens:
-            return ops.layernorm_requant_strided(0, x, strided_tokens, float(s_in), nm.bias_int, nm.sf, nm.mult, nm.qmin,
-                                                 nm.qmax, out=out)
-        return ops.layernorm_requant(0, x, float(s_in), nm.bias_int, nm.sf, nm.mult, nm.qmin, nm.qmax, out=out)
+            r = ops.layernorm_requant_strided(0, x, strided_tokens, float(s_in), nm.bias_int, nm.sf, nm.mult, nm.qmin,
+                                              nm.qmax, out=out)
+        else:
+            r = ops.layernorm_requant(0, x, float(s_in), nm.bias_int, nm.sf, nm.mult, nm.qmin, nm.qmax, out=out)
+        self._mark("layernorm_requant", 0, (1 + x.element_size()) * out.numel() + 16 * x.shape[-1])
+        return r
 
     def forward(self, images: torch.Tensor, taps: dict | None = None) -> torch.Tensor:
+        """Eager launch sequence.  Returns float32 logits [B, classes] (a view of the plan's buffer)."""
+        return self._enqueue(images, taps)
+
+    __call__ = forward
+
+    def _enqueue(self, images: torch.Tensor, taps: dict | None = None) -> torch.Tensor:
         cfg = self.cfg
         if self.host_only or not images.is_cuda or images.dtype != torch.float32:
             raise _cabi.IvitKernelError("images must be a float32 CUDA tensor (there is no CPU fallback)")
@@ -249,13 +264,14 @@ class FrozenSwinPlan:
         L, C = cfg.grid ** 2, cfg.embed_dim
         M = B * L
         ops.quantize_patches(images, self.inv_s_input, cfg.patch_size, out=bufs["patches"])
+        self._mark("quantize_patches", 0, 5 * images.numel())
         self._gemm(bufs["patches"], self.patch, EPI_REQUANT, bufs["pe"])
         tap("patch_embed.qact_before_norm", bufs["pe"], (B, L, C))
         self._ln(bufs["pe"], self.s_bn, self.patch_norm, bufs["pe2"], strided_tokens=L)
         tap("patch_embed.qact", bufs["pe2"], (B, L, C))
         x = bufs["x"][:M * C].view(M, C)
         ops.requant(bufs["pe2"], self.stem_s_in, self.stem_mult, -32768, 32767, out=x, out_bits=16)
-        self.launches_per_forward += 3
+        self._mark("requant_codes", 0, 3 * x.numel())
         tap("qact1", x, (B, L, C))
         cur, other = "x", "xm"
         for i, st in enumerate(self.stages):
@@ -276,7 +292,7 @@ class FrozenSwinPlan:
                 tap(p + "qact1", ln, (B, L, C))
                 self._gemm(ln, b["qkv"], EPI_REQUANT, qkv)
                 ops.window_attention(qkv, B, res, b["ws"], b["shift"], nH, C // nH, b["attn"], out=attn)
-                self.launches_per_forward += 1
+                self._mark("window_attention_i8", 4.0 * M * b["ws"] ** 2 * C, 4 * M * C)
                 tap(p + "attn.qact3.imgorder", attn, (B, L, C))
                 self._gemm(attn, b["proj"], EPI_RESIDUAL, x_mid, identity=x)
                 tap(p + "qact2", x_mid, (B, L, C))
@@ -285,7 +301,7 @@ class FrozenSwinPlan:
                 self._gemm(ln, b["fc1"], EPI_REQUANT, h1)
                 tap(p + "mlp.qact_gelu", h1, (B, L, Hd))
                 ops.gelu_lut_apply(h1, b["gelu_lut"], out=h2)
-                self.launches_per_forward += 1
+                self._mark("gelu_lut_apply", 0, 2 * h1.numel())
                 tap(p + "mlp.qact1", h2, (B, L, Hd))
                 self._gemm(h2, b["fc2"], EPI_RESIDUAL, x, identity=x_mid)
                 tap(p + "qact4", x, (B, L, C))
@@ -294,7 +310,7 @@ class FrozenSwinPlan:
                 Mq = M // 4
                 xm = bufs[other][:M * C].view(Mq, 4 * C)
                 ops.patch_merge_gather(x, B, res, C, out=xm)
-                self.launches_per_forward += 1
+                self._mark("patch_merge_gather", 0, 4 * x.numel())
                 ln4 = bufs["ln"][:Mq * 4 * C].view(Mq, 4 * C)
                 self._ln(xm, st["merge_s_in"], st["merge_norm"], ln4)
                 tap(d + "qact1", ln4, (B, L // 4, 4 * C))
@@ -309,9 +325,7 @@ class FrozenSwinPlan:
         self._ln(x, self.s_final_in, self.norm, ln)
         tap("qact2", ln, (B, L, C))
         ops.avgpool_requant(ln, B, L, C, self.pool_s_in, self.pool_mult, -128, 127, out=bufs["pool"])
-        self.launches_per_forward += 1
+        self._mark("avgpool_requant", 0, ln.numel() + B * C)
         tap("qact3", bufs["pool"], (B, C))
         self._gemm(bufs["pool"], self.head, EPI_LOGITS, bufs["logits"], scale_out=self.head.b_scale)
         return bufs["logits"]
-
-    __call__ = forward
