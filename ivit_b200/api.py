@@ -77,9 +77,33 @@ class InferenceSession:
         return out
 
 
-def config_from_model(model) -> VitConfig:
-    """VitConfig of a VisionTransformer built on the quantization_utils module API (the reference's
-    vit_quant.py class or any caller with the same attribute names)."""
+def swin_config_from_model(model) -> SwinConfig:
+    """SwinConfig of a swin_quant.SwinTransformer (or any caller with the same attribute names) built on
+    the quantization_utils module API.  The layer types and bit-widths are the ones swin_quant.py
+    hard-codes (IntLayerNorm / IntSoftmax / IntGELU = the I-ViT classes; 16-bit residual stream)."""
+    stages = list(model.layers)
+    b0 = stages[0].blocks[0]
+    for st in stages:
+        for blk in st.blocks:
+            if getattr(blk.norm1, "_kind", 0) != 0 or getattr(blk.attn.log_int_softmax, "_kind", 0) != 0 or \
+                    getattr(blk.mlp.act, "_kind", 0) != 0:
+                raise NotImplementedError("FrozenSwinPlan covers the I-ViT layer types swin_quant.py is written for")
+            if (blk.qact2.activation_bit, blk.qact4.activation_bit, blk.attn.qact4.activation_bit) != (16, 16, 16):
+                raise NotImplementedError("FrozenSwinPlan: the 16-bit residual stream of swin_quant.py:110,214,222")
+    pe = model.patch_embed
+    ws = max(blk.window_size for st in stages for blk in st.blocks)
+    return SwinConfig(name="custom", embed_dim=pe.proj.out_channels, depths=tuple(len(st.blocks) for st in stages),
+                      num_heads=tuple(st.blocks[0].attn.num_heads for st in stages), window_size=int(ws),
+                      mlp_ratio=b0.mlp.fc1.out_features // b0.mlp.fc1.in_features, img_size=int(pe.img_size[0]),
+                      patch_size=int(pe.proj.kernel_size[0]), in_chans=pe.proj.in_channels,
+                      num_classes=model.head.out_features)
+
+
+def config_from_model(model):
+    """VitConfig (or SwinConfig) of a model built on the quantization_utils module API (the reference's
+    vit_quant.py / swin_quant.py classes or any caller with the same attribute names)."""
+    if hasattr(model, "layers") and not hasattr(model, "blocks"):
+        return swin_config_from_model(model)
     blk = model.blocks[0]
     C = model.head.in_features
     P = model.patch_embed.proj.kernel_size[0]

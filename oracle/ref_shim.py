@@ -102,6 +102,15 @@ def load_reference_callers_on(qu_package, alias: str = "models_on_b200"):
     return vq, mu
 
 
+def load_reference_swin_on(qu_package, alias: str = "models_on_b200"):
+    """The reference's UNMODIFIED swin_quant.py on `qu_package`: needs only the tkinter stub -- the package
+    itself exports `IntLayerNorm / IntSoftmax / IntGELU` and accepts `QuantLinear(bias=False)`."""
+    import importlib
+
+    load_reference_callers_on(qu_package, alias)
+    return importlib.import_module(alias + ".swin_quant")
+
+
 _SWIN = None
 
 

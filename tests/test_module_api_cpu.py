@@ -91,6 +91,52 @@ def test_reference_vit_quant_runs_unchanged_and_calibrates_identically(case):
         model(synth_images(1, cfg, seed=0))
 
 
+@pytest.mark.reference
+def test_reference_swin_quant_runs_unchanged_and_calibrates_identically():
+    """north_star: swin_quant.py runs unchanged on this package (the reference's own
+    quantization_utils cannot run it -- missing Int* exports, bias=False crash).  Same weights, same
+    calibration batch as oracle/make_golden.py: every calibrated range equals the (shimmed) reference's,
+    i.e. the float-simulated path reproduces it through roll / window partition / bias gather / mask /
+    PatchMerging / average pool."""
+    from functools import partial
+    from ivit_b200.synthetic import load_swin_case
+    from oracle.ref_shim import load_reference_swin_on
+    sw = load_reference_swin_on(qu)
+    cfg, state, fix = load_swin_case("swin_toy")
+    model = sw.SwinTransformer(img_size=cfg.img_size, patch_size=cfg.patch_size, in_chans=cfg.in_chans,
+                               num_classes=cfg.num_classes, embed_dim=cfg.embed_dim, depths=cfg.depths,
+                               num_heads=cfg.num_heads, window_size=cfg.window_size, mlp_ratio=float(cfg.mlp_ratio),
+                               norm_layer=partial(qu.IntLayerNorm, eps=1e-6))
+    assert isinstance(model.layers[0].blocks[0].attn.qkv, qu.QuantLinear)
+    assert model.layers[0].downsample.reduction.bias is None
+    weights = {k: torch.as_tensor(v) for k, v in state.items() if not k.endswith((".x_min", ".x_max"))}
+    missing, unexpected = model.load_state_dict(weights, strict=False)
+    assert not unexpected
+    assert not [k for k in missing if k.endswith((".weight", ".bias", "relative_position_bias_table"))], missing
+    model.eval()
+    with torch.no_grad():
+        logits = model(synth_images(4, cfg, seed=1))
+    assert logits.shape == (4, cfg.num_classes) and torch.isfinite(logits).all()
+    sd = model.state_dict()
+    n = 0
+    for k in fix.files:
+        if k.startswith("range/"):
+            name = k[len("range/"):]
+            assert np.array_equal(sd[name].reshape(-1).numpy().astype(f32), fix[k].astype(f32)), name
+            n += 1
+    assert n >= 80
+    # the calibrated, frozen model maps onto the fused static plan (compile_frozen's host half)
+    from ivit_b200.api import config_from_model
+    from ivit_b200.swin_plan import FrozenSwinPlan
+    got = config_from_model(model)
+    import dataclasses
+    assert dataclasses.replace(got, name=cfg.name) == cfg
+    plan = FrozenSwinPlan(got, model.state_dict(), host_only=True)
+    want = FrozenSwinPlan(cfg, state, host_only=True)
+    assert plan.pool_mult == want.pool_mult and plan.stages[1]["blocks"][1]["proj"].mult2 == \
+        want.stages[1]["blocks"][1]["proj"].mult2
+
+
 def _build_pair(case):
     """The reference's VisionTransformer twice: on its own quantization_utils and on ours, same weights."""
     from oracle.ref_shim import load_reference, load_reference_callers_on
