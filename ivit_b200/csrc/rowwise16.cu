@@ -107,9 +107,28 @@ layernorm_x16_requant_kernel(int kind, const XT* __restrict__ x, long long ldx, 
   float sum_f;
   if (OUTER) {
     __syncwarp();
-    float sv = 0.f;
-    if (lane == 0) sv = outer_order_sum(srow[warp], C, (row % tokens) >= (tokens / 32) * 32);
-    sum_f = __shfl_sync(0xffffffffu, sv, 0);
+    if ((row % tokens) >= (tokens / 32) * 32) {          // warp-uniform; tail tokens of an image only (row_sum form)
+      float sv = 0.f;
+      if (lane == 0) sv = outer_order_sum(srow[warp], C, true);
+      sum_f = __shfl_sync(0xffffffffu, sv, 0);
+    } else {
+      // multi_row_sum form, in parallel: the cascade adds whole groups of 16 elements (each summed
+      // sequentially from zero) into the level-1 accumulator, and 16 of those into level 2 -- lane g sums
+      // group g, then the groups are combined in order (C <= 384: at most 24 groups, two levels)
+      constexpr int G = C / 16;
+      float sg = 0.f;
+      if (lane < G) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) sg = __fadd_rn(sg, srow[warp][16 * lane + u]);
+      }
+      float a1 = 0.f, a2 = 0.f;
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        a1 = __fadd_rn(a1, __shfl_sync(0xffffffffu, sg, g));
+        if (((g + 1) & 15) == 0) { a2 = __fadd_rn(a2, a1); a1 = 0.f; }
+      }
+      sum_f = __fadd_rn(__fadd_rn(0.f, a1), a2);           // acc[0] (empty: C % 16 == 0) += acc[1]; += acc[2]
+    }
   } else {
     sum_f = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
   }

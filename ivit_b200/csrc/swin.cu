@@ -56,19 +56,32 @@ __device__ __forceinline__ int mask_region(int c, int res, int ws, int shift) {
   return c < res - ws ? 0 : (c < res - shift ? 1 : 2);
 }
 
+// a: four unsigned bytes, b: four signed bytes
+__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+
+constexpr int QK_LD = HDMAX + 4;      // row pitch of q / k in shared memory (words: odd multiple -> no bank conflicts)
+constexpr int VT_LD = WMAX + 4;       // row pitch of v^T and of the probability rows
+
 __global__ void __launch_bounds__(256)
 window_attention_i8_kernel(const WinAttnArgs a) {
-  __shared__ __align__(16) int8_t sq[WMAX * HDMAX], sk[WMAX * HDMAX], sv[WMAX * HDMAX];
+  __shared__ __align__(16) int8_t sq[WMAX * QK_LD], sk[WMAX * QK_LD];
+  __shared__ __align__(16) int8_t svt[HDMAX * VT_LD];        // v transposed: [d][token]
   __shared__ float sx[WMAX][WMAX + 1];
-  __shared__ uint8_t sp[WMAX][WMAX + 4];
+  __shared__ __align__(16) uint8_t sp[WMAX][VT_LD];
   __shared__ int tok[WMAX];
   __shared__ int lab[WMAX];
+  __shared__ float srow[WMAX];                               // row max, then the row's factor
   const int ws = a.ws, N = ws * ws, hd = a.hd, res = a.res, nWx = res / ws, nW = nWx * nWx;
   const int h = blockIdx.x % a.nH;
   const int w = (blockIdx.x / a.nH) % nW;
   const int b = blockIdx.x / (a.nH * nW);
   const int C = a.nH * hd, L = res * res;
   const int wy = w / nWx, wx = w % nWx;
+  const int N4 = (N + 3) & ~3;
   if (threadIdx.x < N) {
     const int iy = threadIdx.x / ws, ix = threadIdx.x % ws;
     const int ry = wy * ws + iy, rx = wx * ws + ix;                        // rolled coordinates
@@ -76,22 +89,27 @@ window_attention_i8_kernel(const WinAttnArgs a) {
     lab[threadIdx.x] = 3 * mask_region(ry, res, ws, a.shift) + mask_region(rx, res, ws, a.shift);
   }
   __syncthreads();
-  // q, k, v rows of this (window, head): hd bytes each, 4-byte words
+  // q, k rows and v^T of this (window, head): hd bytes per token, 4-byte words
   const int wpr = hd >> 2;
   for (int t = threadIdx.x; t < 3 * N * wpr; t += blockDim.x) {
     const int which = t / (N * wpr), r = (t / wpr) % N, c4 = t % wpr;
     const int8_t* src = a.qkv + (static_cast<long long>(b) * L + tok[r]) * 3 * C + which * C + h * hd + 4 * c4;
-    int8_t* dst = (which == 0 ? sq : which == 1 ? sk : sv) + r * hd + 4 * c4;
-    *reinterpret_cast<int*>(dst) = __ldg(reinterpret_cast<const int*>(src));
+    const int v = __ldg(reinterpret_cast<const int*>(src));
+    if (which < 2) {
+      *reinterpret_cast<int*>((which == 0 ? sq : sk) + r * QK_LD + 4 * c4) = v;
+    } else {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) svt[(4 * c4 + u) * VT_LD + r] = static_cast<int8_t>(v >> (8 * u));
+    }
   }
   __syncthreads();
   // S = q k^T -> qact_attn1 -> qact2 (+ relative-position bias identity) -> (+ mask) -> x / s
   const int8_t* bias = a.p.bias_codes + static_cast<long long>(h) * N * N;
   for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
-    const int i = t / N, j = t % N;
+    const int i = t / N, j = t - i * N;
     int acc = 0;
-    const int* qi = reinterpret_cast<const int*>(sq + i * hd);
-    const int* kj = reinterpret_cast<const int*>(sk + j * hd);
+    const int* qi = reinterpret_cast<const int*>(sq + i * QK_LD);
+    const int* kj = reinterpret_cast<const int*>(sk + j * QK_LD);
     for (int c = 0; c < wpr; ++c) acc = __dp4a(qi[c], kj[c], acc);
     const int c1 = clampi(requant_i32_fast(acc, a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);        // qact_attn1
     const int c2 = clampi(requant_i32_fast(c1, a.p.mult2) + requant_i32_fast(__ldg(bias + t), a.p.mult_bias),
@@ -101,19 +119,32 @@ window_attention_i8_kernel(const WinAttnArgs a) {
     sx[i][j] = __fdiv_rn(x, a.p.s2);                                       // ivit_modules.py:165
   }
   __syncthreads();
-  // Shiftmax per query row (ivit_modules.py:164-179)
+  // Shiftmax (ivit_modules.py:164-179): row max | exp terms (all threads) | torch-order row sum | codes
   if (threadIdx.x < N) {
-    const int i = threadIdx.x;
-    float* row = sx[i];
+    const float* row = sx[threadIdx.x];
     float mx = row[0];
     for (int j = 1; j < N; ++j) mx = fmaxf(mx, row[j]);
+    srow[threadIdx.x] = mx;
+  }
+  __syncthreads();
+  {
     ExpShiftParams ep;
     ep.x0 = a.x0; ep.nx0 = a.nx0; ep.n = 15;
-    for (int j = 0; j < N; ++j) row[j] = exp_shift(__fsub_rn(row[j], mx), ep);
-    float sum = torch_row_sum_small(row, N);
+    for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
+      const int i = t / N, j = t - i * N;
+      sx[i][j] = exp_shift(__fsub_rn(sx[i][j], srow[i]), ep);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < N) {
+    float sum = torch_row_sum_small(sx[threadIdx.x], N);
     sum = fminf(sum, 2147483648.f);                                        // :171-173
-    const float fs = __fmul_rn(floorf(__fdiv_rn(2147483648.f, sum)), a.out_shift);   // :174-175
-    for (int j = 0; j < N; ++j) sp[i][j] = static_cast<uint8_t>(static_cast<int>(floorf(__fmul_rn(row[j], fs))));
+    srow[threadIdx.x] = __fmul_rn(floorf(__fdiv_rn(2147483648.f, sum)), a.out_shift);   // :174-175
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < N * N4; t += blockDim.x) {
+    const int i = t / N4, j = t - i * N4;
+    sp[i][j] = j < N ? static_cast<uint8_t>(static_cast<int>(floorf(__fmul_rn(sx[i][j], srow[i])))) : uint8_t(0);
   }
   __syncthreads();
   if (a.probs != nullptr) {
@@ -123,9 +154,11 @@ window_attention_i8_kernel(const WinAttnArgs a) {
   // O = P v -> qact3, stored at the window token's image position (window_reverse + roll back)
   if (a.out != nullptr) {
     for (int t = threadIdx.x; t < N * hd; t += blockDim.x) {
-      const int i = t / hd, d = t % hd;
+      const int i = t / hd, d = t - i * hd;
+      const uint32_t* pi = reinterpret_cast<const uint32_t*>(sp[i]);
+      const int* vd = reinterpret_cast<const int*>(svt + d * VT_LD);
       int acc = 0;
-      for (int j = 0; j < N; ++j) acc += static_cast<int>(sp[i][j]) * static_cast<int>(sv[j * hd + d]);
+      for (int j4 = 0; j4 < N4 / 4; ++j4) acc = dp4a_us(pi[j4], vd[j4], acc);
       const int c = clampi(requant_i32_fast(acc, a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
       a.out[(static_cast<long long>(b) * L + tok[i]) * C + h * hd + d] = static_cast<int8_t>(c);
     }
