@@ -607,6 +607,12 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const double m2 = e.mult2, mi = e.mult_id;
     int i = 0;
     const uint32_t ldo = static_cast<uint32_t>(args.ldo), ldi = static_cast<uint32_t>(e.ld_id);   // offsets < 2^31 (host)
+    // MODE 4 (RESIDUAL with an int16 stream: int16 identity in, int16 codes out): 2 x 2 transposes of
+    // 16-bit halves across lane pairs instead of the 4 x 4 byte transposes; after it the even lane
+    // of a pair holds channels (n, n+1) of the even token, the odd lane the same channels of the odd one
+    const uint32_t sel16 = (lane & 1) ? 0x3276u : 0x5410u;
+    const int16_t* const id16 = reinterpret_cast<const int16_t*>(e.identity);
+    int16_t* const out16 = static_cast<int16_t*>(args.out);
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++i, tw.next(), tw_next.next()) {
       const int a = i & 1;
       const int c0 = tw.cb * Cfg::CB + quarter * 32;           // the warp's first channel
@@ -623,8 +629,11 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
       // lane-private byte offsets of (token tok_w + qi, channel nq) in the output / identity
       const bool all_ok = tok_w + Cfg::PART <= args.M && c0 + 32 <= args.N;   // warp-uniform: no guards
-      const uint32_t off_o = static_cast<uint32_t>(tok_w + qi) * ldo + nq;
-      const uint32_t off_i = static_cast<uint32_t>(tok_w + qi) * ldi + nq;
+      const uint32_t off_o = MODE == 4 ? static_cast<uint32_t>(tok_w + (lane & 1)) * ldo + (c0 + (lane & ~1))
+                                       : static_cast<uint32_t>(tok_w + qi) * ldo + nq;
+      const uint32_t off_i = MODE == 4 ? static_cast<uint32_t>(tok_w + (lane & 1)) * ldi + (c0 + (lane & ~1))
+                                       : static_cast<uint32_t>(tok_w + qi) * ldi + nq;
+      const bool np_ok = c0 + (lane & ~1) < args.N;            // MODE 4: this lane pair's channels exist (N % 4 == 0)
       const uint32_t t_row = tmem_base + a * Cfg::ACC_STRIDE + part * Cfg::PART +
                              (static_cast<uint32_t>(quarter * 32) << 16);
       // One tile.  FULL: every token / channel of the warp's 64 x 32 block exists, no guards.
@@ -647,8 +656,27 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               *reinterpret_cast<uint32_t*>(outp + (off_o + (ch * 16 + 4 * g) * ldo)) = w;
           }
         };
-        uint32_t idw[2][4];
-        if (MODE == 2) load_identity(0, idw[0]);
+        // MODE 4: register g of a chunk = tokens (2g, 2g+1); elements (int16) instead of bytes
+        auto load_identity16 = [&](int ch, uint32_t (&w)[8]) {
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const bool ok = FULL || (np_ok && tok_w + ch * 16 + 2 * g + (lane & 1) < args.M);
+            w[g] = ok ? __ldg(reinterpret_cast<const uint32_t*>(id16 + (off_i + (ch * 16 + 2 * g) * ldi))) : 0u;
+          }
+        };
+        auto store_chunk16 = [&](int ch, const uint32_t (&pk)[8]) {
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const uint32_t y = __shfl_xor_sync(0xffffffffu, pk[g], 1);
+            const uint32_t w = __byte_perm(pk[g], y, sel16);
+            if (FULL || (np_ok && tok_w + ch * 16 + 2 * g + (lane & 1) < args.M))
+              *reinterpret_cast<uint32_t*>(out16 + (off_o + (ch * 16 + 2 * g) * ldo)) = w;
+          }
+        };
+        uint32_t idw[2][MODE == 4 ? 8 : 4];
+        uint32_t packed16[MODE == 4 ? 8 : 1];
+        if (MODE == 2) load_identity(0, reinterpret_cast<uint32_t(&)[4]>(idw[0]));
+        if (MODE == 4) load_identity16(0, reinterpret_cast<uint32_t(&)[8]>(idw[0]));
         mbar_wait(&tfull_bar[a], (i >> 1) & 1);
         tc_fence_after();
         uint32_t acc[2][16];
@@ -659,7 +687,8 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           tmem_ld_wait();
           if (ch + 1 < Cfg::NCH) {
             tmem_ld16(t_row + (ch + 1) * 16, acc[(ch + 1) & 1]);
-            if (MODE == 2) load_identity(ch + 1, idw[(ch + 1) & 1]);
+            if (MODE == 2) load_identity(ch + 1, reinterpret_cast<uint32_t(&)[4]>(idw[(ch + 1) & 1]));
+            if (MODE == 4) load_identity16(ch + 1, reinterpret_cast<uint32_t(&)[8]>(idw[(ch + 1) & 1]));
           } else {
             tc_fence_before();
             __syncwarp();
@@ -700,13 +729,33 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             for (int j = 0; j < 16; ++j)
               c[j] = cl_requant_exact(static_cast<int>(z[j]) + bias, s_in, mult, e.qmin, e.qmax);
           }
+          if (MODE == 4) {
+            if (ch > 0) store_chunk16(ch - 1, reinterpret_cast<const uint32_t(&)[8]>(packed16));
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+              const uint32_t y = __shfl_xor_sync(0xffffffffu, idw[ch & 1][g], 1);
+              const uint32_t iw = __byte_perm(idw[ch & 1][g], y, sel16);     // this channel's identity, tokens 2g, 2g+1
+              int r2[2];
+#pragma unroll
+              for (int b = 0; b < 2; ++b) {
+                const int c1 = clampi(c[2 * g + b], e.qmin, e.qmax);
+                const int id = static_cast<int16_t>(iw >> (16 * b));
+                const double cd = __hiloint2double(0x43300000, c1 ^ 0x80000000) - kMagicInt;
+                const double dd = __hiloint2double(0x43300000, id ^ 0x80000000) - kMagicInt;
+                r2[b] = clampi(__double2loint(__fma_rn(cd, m2, kMagicRnd)) + __double2loint(__fma_rn(dd, mi, kMagicRnd)),
+                               e.qmin2, e.qmax2);
+              }
+              packed16[g] = (static_cast<uint32_t>(r2[0]) & 0xffffu) | (static_cast<uint32_t>(r2[1]) << 16);
+            }
+            continue;
+          }
           if (ch > 0) store_chunk(ch - 1, packed);
           if (MODE == 2) {
             // identity words arrive token-major (lane = token, bytes = channels): transpose to
             // channel-major (lane = channel, bytes = tokens) to meet the accumulators
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
-              const uint32_t iw = quad_transpose(idw[ch & 1][g], sel1, sel2);
+              const uint32_t iw = quad_transpose(idw[ch & 1][g & 3], sel1, sel2);
 #pragma unroll
               for (int b = 0; b < 4; ++b) {
                 const int j = 4 * g + b;
@@ -721,7 +770,8 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
           for (int g = 0; g < 4; ++g) packed[g] = pack4_sat_s8(c[4 * g], c[4 * g + 1], c[4 * g + 2], c[4 * g + 3]);
         }
-        if (MODE != 3) store_chunk(Cfg::NCH - 1, packed);
+        if (MODE == 4) store_chunk16(Cfg::NCH - 1, reinterpret_cast<const uint32_t(&)[8]>(packed16));
+        else if (MODE != 3) store_chunk(Cfg::NCH - 1, packed);
       };
       if (all_ok) process(std::true_type{});
       else process(std::false_type{});
@@ -938,6 +988,14 @@ extern "C" int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M
       static_cast<int64_t>(M) * ldo + N < (1ll << 31))
     return launch_cl<192, 3, false>(A, lda, W, args, st);
   const bool checked = epi->z_bound_ok == 0;
+  // RESIDUAL on the int16 residual stream (int16 identity in, int16 codes out; any clamp ranges): the
+  // channels-on-lanes kernel with 16-bit lane-pair transposes
+  if (res && wide && epi->out_bits == 16 && epi->id_bits == 16 && args.allow_fast && epi->group <= 0 && N % 4 == 0 &&
+      ldo % 2 == 0 && epi->ld_id % 2 == 0 && (reinterpret_cast<uintptr_t>(out) & 3) == 0 &&
+      (reinterpret_cast<uintptr_t>(epi->identity) & 3) == 0 && fabs(epi->mult2) < 65536.0 &&
+      fabs(epi->mult_id) < 65536.0 && static_cast<int64_t>(M) * ldo + N < (1ll << 31) &&
+      static_cast<int64_t>(M) * epi->ld_id + N < (1ll << 31) && channels_on_lanes_enabled())
+    return checked ? launch_cl<192, 4, true>(A, lda, W, args, st) : launch_cl<192, 4, false>(A, lda, W, args, st);
   // Hot shapes: channels-on-lanes kernel (per-channel constants in registers).  Needs 4-byte
   // aligned output / identity rows and no row remap.
   const int64_t span_o = static_cast<int64_t>(M) * ldo + N, span_i = static_cast<int64_t>(M) * epi->ld_id + N;

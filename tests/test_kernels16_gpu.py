@@ -147,6 +147,13 @@ def test_gemm16_residual_stream(shape):
     _gemm16_case(*shape, seed=1, epilogue=_cabi.EPI_RESIDUAL, bits1=16, bits2=16, id_bits=16)
 
 
+@pytest.mark.parametrize("shape", [(30000, 384, 384), (20011, 96, 96), (5000, 96, 384), (4099, 192, 768), (777, 100, 64)])
+def test_gemm16_residual_stream_many_tiles(shape):
+    """More tiles than SMs, ragged last token tile, Swin's narrow widths (N = 96: a partial channel block)."""
+    _gemm16_case(*shape, seed=11, epilogue=_cabi.EPI_RESIDUAL, bits1=16, bits2=16, id_bits=16)
+    _gemm16_case(*shape, seed=12, epilogue=_cabi.EPI_RESIDUAL, bits1=8, bits2=16, id_bits=16)
+
+
 def test_gemm16_mixed_widths():
     _gemm16_case(300, 384, 384, seed=2, epilogue=_cabi.EPI_RESIDUAL, bits1=16, bits2=8, id_bits=8)
     _gemm16_case(300, 384, 384, seed=3, epilogue=_cabi.EPI_RESIDUAL, bits1=8, bits2=16, id_bits=16)
