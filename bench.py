@@ -146,6 +146,12 @@ def cpu_reference_images_per_s(case: str, sample: int, repeats: int = 1):
     from ivit_b200.synthetic import synth_images
     cfg, state, Oracle = load_any_case(case)
     o = Oracle(cfg, state)
+    # all host cores for the BLAS part, also under torchrun (which exports OMP_NUM_THREADS=1)
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=os.cpu_count() or 1)
+    except Exception:
+        pass
     x = synth_images(sample, cfg, seed=0).numpy()
     best = None
     for _ in range(repeats):

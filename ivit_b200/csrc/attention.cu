@@ -123,9 +123,10 @@ __device__ __forceinline__ void chunk_pipeline(uint32_t t_row, int n, F&& body) 
 // split into two u8 planes P = 256 Phi + Plo, each its own SWIZZLE_128B tile and its own MMA into
 // its own TMEM accumulator (O_lo columns [0,64), O_hi [64,128), both over the dead score tile);
 // O = 256 O_hi + O_lo reaches 8e8, so attn.qact2 takes the general requant path that replays the
-// float32 carrier of the reference (requant_any).  One CTA per SM (the two planes double sP).
+// float32 carrier of the reference (requant_any).  The two planes double sP; the row-sum exchange buffer
+// is aliased onto the dead Q / K tiles so that two CTAs per SM still fit (110 KB each).
 template <int TPR, int TABLE, bool TAP, bool P16 = false>
-__global__ void __launch_bounds__(128 * TPR, P16 ? 1 : 2)
+__global__ void __launch_bounds__(128 * TPR, 2)
 attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
   constexpr int W = 32 / TPR;               // columns per thread per 32-column chunk
@@ -137,8 +138,10 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint8_t* sQ = smem + P_BYTES;             // [128 x 64 B]  SWIZZLE_64B (TMA)
   uint8_t* sK = sQ + 8192;                  // [<=256 x 64 B]
   uint8_t* sV = sK + 16384;                 // [<=256 x 64 B]
-  float* sAcc = reinterpret_cast<float*>(sV + 16384);          // [32][128] accumulators of threads q > 0 -> thread 0
-  int* sMax = reinterpret_cast<int*>(sAcc + 32 * 128);         // [4][128]
+  // [32][128] accumulators of threads q > 0 -> thread 0.  P16: aliased onto sQ + sK (24 KB, dead once the
+  // score MMA has completed, which every thread waits for before pass 1), so that two CTAs still fit an SM
+  float* sAcc = P16 ? reinterpret_cast<float*>(sQ) : reinterpret_cast<float*>(sV + 16384);
+  int* sMax = P16 ? reinterpret_cast<int*>(sV + 16384) : reinterpret_cast<int*>(sAcc + 32 * 128);   // [4][128]
   float* sFac = reinterpret_cast<float*>(sMax + 512);          // [128]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sFac + 128);    // qk, v, s, o
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
@@ -479,7 +482,7 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
   if ((rc = make_tmap_2d_u8(&tv, qkv, cols, rows, cols, HD, a.KP2, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   const int table = a.exp_table_1d != nullptr ? 2 : (a.exp_table != nullptr ? 1 : 0);
   const bool tap = probs != nullptr;
-  const size_t smem = 1024 + (p16 ? 65536 : 32768) + 8192 + 16384 + 16384 + 32 * 128 * 4 + 512 * 4 + 128 * 4 + 64 +
+  const size_t smem = 1024 + (p16 ? 65536 : 32768) + 8192 + 16384 + 16384 + (p16 ? 0 : 32 * 128 * 4) + 512 * 4 + 128 * 4 + 64 +
                       (table == 2 ? 256 * 16 * 4 : 0);
   const int tpr = p16 ? 2 : g_attn_tpr;
   auto launch = [&](auto kernel) -> int {
