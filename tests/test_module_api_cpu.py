@@ -137,6 +137,34 @@ def test_reference_swin_quant_runs_unchanged_and_calibrates_identically():
         want.stages[1]["blocks"][1]["proj"].mult2
 
 
+def test_swin_caller_calibrates_to_the_reference_ranges():
+    """tests/swin_caller.py (the Swin caller the GPU tests use: the reference file cannot travel) reproduces the
+    reference's calibration on the same weights and batch: every x_min / x_max equals the fixture's, which was
+    produced by the unmodified swin_quant.py.  Runs anywhere."""
+    from ivit_b200.synthetic import load_swin_case
+    from swin_caller import SwinTransformer
+    cfg, state, fix = load_swin_case("swin_toy")
+    model = SwinTransformer(cfg)
+    weights = {k: torch.as_tensor(v) for k, v in state.items() if not k.endswith((".x_min", ".x_max"))}
+    missing, unexpected = model.load_state_dict(weights, strict=False)
+    assert not unexpected, unexpected
+    assert not [k for k in missing if k.endswith((".weight", ".bias", "relative_position_bias_table"))], missing
+    model.eval()
+    with torch.no_grad():
+        model(synth_images(4, cfg, seed=1))
+    sd = model.state_dict()
+    n = 0
+    for k in fix.files:
+        if k.startswith("range/"):
+            name = k[len("range/"):]
+            assert np.array_equal(sd[name].reshape(-1).numpy().astype(f32), fix[k].astype(f32)), name
+            n += 1
+    assert n >= 80
+    from ivit_b200.api import config_from_model
+    import dataclasses
+    assert dataclasses.replace(config_from_model(model), name=cfg.name) == cfg
+
+
 def _build_pair(case):
     """The reference's VisionTransformer twice: on its own quantization_utils and on ours, same weights."""
     from oracle.ref_shim import load_reference, load_reference_callers_on

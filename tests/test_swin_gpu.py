@@ -82,6 +82,31 @@ def test_swin_tiny_batch_invariance():
     assert torch.equal(plan.forward(x[2:5].contiguous()), full[2:5])
 
 
+def test_compile_frozen_from_a_module_api_swin_model():
+    """The drop-in route for Swin: a model built on ivit_b200.quantization_utils with swin_quant.py's module
+    names, calibrated ranges loaded (scripts/inference.py --strict-model-load behaviour), frozen, then
+    compile_frozen -> FrozenSwinPlan -> InferenceSession: host images in, host logits out == oracle."""
+    from ivit_b200.api import compile_frozen
+    from swin_caller import SwinTransformer
+    cfg, state, fix = load_swin_case("swin_toy")
+    model = SwinTransformer(cfg)
+    sd = {k: torch.as_tensor(v).reshape(model.state_dict()[k].shape) for k, v in state.items() if k in model.state_dict()}
+    missing, unexpected = model.load_state_dict(sd, strict=False)
+    assert not unexpected
+    assert not [k for k in missing if k.endswith((".weight", ".bias", ".x_min", ".x_max"))], missing
+    model.cuda().eval()
+    for m in model.modules():
+        if hasattr(m, "fix"):
+            m.fix()
+    sess = compile_frozen(model, batch=4)
+    x = synth_images(4, cfg, seed=7)
+    got = sess.infer(x.pin_memory()).clone().numpy()
+    exp = SO.SwinOracle(cfg, state).forward(x.numpy())
+    assert np.array_equal(got, exp)
+    sess2 = compile_frozen(model, batch=4, chunks=2)
+    assert np.array_equal(sess2.infer(x.pin_memory()).numpy(), exp)
+
+
 def test_patch_merge_gather_and_avgpool():
     rng = np.random.default_rng(0)
     B, res, C = 3, 8, 96
