@@ -18,7 +18,7 @@ int fail(int code, const char* msg);
 int check_launch(const char* what);
 
 // exact replay of the QuantAct behind the LayerNorm for one element (quant_utils.py:220-251)
-__device__ __forceinline__ int ln16_requant(float v, float sc, double mult, int qmin, int qmax) {
+__device__ __noinline__ int ln16_requant(float v, float sc, double mult, int qmin, int qmax) {
   const float xo = __fmul_rn(v, sc);
   const float z = rintf(__fdiv_rn(xo, sc));
   const double rd = requant_d(static_cast<double>(z), mult);
@@ -182,7 +182,17 @@ layernorm_x16_requant_kernel(int kind, const XT* __restrict__ x, long long ldx, 
     const int c = 32 * i + lane;
     float v = floorf(__fmul_rn(__fmul_rn(y[i], factor), 0.5f));               // ivit :52 / ibert :147
     v = __fadd_rn(v, __ldg(bias_int + c));                                    // :61 / :154
-    stage[warp][c] = static_cast<int8_t>(ln16_requant(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax));
+    // QuantAct: the exact value is rint(z * mult), z = rint(fl32(fl32(v sf) / sf)), |z - v| <= |v| 2^-22.  Inside the
+    // clamp range the float32 product v * fl32(mult) is within 5e-5 of z * mult, so unless it lies within 1e-4
+    // of a rounding tie (or is a NaN from a zero-variance row) its rounding IS the exact answer (same argument
+    // as rowwise.cu); the replay runs for those elements only -- it costs four XU-pipe operations.
+    const double md = __ldg(mult + c);
+    const float ra = fminf(fmaxf(__fmul_rn(v, static_cast<float>(md)), -200.f), 200.f);
+    const float tm = __fadd_rn(ra, 12582912.f);                                 // rint(ra) in the low mantissa bits
+    const float rr = __fsub_rn(tm, 12582912.f);
+    int code = clampi(__float_as_int(tm) - 0x4B400000, qmin, qmax);
+    if (!(fabsf(__fsub_rn(ra, rr)) < 0.4999f)) code = ln16_requant(v, __ldg(sf + c), md, qmin, qmax);
+    stage[warp][c] = static_cast<int8_t>(code);
   }
   __syncwarp();
   int8_t* orow = out + static_cast<long long>(row) * C;
