@@ -219,6 +219,14 @@ typedef struct {
   int output_bit;            /* softmax output bits (<= 8) */
   double mult_out;           /* qact3: (s_softmax*s_v) / s3 */
   int qmin_out, qmax_out;
+  /* optional: the [256][256] float32 table of ivit_softmax_table_build for kind 0, s_attn = s2 (exp term
+   * over [row-max code + 128][code + 128]).  With a shift mask it is used only if mask_clamps != 0: the
+   * caller has checked, in float32, that the largest masked score (code qmax2, carrier - 100) minus the
+   * smallest possible row maximum (code qmin2) is negative and maps below 15 * floor(-1/s2) under
+   * x + floor(x/2) - floor(x/16), so that int_exp_shift (ivit_modules.py:151-155) clamps every masked entry
+   * and returns -floor(-1/s2).  NULL: computed per score. */
+  const float* exp_table;
+  int mask_clamps;
 } ivit_window_attention_params_t;
 int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int res, int ws, int shift, int nH,
                              int hd, const ivit_window_attention_params_t* p, void* stream);

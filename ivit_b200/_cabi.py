@@ -64,6 +64,8 @@ class WindowAttentionParams(C.Structure):
         ("output_bit", C.c_int),
         ("mult_out", C.c_double),
         ("qmin_out", C.c_int), ("qmax_out", C.c_int),
+        ("exp_table", C.c_void_p),
+        ("mask_clamps", C.c_int),
     ]
 
 

@@ -66,6 +66,14 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {
 constexpr int QK_LD = HDMAX + 4;      // row pitch of q / k in shared memory (words: odd multiple -> no bank conflicts)
 constexpr int VT_LD = WMAX + 4;       // row pitch of v^T and of the probability rows
 
+// TABLE: the Shiftmax exp term of an unmasked score depends only on (its qact2 code, the row-max code):
+// gathered from the per-layer [256][256] table ivit_softmax_table_build makes with the very same device
+// arithmetic, instead of ~45 instructions (two IEEE divisions) per score.  A masked score (carrier - 100)
+// lies so far below the row maximum -- the diagonal is never masked -- that int_exp_shift clamps it to
+// n x0 and returns exactly -x0; the host proves that bound for the layer's scale before choosing TABLE.
+constexpr int kMasked = -1000;
+
+template <bool TABLE>
 __global__ void __launch_bounds__(256)
 window_attention_i8_kernel(const WinAttnArgs a) {
   __shared__ __align__(16) int8_t sq[WMAX * QK_LD], sk[WMAX * QK_LD];
@@ -114,20 +122,38 @@ window_attention_i8_kernel(const WinAttnArgs a) {
     const int c1 = clampi(requant_i32_fast(acc, a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);        // qact_attn1
     const int c2 = clampi(requant_i32_fast(c1, a.p.mult2) + requant_i32_fast(__ldg(bias + t), a.p.mult_bias),
                           a.p.qmin2, a.p.qmax2);                                                      // qact2 (:147)
-    float x = __fmul_rn(static_cast<float>(c2), a.p.s2);                   // the float carrier
-    if (a.shift > 0) x = __fadd_rn(x, lab[i] != lab[j] ? -100.f : 0.f);    // attn + mask (:151)
-    sx[i][j] = __fdiv_rn(x, a.p.s2);                                       // ivit_modules.py:165
+    if (TABLE) {
+      sx[i][j] = __int_as_float((a.shift > 0 && lab[i] != lab[j]) ? kMasked : c2);
+    } else {
+      float x = __fmul_rn(static_cast<float>(c2), a.p.s2);                 // the float carrier
+      if (a.shift > 0) x = __fadd_rn(x, lab[i] != lab[j] ? -100.f : 0.f);  // attn + mask (:151)
+      sx[i][j] = __fdiv_rn(x, a.p.s2);                                     // ivit_modules.py:165
+    }
   }
   __syncthreads();
   // Shiftmax (ivit_modules.py:164-179): row max | exp terms (all threads) | torch-order row sum | codes
   if (threadIdx.x < N) {
     const float* row = sx[threadIdx.x];
-    float mx = row[0];
-    for (int j = 1; j < N; ++j) mx = fmaxf(mx, row[j]);
-    srow[threadIdx.x] = mx;
+    if (TABLE) {
+      int mx = __float_as_int(row[0]);
+      for (int j = 1; j < N; ++j) mx = max(mx, __float_as_int(row[j]));
+      srow[threadIdx.x] = __int_as_float(mx);
+    } else {
+      float mx = row[0];
+      for (int j = 1; j < N; ++j) mx = fmaxf(mx, row[j]);
+      srow[threadIdx.x] = mx;
+    }
   }
   __syncthreads();
-  {
+  if (TABLE) {
+    const float e_mask = -a.x0;
+    for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
+      const int i = t / N, j = t - i * N;
+      const int c = __float_as_int(sx[i][j]);
+      const float* trow = a.p.exp_table + (__float_as_int(srow[i]) + 128) * 256 + 128;
+      sx[i][j] = c == kMasked ? e_mask : __ldg(trow + c);
+    }
+  } else {
     ExpShiftParams ep;
     ep.x0 = a.x0; ep.nx0 = a.nx0; ep.n = 15;
     for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
@@ -144,7 +170,9 @@ window_attention_i8_kernel(const WinAttnArgs a) {
   __syncthreads();
   for (int t = threadIdx.x; t < N * N4; t += blockDim.x) {
     const int i = t / N4, j = t - i * N4;
-    sp[i][j] = j < N ? static_cast<uint8_t>(static_cast<int>(floorf(__fmul_rn(sx[i][j], srow[i])))) : uint8_t(0);
+    // floor of a value in [0, 2^22) through the 2^23 magic constant (round toward zero), not F2I
+    sp[i][j] = j < N ? static_cast<uint8_t>(__float_as_uint(__fadd_rz(__fmul_rn(sx[i][j], srow[i]), 8388608.f)) & 0xffu)
+                     : uint8_t(0);
   }
   __syncthreads();
   if (a.probs != nullptr) {
@@ -233,7 +261,9 @@ extern "C" int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t*
   a.x0 = floorf(-1.0f / p->s2);                                              // ivit_modules.py:154
   a.nx0 = 15.f * a.x0;                                                       // :155
   a.out_shift = 1.f / ldexpf(1.f, 31 - p->output_bit + 1);
-  window_attention_i8_kernel<<<static_cast<int>(ctas), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  const bool table = p->exp_table != nullptr && (shift == 0 || p->mask_clamps != 0) && p->qmin2 >= -128 && p->qmax2 <= 127;
+  if (table) window_attention_i8_kernel<true><<<static_cast<int>(ctas), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  else window_attention_i8_kernel<false><<<static_cast<int>(ctas), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
   return check_launch("window_attention_i8_kernel");
 }
 

@@ -30,7 +30,7 @@ import numpy as np
 import torch
 
 from . import _cabi, hostmath as hm, ops
-from ._cabi import EPI_LOGITS, EPI_REQUANT, EPI_RESIDUAL, WindowAttentionParams
+from ._cabi import EPI_LOGITS, EPI_REQUANT, EPI_RESIDUAL, AttentionParams, WindowAttentionParams
 from .plan import GraphCaptureMixin, _Linear, _Norm, _np
 from .synthetic import SwinConfig
 
@@ -45,6 +45,18 @@ def relative_position_index(ws: int) -> np.ndarray:
     rel[:, :, 1] += ws - 1
     rel[:, :, 0] *= 2 * ws - 1
     return rel.sum(-1)
+
+
+def mask_always_clamps(s2, qmin2: int, qmax2: int) -> bool:
+    """float32 restatement of the kernel's masked score: x = fl(fl(c s) - 100) / s against the smallest
+    possible row maximum fl(fl(qmin s) / s); int_exp_shift (ivit_modules.py:150-162) clamps at 15 x0."""
+    s = f32(s2)
+    x0 = np.floor(f32(-1.0) / s)
+    xm = f32(f32(f32(f32(qmax2) * s) + f32(-100.0)) / s)
+    xmin = f32(f32(f32(qmin2) * s) / s)
+    d = f32(xm - xmin)                                     # largest possible (masked score - row maximum)
+    t = f32(f32(d + np.floor(d * f32(0.5))) - np.floor(d * f32(0.0625)))      # :151, non-decreasing in d
+    return bool(np.isfinite(x0) and d < 0 and t <= f32(15.0) * x0 - f32(2.0))
 
 
 class FrozenSwinPlan(GraphCaptureMixin):
@@ -130,6 +142,14 @@ class FrozenSwinPlan(GraphCaptureMixin):
         a.qmin2, a.qmax2 = -128, 127
         a.s2 = float(s2[0])
         a.output_bit = 8
+        # exp term tabulated over (row-max code, code) by the library's own arithmetic; a masked score must
+        # provably hit int_exp_shift's clamp for the table path to be taken with a shift mask
+        a.mask_clamps = int(mask_always_clamps(s2[0], a.qmin2, a.qmax2))
+        if not self.host_only:
+            tp = AttentionParams()
+            tp.kind, tp.output_bit, tp.s_attn = 0, 8, float(s2[0])
+            self._keep.append(ops.softmax_table_build(tp, self.device, collapse=False))
+            a.exp_table = tp.exp_table
         s_sm = np.array([1 / 2 ** 7], dtype=f32)                           # ivit_modules.py:177
         s_mm2 = (s_sm * s_qkv).astype(f32)
         s3 = self._act_scale(p + "qact3")

@@ -107,6 +107,81 @@ def test_compile_frozen_from_a_module_api_swin_model():
     assert np.array_equal(sess2.infer(x.pin_memory()).numpy(), exp)
 
 
+def _window_attention_case(res, ws, shift, nH, hd, seed, s2_target, use_table):
+    """ivit_window_attention_i8 alone against the oracle's statement of WindowAttention.forward (swin_quant.py:131-160)
+    on random int8 qkv codes, for a chosen softmax-input scale s2 (decides whether a masked score can be proven to clamp)."""
+    from ivit_b200.swin_plan import mask_always_clamps, relative_position_index
+    rng = np.random.default_rng(seed)
+    B, C, L, N = 2, nH * hd, res * res, ws * ws
+    qkv = np.clip(np.rint(rng.standard_normal((B, L, 3 * C)) * 40), -128, 127).astype(np.int8)
+    s1 = np.array([0.05], dtype=f32)
+    x = (qkv.astype(f32) * s1).astype(f32).reshape(B, res, res, 3 * C)
+    if shift:
+        x = np.roll(x, (-shift, -shift), axis=(1, 2))
+    xw = SO.window_partition(x, ws).reshape(-1, N, 3, nH, hd).transpose(2, 0, 3, 1, 4)
+    q, k, v = xw[0], xw[1], xw[2]
+    attn, s, _ = O.quant_matmul(q, s1, np.swapaxes(k, -2, -1), s1)
+    sc = f32(hd ** -0.5)
+    attn, s = (attn * sc).astype(f32), (s * sc).astype(f32)
+    a1 = np.array([np.abs(attn).max() * 0.6], dtype=f32)
+    attn, s_a1, _ = O.quant_act(attn, 8, -a1, a1, pre_scale=s)
+    tab = (rng.standard_normal(((2 * ws - 1) ** 2, nH)) * 0.5).astype(f32)
+    tmax = np.array([np.abs(tab).max()], dtype=f32)
+    tabq, s_tab, tab_codes = O.quant_act(tab, 8, -tmax, tmax)
+    idx = relative_position_index(ws).reshape(-1)
+    bias = tabq[idx].reshape(N, N, nH).transpose(2, 0, 1)
+    a2 = np.array([127 * s2_target], dtype=f32)
+    attn, s2, _ = O.quant_act(attn, 8, -a2, a2, pre_scale=s_a1, identity=np.broadcast_to(bias[None], attn.shape),
+                              identity_scale=s_tab)
+    mask = SO.shift_mask(res, ws, shift)
+    if mask is not None:
+        nW = mask.shape[0]
+        attn = (attn.reshape(-1, nW, nH, N, N) + mask[None, :, None]).astype(f32).reshape(-1, nH, N, N)
+    pr, s_p, pr_codes = O.ivit_softmax(attn, s2, 8)
+    o, s_o, _ = O.quant_matmul(pr, s_p, v, s1)
+    o = o.transpose(0, 2, 1, 3).reshape(-1, N, C)
+    omax = np.array([np.abs(o).max() * 0.7], dtype=f32)
+    _, s3, out_codes = O.quant_act(o, 8, -omax, omax, pre_scale=s_o)
+    exp = SO.window_reverse(out_codes.reshape(-1, ws, ws, C), ws, res, res)
+    if shift:
+        exp = np.roll(exp, (shift, shift), axis=(1, 2))
+    p = _cabi.WindowAttentionParams()
+    p.mult_attn = float(hm.dyadic_mult(s, s_a1).reshape(-1)[0])
+    p.qmin_attn, p.qmax_attn, p.qmin2, p.qmax2, p.qmin_out, p.qmax_out = -128, 127, -128, 127, -128, 127
+    p.mult2 = float(hm.dyadic_mult(s_a1, s2).reshape(-1)[0])
+    p.mult_bias = float(hm.dyadic_mult(s_tab, s2).reshape(-1)[0])
+    p.s2, p.output_bit = float(s2[0]), 8
+    p.mult_out = float(hm.dyadic_mult(s_o, s3).reshape(-1)[0])
+    bias_codes = torch.from_numpy(np.ascontiguousarray(
+        tab_codes[idx].reshape(N, N, nH).transpose(2, 0, 1)).astype(np.int8)).cuda()
+    p.bias_codes = bias_codes.data_ptr()
+    clamps = mask_always_clamps(s2[0], -128, 127)
+    keep = None
+    if use_table:
+        tp = _cabi.AttentionParams()
+        tp.kind, tp.output_bit, tp.s_attn = 0, 8, float(s2[0])
+        keep = ops.softmax_table_build(tp, "cuda", collapse=False)
+        p.exp_table, p.mask_clamps = tp.exp_table, int(clamps)
+    out, probs = ops.window_attention(torch.from_numpy(qkv).cuda(), B, res, ws, shift, nH, hd, p, want_probs=True)
+    assert np.array_equal(probs.cpu().numpy().astype(np.int64), pr_codes.astype(np.int64)), "softmax codes"
+    assert np.array_equal(out.cpu().numpy().reshape(exp.shape).astype(np.int64), exp.astype(np.int64)), "output codes"
+    del keep
+    return clamps
+
+
+@pytest.mark.parametrize("use_table", [False, True])
+@pytest.mark.parametrize("s2_target", [0.03, 0.25, 0.6, 1.7])
+def test_window_attention_kernel(s2_target, use_table):
+    """Computed and tabulated exp terms, without and with the shift mask, from scales at which a masked score
+    provably clamps (table path) up to scales at which it does not (masked scores can win the row maximum:
+    the kernel must then take the computed path even when a table is attached)."""
+    _window_attention_case(14, 7, 0, 3, 32, seed=1, s2_target=s2_target, use_table=use_table)
+    clamps = _window_attention_case(14, 7, 3, 3, 32, seed=2, s2_target=s2_target, use_table=use_table)
+    assert clamps == (s2_target < 0.4)
+    _window_attention_case(8, 4, 2, 2, 32, seed=3, s2_target=s2_target, use_table=use_table)      # 4x4 windows
+    _window_attention_case(7, 7, 0, 6, 32, seed=4, s2_target=s2_target, use_table=use_table)      # one window, 6 heads
+
+
 def test_patch_merge_gather_and_avgpool():
     rng = np.random.default_rng(0)
     B, res, C = 3, 8, 96
