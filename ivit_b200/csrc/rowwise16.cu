@@ -200,6 +200,101 @@ layernorm_x16_requant_kernel(int kind, const XT* __restrict__ x, long long ldx, 
     *reinterpret_cast<int4*>(orow + v * 16) = *reinterpret_cast<const int4*>(&stage[warp][v * 16]);
 }
 
+// Swin stage 0 (C = 96, channel-strided order, every token inside a whole block of 32 of its image): eight
+// lanes per row, four rows per warp.  Lane g < 6 of a row owns channels [16 g, 16 g + 16) -- exactly one group
+// of torch's 16-element cascade -- so the ordered mean needs 16 sequential adds per lane plus a 6-step
+// in-order combine, the per-row scalar work (ten Newton steps) is replicated on 8 lanes instead of 32,
+// rows come in as 32-byte and leave as 16-byte vectors without shared-memory staging, and the
+// per-channel constants live in registers across the grid-stride loop.  I-ViT kind only.
+template <typename XT>
+__global__ void __launch_bounds__(256)
+layernorm96_strided_kernel(const XT* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows, float s_in,
+                           const float* __restrict__ bias_int, const float* __restrict__ sf,
+                           const double* __restrict__ mult, int qmin, int qmax) {
+  constexpr int C = 96;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane & 7, sub = lane >> 3;
+  const bool owner = g < 6;
+  const int c0 = 16 * (owner ? g : 0);
+  float bia[16], mf[16];
+#pragma unroll
+  for (int u = 0; u < 16; ++u) {
+    bia[u] = __ldg(bias_int + c0 + u);
+    mf[u] = static_cast<float>(__ldg(mult + c0 + u));
+  }
+  const int quads = (rows + 3) / 4;
+  for (int q = blockIdx.x * 8 + warp; q < quads; q += gridDim.x * 8) {
+    const int row = 4 * q + sub;
+    const bool live = owner && row < rows;
+    int qv[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) qv[u] = 0;
+    if (live) {
+      const XT* xr = x + static_cast<long long>(row) * ldx + c0;
+      if (sizeof(XT) == 2) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int4 w = __ldg(reinterpret_cast<const int4*>(xr) + h);
+          const int ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+          for (int u = 0; u < 8; ++u) qv[8 * h + u] = static_cast<int16_t>(ww[u >> 1] >> (16 * (u & 1)));
+        }
+      } else {
+        const int4 w = __ldg(reinterpret_cast<const int4*>(xr));
+        const int ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int u = 0; u < 16; ++u) qv[u] = static_cast<int8_t>(ww[u >> 2] >> (8 * (u & 3)));
+      }
+    }
+    float xe[16];
+    float sg = 0.f;
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+      xe[u] = x_eff(static_cast<float>(qv[u]), s_in);                           // ivit_modules.py:36
+      sg = __fadd_rn(sg, xe[u]);                                               // one 16-element cascade group
+    }
+    float a1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) a1 = __fadd_rn(a1, __shfl_sync(0xffffffffu, sg, k, 8));   // groups in order
+    const int mean_i = static_cast<int>(rintf(__fdiv_rn(a1, static_cast<float>(C))));    // :37
+    long long var = 0;
+    int yi[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+      yi[u] = static_cast<int>(xe[u]) - mean_i;                                // :38 trunc, :40
+      const int sq = static_cast<int>(static_cast<uint32_t>(yi[u]) * static_cast<uint32_t>(yi[u]));   // :41 wraps (H9)
+      var += owner ? static_cast<long long>(sq) : 0ll;                         // :42
+    }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) var += __shfl_xor_sync(0xffffffffu, var, o, 8);
+    const float var_f = static_cast<float>(var);
+    float k = 65536.f;
+#pragma unroll
+    for (int it = 0; it < 10; ++it) k = floorf(__fmul_rn(__fadd_rn(k, floorf(__fdiv_rn(var_f, k))), 0.5f));   // :45-49
+    const float factor = floorf(__fdiv_rn(2147483648.f, k));                   // :51
+    int code[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+      float v = floorf(__fmul_rn(__fmul_rn(static_cast<float>(yi[u]), factor), 0.5f));      // :52
+      v = __fadd_rn(v, bia[u]);                                                // :61
+      const float ra = fminf(fmaxf(__fmul_rn(v, mf[u]), -200.f), 200.f);
+      const float tm = __fadd_rn(ra, 12582912.f);
+      const float rr = __fsub_rn(tm, 12582912.f);
+      code[u] = clampi(__float_as_int(tm) - 0x4B400000, qmin, qmax);
+      if (!(fabsf(__fsub_rn(ra, rr)) < 0.4999f))                               // near a tie / NaN: exact replay
+        code[u] = ln16_requant(v, __ldg(sf + c0 + u), __ldg(mult + c0 + u), qmin, qmax);
+    }
+    if (live) {
+      uint32_t w[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        w[j] = (code[4 * j] & 0xff) | ((code[4 * j + 1] & 0xff) << 8) | ((code[4 * j + 2] & 0xff) << 16) |
+               (static_cast<uint32_t>(code[4 * j + 3]) << 24);
+      *reinterpret_cast<int4*>(out + static_cast<long long>(row) * C + c0) = make_int4(w[0], w[1], w[2], w[3]);
+    }
+  }
+}
+
 __global__ void fill_cls_rows16_kernel(int16_t* __restrict__ out, const int16_t* __restrict__ cls_row, int B, int N,
                                        int C) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -278,6 +373,15 @@ static int launch_ln16(int kind, const XT* x, int64_t ldx, int8_t* out, int rows
   const float sp = ldexpf(1.f, static_cast<int>(shift));
   const int grid = (rows + 7) / 8;
   const bool outer = strided_tokens > 0;
+  // Swin stage 0: C = 96, no tail tokens (L % 32 == 0), aligned rows -> the eight-lanes-per-row kernel
+  if (outer && kind == 0 && C == 96 && strided_tokens % 32 == 0 && (ldx * sizeof(XT)) % 16 == 0 &&
+      (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+    const int quads = (rows + 3) / 4;
+    int g = (quads + 7) / 8;
+    if (g > 148 * 8) g = 148 * 8;
+    layernorm96_strided_kernel<XT><<<g, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax);
+    return check_launch("layernorm96_strided_kernel");
+  }
 #define IVIT_LN16_CASE(c, ALLOW_OUTER)                                                                            \
   case c:                                                                                                         \
     if (outer) {                                                                                                  \

@@ -201,7 +201,8 @@ def test_patch_merge_gather_and_avgpool():
         assert np.array_equal(got.astype(np.int64), codes[:, :, 0].astype(np.int64)), (L, Cc)
 
 
-@pytest.mark.parametrize("C,tokens,bits", [(96, 196, 16), (96, 64, 16), (128, 49, 16), (96, 196, 8), (192, 100, 16)])
+@pytest.mark.parametrize("C,tokens,bits", [(96, 196, 16), (96, 64, 16), (128, 49, 16), (96, 196, 8), (192, 100, 16),
+                                           (96, 64, 8), (96, 160, 16), (96, 3136, 16), (384, 64, 16)])
 def test_layernorm_strided_order(C, tokens, bits):
     """LayerNorm whose reference input is channel-strided: torch's outer-reduction order of the mean, both
     forms (whole 32-token blocks / tail tokens).  16-bit codes make the order matter on ordinary rows."""
