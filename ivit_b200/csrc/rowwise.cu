@@ -532,6 +532,7 @@ __global__ void gelu_ivit_raw_kernel(float* __restrict__ out, GeluIvitParams gi)
 }
 
 // One warp per row: row max (needed by ShiftGELU, ivit_modules.py:110), then table lookup.
+template <int NV>                   // 16-byte vectors per lane: C <= NV * 512
 __global__ void __launch_bounds__(256)
 gelu_lut_apply_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, const int8_t* __restrict__ lut,
                       int rows, int C) {
@@ -541,10 +542,10 @@ gelu_lut_apply_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, co
   const int4* xr = reinterpret_cast<const int4*>(x + static_cast<long long>(row) * C);
   int4* orow = reinterpret_cast<int4*>(out + static_cast<long long>(row) * C);
   const int nv = C / 16;
-  int4 v[6];                       // up to C = 3072 (6 * 32 lanes * 16 B)
+  int4 v[NV];                      // NV = 6: up to C = 3072 (6 * 32 lanes * 16 B)
   uint32_t m = 0x80808080u;        // four int8 lanes of -128
 #pragma unroll
-  for (int i = 0; i < 6; ++i) {
+  for (int i = 0; i < NV; ++i) {
     const int idx = i * 32 + lane;
     if (idx < nv) {
       v[i] = __ldg(xr + idx);
@@ -571,7 +572,7 @@ gelu_lut_apply_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, co
     return b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
   };
 #pragma unroll
-  for (int i = 0; i < 6; ++i) {
+  for (int i = 0; i < NV; ++i) {
     const int idx = i * 32 + lane;
     if (idx < nv) {
       int4 o;
@@ -791,8 +792,11 @@ extern "C" int ivit_gelu_ivit_raw_table(float* out65536, float s_in, int output_
 extern "C" int ivit_gelu_lut_apply_i8(const int8_t* x, int8_t* out, const int8_t* lut, int rows, int C,
                                       void* stream) {
   if (rows <= 0) return 0;
-  if (C % 16 != 0 || C > 3072) return fail(IVIT_ERR_UNSUPPORTED, "gelu: C % 16 == 0 and C <= 3072 required");
-  gelu_lut_apply_kernel<<<(rows + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, out, lut, rows, C);
+  if (C % 16 != 0 || C > 6144) return fail(IVIT_ERR_UNSUPPORTED, "gelu: C % 16 == 0 and C <= 6144 required");
+  if (C <= 3072)
+    gelu_lut_apply_kernel<6><<<(rows + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, out, lut, rows, C);
+  else      // ViT-L / Swin-B hidden widths (4096), Swin-L (6144)
+    gelu_lut_apply_kernel<12><<<(rows + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, out, lut, rows, C);
   return check_launch("gelu_lut_apply_kernel");
 }
 

@@ -397,12 +397,15 @@ static int launch_ln16(int kind, const XT* x, int64_t ldx, int8_t* out, int rows
     IVIT_LN16_CASE(96, true)
     IVIT_LN16_CASE(128, true)
     IVIT_LN16_CASE(192, true)
+    IVIT_LN16_CASE(256, true)
     IVIT_LN16_CASE(384, true)
+    IVIT_LN16_CASE(512, false)
     IVIT_LN16_CASE(768, false)
     IVIT_LN16_CASE(1024, false)
     IVIT_LN16_CASE(1536, false)
+    IVIT_LN16_CASE(2048, false)
     default:
-      return fail(IVIT_ERR_UNSUPPORTED, "layernorm16: C must be one of 96,128,192,384,768,1024,1536");
+      return fail(IVIT_ERR_UNSUPPORTED, "layernorm16: C must be one of 96,128,192,256,384,512,768,1024,1536,2048");
   }
 #undef IVIT_LN16_CASE
   return check_launch("layernorm_x16_requant_kernel");

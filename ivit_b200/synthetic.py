@@ -199,7 +199,15 @@ SWIN_CONFIGS = {
     "swin_toy": SwinConfig("swin_toy", embed_dim=96, depths=(2, 2), num_heads=(3, 6), img_size=56, num_classes=100),
 }
 
-SWIN_CASES = {"swin_toy": "swin_toy", "swin_tiny": "swin_tiny"}
+SWIN_CONFIGS.update({
+    # Swin-B widths (C = 128 -> 256, LayerNorm over 512 channels in PatchMerging, 4 / 8 heads of 32)
+    "swin_toy_b": SwinConfig("swin_toy_b", embed_dim=128, depths=(2, 2), num_heads=(4, 8), img_size=56, num_classes=100),
+    # 4 x 4 windows (16 tokens, shift 2) on an 8 x 8 token grid, then one 4 x 4 window
+    "swin_toy_w4": SwinConfig("swin_toy_w4", embed_dim=96, depths=(2, 2), num_heads=(3, 6), window_size=4, img_size=32,
+                              num_classes=100),
+})
+
+SWIN_CASES = {"swin_toy": "swin_toy", "swin_tiny": "swin_tiny", "swin_toy_b": "swin_toy_b", "swin_toy_w4": "swin_toy_w4"}
 
 
 def synth_swin_state(cfg: SwinConfig, seed: int = 0) -> dict:

@@ -113,6 +113,8 @@ def make_vit_case(name: str) -> dict:
 SWIN_CASES = {
     "swin_toy": ("swin_toy", 2, 4, ("layers.0.blocks.1.attn.qact3", "layers.1.blocks.1.qact4")),
     "swin_tiny": ("swin_tiny", 2, 2, ("qact3",)),
+    "swin_toy_b": ("swin_toy_b", 2, 4, ("layers.1.blocks.1.qact4",)),
+    "swin_toy_w4": ("swin_toy_w4", 2, 4, ("layers.0.blocks.1.attn.qact3",)),
 }
 
 

@@ -61,7 +61,7 @@ def _ln16_case(kind, C, rows, seed, s_in, spread, neg=False, use_int_sqrt=False,
     return int(ok.sum())
 
 
-@pytest.mark.parametrize("C", [128, 192, 384, 768])
+@pytest.mark.parametrize("C", [96, 128, 192, 256, 384, 512, 768, 1024, 1536, 2048])
 def test_layernorm16_ivit(C):
     assert _ln16_case(0, C, 203, seed=C, s_in=1.37e-4, spread=9000.0) >= 200
     _ln16_case(0, C, 64, seed=C + 1, s_in=3.1e-5, spread=20000.0, neg=True)

@@ -132,6 +132,20 @@ def test_gelu_ivit_table_exhaustive(s_in):
     _cmp(outk, expr, "gelu ivit apply")
 
 
+def test_gelu_apply_wide_rows():
+    """Hidden widths beyond 3072 (ViT-L / Swin-B: 4096, Swin-L: 6144) take the wider instantiation."""
+    s_in = f32(0.0371)
+    rng = np.random.default_rng(2)
+    for Cw in (4096, 6144, 3072):
+        xr = np.clip(np.rint(rng.standard_normal((21, Cw)) * 30), -128, 100).astype(np.int8)
+        yr, sgr, _ = O.ivit_gelu((xr.astype(f32) * s_in).astype(f32), np.array([s_in]))
+        x_max = np.array([np.abs(yr).max() * 0.8], dtype=f32)
+        _, s_out, expr = O.quant_act(yr, 8, -x_max, x_max, pre_scale=sgr)
+        mult = float(hm.dyadic_mult(sgr, s_out).reshape(-1)[0])
+        lut, _ = ops.gelu_lut_build(0, float(s_in), 8, mult, -128, 127, DEV)
+        _cmp(ops.gelu_lut_apply(_t(xr, torch.int8), lut).cpu().numpy(), expr, f"gelu apply C={Cw}")
+
+
 @pytest.mark.parametrize("s_in", [0.0371, 0.0123, 0.113])
 def test_gelu_ibert_table(s_in):
     s_in = f32(s_in)

@@ -61,6 +61,28 @@ def test_swin_toy_all_boundaries():
     assert np.allclose(logits, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
 
 
+@pytest.mark.parametrize("case", ["swin_toy_b", "swin_toy_w4"])
+def test_swin_other_shapes(case):
+    """Swin-B widths (C = 128 / 256, 4 and 8 heads, LayerNorm over 512 channels) and 4 x 4 windows (16 tokens)."""
+    _, _, logits, fix, ntaps = _run_case(case, 2)
+    ref = fix["logits"]
+    assert np.array_equal(logits.argmax(1), ref.argmax(1))
+    assert np.allclose(logits, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
+def test_swin_tiny_graph_session_and_permutation_invariance():
+    """Swin-T at batch 32 through InferenceSession (CUDA graph, host in / host out): every image's logits are
+    independent of its position in the batch."""
+    from ivit_b200.api import InferenceSession
+    cfg, state, _ = load_swin_case("swin_tiny")
+    sess = InferenceSession(cfg, state, batch=32)
+    x = synth_images(32, cfg, seed=9)
+    full = sess.infer(x.pin_memory()).clone()
+    perm = torch.randperm(32, generator=torch.Generator().manual_seed(0))
+    assert torch.equal(sess.infer(x[perm].contiguous().pin_memory()), full[perm])
+    assert torch.equal(sess.plan.forward(x[:5].cuda()).cpu(), full[:5])
+
+
 def test_swin_toy_fresh_inputs_batch3():
     _run_case("swin_toy", 3, seed=5)
 

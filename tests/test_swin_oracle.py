@@ -21,7 +21,7 @@ def _codes(y, s):
     return np.rint(np.asarray(y, dtype=f32) / np.asarray(s, dtype=f32)).astype(np.int64)
 
 
-@pytest.mark.parametrize("case", ["swin_toy", "swin_tiny"])
+@pytest.mark.parametrize("case", ["swin_toy", "swin_tiny", "swin_toy_b", "swin_toy_w4"])
 def test_swin_oracle_matches_reference_fixture(case):
     cfg, state, fix = load_swin_case(case)
     x = synth_images(2, cfg, seed=0).numpy()
