@@ -55,6 +55,7 @@ CONFIGS = {
     "deit_small": VitConfig("deit_small", 384, 12, 6),
     "deit_base": VitConfig("deit_base", 768, 12, 12),
     "vit_base": VitConfig("vit_base", 768, 12, 12),
+    "vit_large": VitConfig("vit_large", 1024, 24, 16),
     # a 2-block, 2-head toy used by fast unit tests (not a reference factory)
     "toy": VitConfig("toy", 128, 2, 2),
 }
@@ -125,6 +126,7 @@ CASES = {
     "deit_small_ivit": ("deit_small", "ivit", "ivit", "ivit", 0.0),
     "vit_base_mixed": ("vit_base", "ivit", "ibert", "ivit", 0.0),
     "deit_base_ibert": ("deit_base", "ibert", "ibert", "ibert", 0.0),
+    "vit_large_ivit": ("vit_large", "ivit", "ivit", "ivit", 0.0),
     # 16-bit activation locations (vit_quant.py:180-187)
     "toy_ivit_w16": ("toy", "ivit", "ivit", "ivit", 0.0, (16,) * 8),
     "toy_ibert_w16": ("toy", "ibert", "ibert", "ibert", 0.0, (16,) * 8),

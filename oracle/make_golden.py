@@ -52,6 +52,8 @@ CASES = {
     # configs[2]: ViT-Base, mixed layer selection
     "vit_base_mixed": ("vit_base", "ivit", "ibert", "ivit", None, 2, 0.0, ("qact2",)),
     "deit_base_ibert": ("deit_base", "ibert", "ibert", "ibert", None, 2, 0.0, ("qact2",)),
+    # the largest factory of vit_quant.py (:390-406): ViT-Large, 24 blocks of width 1024
+    "vit_large_ivit": ("vit_large", "ivit", "ivit", "ivit", None, 2, 0.0, ("qact2",)),
     # 16-bit activation locations (vit_quant.py:180-187; scripts/inference.py:297 --bitwidth 16): all eight
     # at 16 bit, and a mix (patch_embed, pos, block_input, attention_out, softmax, mlp_out, norm2_in, block_out)
     "toy_ivit_w16": ("toy", "ivit", "ivit", "ivit", (16,) * 8, 2, 0.0, ("blocks.0.attn.qact2", "blocks.1.qact4")),

@@ -19,6 +19,7 @@ _FACTORY = {
     "deit_small": "deit_small_patch16_224",
     "deit_base": "deit_base_patch16_224",
     "vit_base": "vit_base_patch16_224",
+    "vit_large": "vit_large_patch16_224",
 }
 
 

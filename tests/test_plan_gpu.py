@@ -104,10 +104,11 @@ def test_deit_small_b256_configs1():
     assert torch.equal(plan.forward(x[perm].contiguous()), full[perm])
 
 
-@pytest.mark.parametrize("case", ["vit_base_mixed", "deit_base_ibert", "deit_base_ibert_w16"])
+@pytest.mark.parametrize("case", ["vit_base_mixed", "deit_base_ibert", "deit_base_ibert_w16", "vit_large_ivit"])
 def test_base_models_vs_reference_logits(case):
     """configs[2] (ViT-Base, --gelu ivit --softmax ibert --layernorm ivit), DeiT-Base ibert, and configs[4]
-    (DeiT-Base ibert with all eight activation locations at 16 bit)."""
+    (DeiT-Base ibert with all eight activation locations at 16 bit), and ViT-Large (24 blocks of width 1024: the
+    largest factory of vit_quant.py)."""
     _, _, _, logits, fix = _run_case(case, 2)
     ref = fix["logits"]
     assert np.array_equal(logits.argmax(1), ref.argmax(1))
