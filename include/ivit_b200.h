@@ -230,6 +230,9 @@ typedef struct {
 } ivit_window_attention_params_t;
 int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int res, int ws, int shift, int nH,
                              int hd, const ivit_window_attention_params_t* p, void* stream);
+/* Two kernels: the products on tcgen05 (head_dim 32, default) or on dp4a (any head_dim % 4 == 0).  variant 0 =
+ * choose per call, 1 = always dp4a.  Returns the previous setting.  Process-wide; for A/B timing and tests. */
+int ivit_window_attention_set_variant(int variant);
 /* PatchMerging.forward's strided slices + cat (:339-344): [B, res, res, C] -> [B, (res/2)^2, 4C]. */
 int ivit_patch_merge_gather(const void* x, void* out, int elem_bits, int B, int res, int C, void* stream);
 /* AdaptiveAvgPool1d(1) over the tokens of the float carrier + qact3 (:554-555), torch's summation order:

@@ -99,6 +99,7 @@ _SIGS = {
                                                  C.c_float, C.c_int, C.c_int, C.c_void_p]),
     "ivit_window_attention_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                            C.c_int, C.c_int, C.POINTER(WindowAttentionParams), C.c_void_p]),
+    "ivit_window_attention_set_variant": (C.c_int, [C.c_int]),
     "ivit_patch_merge_gather": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "ivit_avgpool_requant_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_double,
                                           C.c_int, C.c_int, C.c_void_p]),

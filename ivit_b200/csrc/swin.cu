@@ -10,6 +10,7 @@
 // buffer and writes its output row to the same token, so no permuted copy ever exists in HBM.
 #include "intmath.cuh"
 #include "ivit_b200.h"
+#include "ptx.cuh"
 
 namespace ivit {
 int fail(int code, const char* msg);
@@ -193,6 +194,216 @@ window_attention_i8_kernel(const WinAttnArgs a) {
   }
 }
 
+// ------------------------------------------------------------------ tensor-core variant (hd = 32)
+// Same kernel with the two QuantMatMul products (quant_modules.py:404-409) on tcgen05 kind::i8:
+//   S = Q K^T   one 128 x 64 x 64 tile: the window's 49 query rows in TMEM lanes 0..48, 49 key columns;
+//               hd = 32 is zero-padded to the 64-byte rows of the SWIZZLE_64B K-major layout the ViT
+//               attention kernel uses (two K = 32 MMAs, the second multiplies zeros)
+//   O = P V     128 x 32 x 64: P (u8) rows of 64 bytes (columns past the window are zero), V^T [d][token]
+// Operand tiles are written by the threads straight in the swizzled layout (the window rows are a
+// gather, not a TMA box).  The score tile is copied TMEM -> shared memory by the two warps that can
+// reach lanes 0..63 and the per-score epilogue then runs on all 256 threads exactly as above; the
+// output rows are requantised by those two warps straight from TMEM.  64 TMEM columns per CTA.
+__device__ __forceinline__ int sw64_off(int r, int byte) {       // 64-byte rows, 8-row groups 512 B apart
+  return (r >> 3) * 512 + (r & 7) * 64 + ((((byte >> 4) ^ (r >> 1)) & 3) << 4) + (byte & 15);
+}
+
+template <bool TABLE>
+__global__ void __launch_bounds__(256)
+window_attention_tc_kernel(const WinAttnArgs a) {
+  __shared__ __align__(1024) uint8_t tiles[8192 + 4096 + 8192 + 2048];
+  __shared__ float sx[WMAX][WMAX + 1];
+  __shared__ int tok[WMAX];
+  __shared__ int lab[WMAX];
+  __shared__ float srow[WMAX];
+  __shared__ __align__(8) uint64_t bars[2];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* const sQ = tiles;                 // [128][64 B]  rows >= N never read back
+  uint8_t* const sK = tiles + 8192;          // [64][64 B]
+  uint8_t* const sP = tiles + 12288;         // [128][64 B]
+  uint8_t* const sVt = tiles + 20480;        // [32][64 B]   v transposed: [d][token]
+  const int ws = a.ws, N = ws * ws, res = a.res, nWx = res / ws, nW = nWx * nWx;
+  constexpr int hd = 32;
+  const int h = blockIdx.x % a.nH;
+  const int w = (blockIdx.x / a.nH) % nW;
+  const int b = blockIdx.x / (a.nH * nW);
+  const int C = a.nH * hd, L = res * res;
+  const int wy = w / nWx, wx = w % nWx;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(&tmem_slot, 64);
+    tmem_relinquish();
+  }
+  if (threadIdx.x < N) {
+    const int iy = threadIdx.x / ws, ix = threadIdx.x % ws;
+    const int ry = wy * ws + iy, rx = wx * ws + ix;                        // rolled coordinates
+    tok[threadIdx.x] = ((ry + a.shift) % res) * res + (rx + a.shift) % res;
+    lab[threadIdx.x] = 3 * mask_region(ry, res, ws, a.shift) + mask_region(rx, res, ws, a.shift);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  // gather q, k (K-major rows, bytes 32..63 zero) and v^T into the swizzled operand tiles
+  constexpr int wpr = hd / 4;
+  for (int t = threadIdx.x; t < 3 * N * wpr; t += blockDim.x) {
+    const int which = t / (N * wpr), r = (t / wpr) % N, c4 = t % wpr;
+    const int8_t* src = a.qkv + (static_cast<long long>(b) * L + tok[r]) * 3 * C + which * C + h * hd + 4 * c4;
+    const int v = __ldg(reinterpret_cast<const int*>(src));
+    if (which < 2) {
+      *reinterpret_cast<int*>((which == 0 ? sQ : sK) + sw64_off(r, 4 * c4)) = v;
+    } else {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) sVt[sw64_off(4 * c4 + u, r)] = static_cast<uint8_t>(v >> (8 * u));
+    }
+  }
+  for (int t = threadIdx.x; t < 2 * N * 2; t += blockDim.x) {              // zero the K padding of q and k
+    const int which = t / (2 * N), r = (t >> 1) % N, c = 2 + (t & 1);
+    *reinterpret_cast<int4*>((which == 0 ? sQ : sK) + sw64_off(r, 16 * c)) = make_int4(0, 0, 0, 0);
+  }
+  fence_proxy_async_smem();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    tc_fence_after();
+    constexpr uint32_t idesc1 = make_idesc_i8(128, 64, true, true, false, false);
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const uint64_t da = make_smem_desc(smem_u32(sQ) + k * 32, 16, 512, kLayoutSW64);
+      const uint64_t db = make_smem_desc(smem_u32(sK) + k * 32, 16, 512, kLayoutSW64);
+      mma_i8_ss(tmem_base, da, db, idesc1, k != 0 ? 1u : 0u);
+    }
+    tc_commit(&bars[0]);
+  }
+  __syncwarp();
+  int (*sacc)[WMAX + 1] = reinterpret_cast<int (*)[WMAX + 1]>(sx);
+  if (warp < 2) {                              // TMEM lanes 0..63 -> the score tile in shared memory
+    mbar_wait(&bars[0], 0);
+    tc_fence_after();
+    const int row = 32 * warp + lane;
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(32 * warp) << 16);
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      uint32_t v[32];
+      tmem_ld32(t_row + 32 * half, v);
+      tmem_ld_wait();
+      if (row < N) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (32 * half + j < N) sacc[row][32 * half + j] = static_cast<int>(v[j]);
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  // qact_attn1 -> qact2 (+ relative-position bias identity) -> (+ mask) -> x / s   (as in the kernel above)
+  const int8_t* bias = a.p.bias_codes + static_cast<long long>(h) * N * N;
+  for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
+    const int i = t / N, j = t - i * N;
+    const int acc = sacc[i][j];
+    const int c1 = clampi(requant_i32_fast(acc, a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
+    const int c2 = clampi(requant_i32_fast(c1, a.p.mult2) + requant_i32_fast(__ldg(bias + t), a.p.mult_bias),
+                          a.p.qmin2, a.p.qmax2);
+    if (TABLE) {
+      sx[i][j] = __int_as_float((a.shift > 0 && lab[i] != lab[j]) ? kMasked : c2);
+    } else {
+      float x = __fmul_rn(static_cast<float>(c2), a.p.s2);
+      if (a.shift > 0) x = __fadd_rn(x, lab[i] != lab[j] ? -100.f : 0.f);
+      sx[i][j] = __fdiv_rn(x, a.p.s2);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < N) {
+    const float* row = sx[threadIdx.x];
+    if (TABLE) {
+      int mx = __float_as_int(row[0]);
+      for (int j = 1; j < N; ++j) mx = max(mx, __float_as_int(row[j]));
+      srow[threadIdx.x] = __int_as_float(mx);
+    } else {
+      float mx = row[0];
+      for (int j = 1; j < N; ++j) mx = fmaxf(mx, row[j]);
+      srow[threadIdx.x] = mx;
+    }
+  }
+  __syncthreads();
+  if (TABLE) {
+    const float e_mask = -a.x0;
+    for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
+      const int i = t / N, j = t - i * N;
+      const int c = __float_as_int(sx[i][j]);
+      const float* trow = a.p.exp_table + (__float_as_int(srow[i]) + 128) * 256 + 128;
+      sx[i][j] = c == kMasked ? e_mask : __ldg(trow + c);
+    }
+  } else {
+    ExpShiftParams ep;
+    ep.x0 = a.x0; ep.nx0 = a.nx0; ep.n = 15;
+    for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
+      const int i = t / N, j = t - i * N;
+      sx[i][j] = exp_shift(__fsub_rn(sx[i][j], srow[i]), ep);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < N) {
+    float sum = torch_row_sum_small(sx[threadIdx.x], N);
+    sum = fminf(sum, 2147483648.f);
+    srow[threadIdx.x] = __fmul_rn(floorf(__fdiv_rn(2147483648.f, sum)), a.out_shift);
+  }
+  __syncthreads();
+  // probabilities -> the u8 A operand (rows of 64 bytes; columns past the window are zero)
+  for (int t = threadIdx.x; t < N * 64; t += blockDim.x) {
+    const int i = t >> 6, j = t & 63;
+    sP[sw64_off(i, j)] =
+        j < N ? static_cast<uint8_t>(__float_as_uint(__fadd_rz(__fmul_rn(sx[i][j], srow[i]), 8388608.f)) & 0xffu)
+              : uint8_t(0);
+  }
+  fence_proxy_async_smem();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    tc_fence_after();
+    constexpr uint32_t idesc2 = make_idesc_i8(128, 32, false, true, false, false);     // P u8, v^T s8, both K-major
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const uint64_t da = make_smem_desc(smem_u32(sP) + k * 32, 16, 512, kLayoutSW64);
+      const uint64_t db = make_smem_desc(smem_u32(sVt) + k * 32, 16, 512, kLayoutSW64);
+      mma_i8_ss(tmem_base, da, db, idesc2, k != 0 ? 1u : 0u);           // over the dead score columns
+    }
+    tc_commit(&bars[1]);
+  }
+  __syncwarp();
+  if (a.probs != nullptr) {
+    uint8_t* pr = a.probs + (static_cast<long long>(b * nW + w) * a.nH + h) * N * N;
+    for (int t = threadIdx.x; t < N * N; t += blockDim.x) pr[t] = sP[sw64_off(t / N, t % N)];
+  }
+  if (warp < 2) {                              // O rows from TMEM -> qact3 -> the token's image position
+    mbar_wait(&bars[1], 0);
+    tc_fence_after();
+    const int row = 32 * warp + lane;
+    uint32_t o[32];
+    tmem_ld32(tmem_base + (static_cast<uint32_t>(32 * warp) << 16), o);
+    tmem_ld_wait();
+    if (row < N && a.out != nullptr) {
+      uint32_t wds[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) wds[j] = 0;
+#pragma unroll
+      for (int d = 0; d < 32; ++d) {
+        const int c = clampi(requant_i32_fast(static_cast<int>(o[d]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
+        wds[d >> 2] |= (static_cast<uint32_t>(c) & 0xffu) << (8 * (d & 3));
+      }
+      int4* op = reinterpret_cast<int4*>(a.out + (static_cast<long long>(b) * L + tok[row]) * C + h * hd);
+      op[0] = make_int4(wds[0], wds[1], wds[2], wds[3]);
+      op[1] = make_int4(wds[4], wds[5], wds[6], wds[7]);
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 64);
+}
+
 // PatchMerging gather (swin_quant.py:339-344): [B, res, res, C] -> [B, (res/2)^2, 4C], channel block k
 // of output token (i, j) = input token (2 i + k % 2, 2 j + k / 2).
 template <typename T>
@@ -244,6 +455,14 @@ __global__ void avgpool_requant_kernel(const int8_t* __restrict__ x, int8_t* __r
 
 using namespace ivit;
 
+// 0: tcgen05 products where hd = 32 (default); 1: the dp4a kernel always (A/B timing, tests)
+static int g_win_variant = 1;   // TEMP until the tcgen05 variant is verified on the GPU
+extern "C" int ivit_window_attention_set_variant(int variant) {
+  const int prev = g_win_variant;
+  g_win_variant = variant;
+  return prev;
+}
+
 extern "C" int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int res, int ws, int shift,
                                         int nH, int hd, const ivit_window_attention_params_t* p, void* stream) {
   if (!p || !p->bias_codes) return fail(IVIT_ERR_BAD_ARG, "window attention: params / bias codes NULL");
@@ -262,8 +481,18 @@ extern "C" int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t*
   a.nx0 = 15.f * a.x0;                                                       // :155
   a.out_shift = 1.f / ldexpf(1.f, 31 - p->output_bit + 1);
   const bool table = p->exp_table != nullptr && (shift == 0 || p->mask_clamps != 0) && p->qmin2 >= -128 && p->qmax2 <= 127;
-  if (table) window_attention_i8_kernel<true><<<static_cast<int>(ctas), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
-  else window_attention_i8_kernel<false><<<static_cast<int>(ctas), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = static_cast<int>(ctas);
+  // hd = 32 (every Swin size): the two products on tcgen05; otherwise (or variant 1) the dp4a kernel
+  const bool tc = g_win_variant == 0 && hd == 32 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+                  (reinterpret_cast<uintptr_t>(qkv) & 3) == 0;
+  if (tc) {
+    if (table) window_attention_tc_kernel<true><<<grid, 256, 0, st>>>(a);
+    else window_attention_tc_kernel<false><<<grid, 256, 0, st>>>(a);
+    return check_launch("window_attention_tc_kernel");
+  }
+  if (table) window_attention_i8_kernel<true><<<grid, 256, 0, st>>>(a);
+  else window_attention_i8_kernel<false><<<grid, 256, 0, st>>>(a);
   return check_launch("window_attention_i8_kernel");
 }
 

@@ -269,6 +269,11 @@ def window_attention(qkv: torch.Tensor, B: int, res: int, ws: int, shift: int, n
     return (out, probs) if want_probs else out
 
 
+def set_window_attention_variant(variant: int) -> int:
+    """0: tcgen05 products where head_dim = 32; 1: dp4a kernel always.  Returns the old value."""
+    return _cabi.load().ivit_window_attention_set_variant(int(variant))
+
+
 def patch_merge_gather(x: torch.Tensor, B: int, res: int, Cdim: int, out: torch.Tensor | None = None) -> torch.Tensor:
     """[B, res, res, C] -> [B, (res/2)^2, 4C] (PatchMerging's strided slices + cat)."""
     assert x.dtype in (torch.int8, torch.int16) and x.is_contiguous() and x.numel() == B * res * res * Cdim

@@ -191,9 +191,24 @@ def _window_attention_case(res, ws, shift, nH, hd, seed, s2_target, use_table):
     return clamps
 
 
+@pytest.fixture(params=[0, 1], ids=["tcgen05", "dp4a"])
+def window_variant(request):
+    prev = ops.set_window_attention_variant(request.param)
+    yield request.param
+    ops.set_window_attention_variant(prev)
+
+
+def test_swin_toy_on_the_dp4a_window_kernel():
+    prev = ops.set_window_attention_variant(1)
+    try:
+        _run_case("swin_toy", 2)
+    finally:
+        ops.set_window_attention_variant(prev)
+
+
 @pytest.mark.parametrize("use_table", [False, True])
 @pytest.mark.parametrize("s2_target", [0.03, 0.25, 0.6, 1.7])
-def test_window_attention_kernel(s2_target, use_table):
+def test_window_attention_kernel(s2_target, use_table, window_variant):
     """Computed and tabulated exp terms, without and with the shift mask, from scales at which a masked score
     provably clamps (table path) up to scales at which it does not (masked scores can win the row maximum:
     the kernel must then take the computed path even when a table is attached)."""
@@ -202,6 +217,9 @@ def test_window_attention_kernel(s2_target, use_table):
     assert clamps == (s2_target < 0.4)
     _window_attention_case(8, 4, 2, 2, 32, seed=3, s2_target=s2_target, use_table=use_table)      # 4x4 windows
     _window_attention_case(7, 7, 0, 6, 32, seed=4, s2_target=s2_target, use_table=use_table)      # one window, 6 heads
+    _window_attention_case(16, 8, 4, 2, 32, seed=5, s2_target=s2_target, use_table=use_table)     # 8x8 windows: 64 tokens
+    if window_variant == 1:
+        _window_attention_case(14, 7, 3, 2, 64, seed=6, s2_target=s2_target, use_table=use_table)  # head_dim 64: dp4a only
 
 
 def test_patch_merge_gather_and_avgpool():
