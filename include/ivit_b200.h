@@ -227,6 +227,9 @@ typedef struct {
    * and returns -floor(-1/s2).  NULL: computed per score. */
   const float* exp_table;
   int mask_clamps;
+  /* optional int32 [nH, ws*ws, ws*ws]: the identity branch of qact2 evaluated once per layer,
+   * rint(float64(bias_codes) * mult_bias) (quant_utils.py:232-245; batch independent).  NULL: per score. */
+  const int32_t* bias_terms;
 } ivit_window_attention_params_t;
 int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int res, int ws, int shift, int nH,
                              int hd, const ivit_window_attention_params_t* p, void* stream);

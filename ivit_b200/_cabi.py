@@ -66,6 +66,7 @@ class WindowAttentionParams(C.Structure):
         ("qmin_out", C.c_int), ("qmax_out", C.c_int),
         ("exp_table", C.c_void_p),
         ("mask_clamps", C.c_int),
+        ("bias_terms", C.c_void_p),
     ]
 
 

@@ -85,6 +85,7 @@ window_attention_i8_kernel(const WinAttnArgs a) {
   __shared__ int lab[WMAX];
   __shared__ float srow[WMAX];                               // row max, then the row's factor
   const int ws = a.ws, N = ws * ws, hd = a.hd, res = a.res, nWx = res / ws, nW = nWx * nWx;
+  const uint32_t magicN = 0xFFFFFFFFu / static_cast<uint32_t>(N) + 1u;   // t / N == umulhi(t, magicN) for t < 2^16
   const int h = blockIdx.x % a.nH;
   const int w = (blockIdx.x / a.nH) % nW;
   const int b = blockIdx.x / (a.nH * nW);
@@ -114,15 +115,16 @@ window_attention_i8_kernel(const WinAttnArgs a) {
   __syncthreads();
   // S = q k^T -> qact_attn1 -> qact2 (+ relative-position bias identity) -> (+ mask) -> x / s
   const int8_t* bias = a.p.bias_codes + static_cast<long long>(h) * N * N;
+  const int32_t* bterms = a.p.bias_terms != nullptr ? a.p.bias_terms + static_cast<long long>(h) * N * N : nullptr;
   for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
-    const int i = t / N, j = t - i * N;
+    const int i = static_cast<int>(__umulhi(static_cast<uint32_t>(t), magicN)), j = t - i * N;
     int acc = 0;
     const int* qi = reinterpret_cast<const int*>(sq + i * QK_LD);
     const int* kj = reinterpret_cast<const int*>(sk + j * QK_LD);
     for (int c = 0; c < wpr; ++c) acc = __dp4a(qi[c], kj[c], acc);
     const int c1 = clampi(requant_i32_fast(acc, a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);        // qact_attn1
-    const int c2 = clampi(requant_i32_fast(c1, a.p.mult2) + requant_i32_fast(__ldg(bias + t), a.p.mult_bias),
-                          a.p.qmin2, a.p.qmax2);                                                      // qact2 (:147)
+    const int bterm = bterms != nullptr ? __ldg(bterms + t) : requant_i32_fast(__ldg(bias + t), a.p.mult_bias);
+    const int c2 = clampi(requant_i32_fast(c1, a.p.mult2) + bterm, a.p.qmin2, a.p.qmax2);            // qact2 (:147)
     if (TABLE) {
       sx[i][j] = __int_as_float((a.shift > 0 && lab[i] != lab[j]) ? kMasked : c2);
     } else {
@@ -149,7 +151,7 @@ window_attention_i8_kernel(const WinAttnArgs a) {
   if (TABLE) {
     const float e_mask = -a.x0;
     for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
-      const int i = t / N, j = t - i * N;
+      const int i = static_cast<int>(__umulhi(static_cast<uint32_t>(t), magicN)), j = t - i * N;
       const int c = __float_as_int(sx[i][j]);
       const float* trow = a.p.exp_table + (__float_as_int(srow[i]) + 128) * 256 + 128;
       sx[i][j] = c == kMasked ? e_mask : __ldg(trow + c);
@@ -158,7 +160,7 @@ window_attention_i8_kernel(const WinAttnArgs a) {
     ExpShiftParams ep;
     ep.x0 = a.x0; ep.nx0 = a.nx0; ep.n = 15;
     for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
-      const int i = t / N, j = t - i * N;
+      const int i = static_cast<int>(__umulhi(static_cast<uint32_t>(t), magicN)), j = t - i * N;
       sx[i][j] = exp_shift(__fsub_rn(sx[i][j], srow[i]), ep);
     }
   }
@@ -223,6 +225,7 @@ window_attention_tc_kernel(const WinAttnArgs a) {
   uint8_t* const sP = tiles + 12288;         // [128][64 B]
   uint8_t* const sVt = tiles + 20480;        // [32][64 B]   v transposed: [d][token]
   const int ws = a.ws, N = ws * ws, res = a.res, nWx = res / ws, nW = nWx * nWx;
+  const uint32_t magicN = 0xFFFFFFFFu / static_cast<uint32_t>(N) + 1u;   // t / N == umulhi(t, magicN) for t < 2^16
   constexpr int hd = 32;
   const int h = blockIdx.x % a.nH;
   const int w = (blockIdx.x / a.nH) % nW;
@@ -252,7 +255,8 @@ window_attention_tc_kernel(const WinAttnArgs a) {
   // gather q, k (K-major rows, bytes 32..63 zero) and v^T into the swizzled operand tiles
   constexpr int wpr = hd / 4;
   for (int t = threadIdx.x; t < 3 * N * wpr; t += blockDim.x) {
-    const int which = t / (N * wpr), r = (t / wpr) % N, c4 = t % wpr;
+    const int rr = t / wpr, c4 = t % wpr;                                  // wpr is a compile-time 8
+    const int which = static_cast<int>(__umulhi(static_cast<uint32_t>(rr), magicN)), r = rr - which * N;
     const int8_t* src = a.qkv + (static_cast<long long>(b) * L + tok[r]) * 3 * C + which * C + h * hd + 4 * c4;
     const int v = __ldg(reinterpret_cast<const int*>(src));
     if (which < 2) {
@@ -302,12 +306,13 @@ window_attention_tc_kernel(const WinAttnArgs a) {
   __syncthreads();
   // qact_attn1 -> qact2 (+ relative-position bias identity) -> (+ mask) -> x / s   (as in the kernel above)
   const int8_t* bias = a.p.bias_codes + static_cast<long long>(h) * N * N;
+  const int32_t* bterms = a.p.bias_terms != nullptr ? a.p.bias_terms + static_cast<long long>(h) * N * N : nullptr;
   for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
-    const int i = t / N, j = t - i * N;
+    const int i = static_cast<int>(__umulhi(static_cast<uint32_t>(t), magicN)), j = t - i * N;
     const int acc = sacc[i][j];
     const int c1 = clampi(requant_i32_fast(acc, a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
-    const int c2 = clampi(requant_i32_fast(c1, a.p.mult2) + requant_i32_fast(__ldg(bias + t), a.p.mult_bias),
-                          a.p.qmin2, a.p.qmax2);
+    const int bterm = bterms != nullptr ? __ldg(bterms + t) : requant_i32_fast(__ldg(bias + t), a.p.mult_bias);
+    const int c2 = clampi(requant_i32_fast(c1, a.p.mult2) + bterm, a.p.qmin2, a.p.qmax2);
     if (TABLE) {
       sx[i][j] = __int_as_float((a.shift > 0 && lab[i] != lab[j]) ? kMasked : c2);
     } else {
@@ -333,7 +338,7 @@ window_attention_tc_kernel(const WinAttnArgs a) {
   if (TABLE) {
     const float e_mask = -a.x0;
     for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
-      const int i = t / N, j = t - i * N;
+      const int i = static_cast<int>(__umulhi(static_cast<uint32_t>(t), magicN)), j = t - i * N;
       const int c = __float_as_int(sx[i][j]);
       const float* trow = a.p.exp_table + (__float_as_int(srow[i]) + 128) * 256 + 128;
       sx[i][j] = c == kMasked ? e_mask : __ldg(trow + c);
@@ -342,7 +347,7 @@ window_attention_tc_kernel(const WinAttnArgs a) {
     ExpShiftParams ep;
     ep.x0 = a.x0; ep.nx0 = a.nx0; ep.n = 15;
     for (int t = threadIdx.x; t < N * N; t += blockDim.x) {
-      const int i = t / N, j = t - i * N;
+      const int i = static_cast<int>(__umulhi(static_cast<uint32_t>(t), magicN)), j = t - i * N;
       sx[i][j] = exp_shift(__fsub_rn(sx[i][j], srow[i]), ep);
     }
   }
@@ -376,7 +381,7 @@ window_attention_tc_kernel(const WinAttnArgs a) {
   __syncwarp();
   if (a.probs != nullptr) {
     uint8_t* pr = a.probs + (static_cast<long long>(b * nW + w) * a.nH + h) * N * N;
-    for (int t = threadIdx.x; t < N * N; t += blockDim.x) pr[t] = sP[sw64_off(t / N, t % N)];
+    for (int t = threadIdx.x; t < N * N; t += blockDim.x) { const int i = static_cast<int>(__umulhi(static_cast<uint32_t>(t), magicN)); pr[t] = sP[sw64_off(i, t - i * N)]; }
   }
   if (warp < 2) {                              // O rows from TMEM -> qact3 -> the token's image position
     mbar_wait(&bars[1], 0);
@@ -456,7 +461,7 @@ __global__ void avgpool_requant_kernel(const int8_t* __restrict__ x, int8_t* __r
 using namespace ivit;
 
 // 0: tcgen05 products where hd = 32 (default); 1: the dp4a kernel always (A/B timing, tests)
-static int g_win_variant = 1;   // TEMP until the tcgen05 variant is verified on the GPU
+static int g_win_variant = 0;
 extern "C" int ivit_window_attention_set_variant(int variant) {
   const int prev = g_win_variant;
   g_win_variant = variant;

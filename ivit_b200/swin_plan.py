@@ -140,6 +140,12 @@ class FrozenSwinPlan(GraphCaptureMixin):
         a.mult2 = float(hm.dyadic_mult(s_a1, s2).reshape(-1)[0])
         a.mult_bias = float(hm.dyadic_mult(s_tab, s2).reshape(-1)[0])
         a.qmin2, a.qmax2 = -128, 127
+        # identity branch of qact2, batch independent: rint(bias * m 2^-e) in float64 (exact product: 8 + 32 bits)
+        terms = np.rint(np.ascontiguousarray(bias).astype(np.float64) * a.mult_bias)
+        if np.abs(terms).max() < 2 ** 31 and not self.host_only:
+            terms_dev = self._dev(terms.astype(np.int64), torch.int32)
+            self._keep.append(terms_dev)
+            a.bias_terms = terms_dev.data_ptr()
         a.s2 = float(s2[0])
         a.output_bit = 8
         # exp term tabulated over (row-max code, code) by the library's own arithmetic; a masked score must
