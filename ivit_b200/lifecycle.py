@@ -24,12 +24,45 @@ _FREEZABLE = (_m.QuantAct, _m.QuantLinear, _m.QuantConv2d, _m.QuantMatMul, _m.IV
               _m.IVITIntGELU, _m.IBERTIntGELU, _m.IVITIntSoftmax, _m.IBERTIntSoftmax)
 
 
+class _FusedPlanForward:
+    """``model.forward`` of a frozen Swin model: the integer forward as the fused static plan.
+
+    The frozen module path exchanges integer-code carriers between modules and recognises the call
+    patterns of vit_quant.py; swin_quant.py's glue (torch.roll, window partition, the bias gather, the float
+    mask add) has no carrier form, so a frozen ``SwinTransformer`` runs as ``FrozenSwinPlan`` instead: the
+    same kernels, bit-identical logits, built once per device from the model's own ``state_dict``."""
+
+    def __init__(self, model: nn.Module):
+        self._model = model
+        self._plans = {}
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        from . import _cabi
+        from .api import swin_config_from_model
+        from .swin_plan import FrozenSwinPlan
+        if not x.is_cuda:
+            raise _cabi.IvitKernelError("a frozen model runs the integer kernels: CUDA tensors only (no CPU fallback); "
+                                        "use unfreeze_model() for the float-simulated calibration mode")
+        key = (x.device.type, x.device.index)
+        if key not in self._plans:
+            self._plans[key] = FrozenSwinPlan(swin_config_from_model(self._model), self._model.state_dict(), x.device)
+        return self._plans[key].forward(x.float().contiguous()).clone()
+
+
+def _is_swin(model: nn.Module) -> bool:
+    return hasattr(model, "layers") and not hasattr(model, "blocks") and hasattr(model, "patch_embed") and \
+        all(hasattr(st, "blocks") for st in model.layers)
+
+
 def freeze_model(model: nn.Module) -> nn.Module:
     """model_utils.py ``freeze_model``: every module that has ``fix()`` stops updating its running
-    statistics; from here on the forward is the integer path."""
+    statistics; from here on the forward is the integer path.  A Swin model additionally gets its
+    forward routed to the fused plan (see ``_FusedPlanForward``); ``unfreeze_model`` undoes it."""
     for mod in model.modules():
         if isinstance(mod, _FREEZABLE) and hasattr(mod, "fix"):
             mod.fix()
+    if _is_swin(model):
+        model.__dict__["forward"] = _FusedPlanForward(model)
     return model
 
 
@@ -38,6 +71,8 @@ def unfreeze_model(model: nn.Module) -> nn.Module:
     for mod in model.modules():
         if isinstance(mod, _FREEZABLE) and hasattr(mod, "unfix"):
             mod.unfix()
+    if isinstance(model.__dict__.get("forward"), _FusedPlanForward):
+        del model.__dict__["forward"]
     return model
 
 

@@ -163,6 +163,14 @@ def test_swin_caller_calibrates_to_the_reference_ranges():
     from ivit_b200.api import config_from_model
     import dataclasses
     assert dataclasses.replace(config_from_model(model), name=cfg.name) == cfg
+    # frozen = integer kernels = CUDA only, also for the plan-routed Swin forward; unfreeze restores the module forward
+    from ivit_b200 import lifecycle
+    lifecycle.freeze_model(model)
+    with pytest.raises(IvitKernelError):
+        model(synth_images(1, cfg, seed=0))
+    lifecycle.unfreeze_model(model)
+    with torch.no_grad():
+        assert model(synth_images(1, cfg, seed=0)).shape == (1, cfg.num_classes)
 
 
 def _build_pair(case):

@@ -222,6 +222,23 @@ def test_window_attention_kernel(s2_target, use_table, window_variant):
         _window_attention_case(14, 7, 3, 2, 64, seed=6, s2_target=s2_target, use_table=use_table)  # head_dim 64: dp4a only
 
 
+def test_lifecycle_freeze_runs_a_swin_model_on_the_kernels():
+    """lifecycle: load ranges -> freeze_model -> model(x) on CUDA == oracle; unfreeze_model restores the module forward."""
+    from ivit_b200 import lifecycle
+    from swin_caller import SwinTransformer
+    cfg, state, _ = load_swin_case("swin_toy")
+    model = SwinTransformer(cfg)
+    lifecycle.load_checkpoint(model, {"model": {k: torch.as_tensor(v) for k, v in state.items()}})
+    model.cuda().eval()
+    lifecycle.freeze_model(model)
+    x = synth_images(3, cfg, seed=4)
+    with torch.no_grad():
+        got = model(x.cuda()).cpu().numpy()
+    assert np.array_equal(got, SO.SwinOracle(cfg, state).forward(x.numpy()))
+    lifecycle.unfreeze_model(model)
+    assert "forward" not in model.__dict__ and model.qact_input.running_stat is True
+
+
 def test_patch_merge_gather_and_avgpool():
     rng = np.random.default_rng(0)
     B, res, C = 3, 8, 96
