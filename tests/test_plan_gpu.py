@@ -74,6 +74,21 @@ def test_16bit_fresh_inputs_and_graph_replay():
     assert np.array_equal(g(x.cuda()).cpu().numpy(), logits)
 
 
+@pytest.mark.parametrize("batch", [1, 7])
+def test_odd_batch_sizes(batch):
+    """Ragged sizes: one image, and a batch whose token count (7 x 65) is not a multiple of any tile."""
+    _run_case("toy_ivit", batch, seed=3)
+    _run_case("toy_ibert_w16", batch, seed=4)
+
+
+def test_empty_batch():
+    cfg, state, _ = load_case("toy_ivit")
+    plan = FrozenVitPlan(cfg, state, "cuda")
+    out = plan.forward(torch.zeros((0, 3, cfg.img_size, cfg.img_size), device="cuda"))
+    torch.cuda.synchronize()
+    assert tuple(out.shape) == (0, cfg.num_classes)
+
+
 def test_fresh_inputs_and_graph_replay():
     cfg, plan, x, logits, _ = _run_case("toy_ivit", 3, seed=11)
     g = plan.capture(3)

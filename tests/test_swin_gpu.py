@@ -87,6 +87,15 @@ def test_swin_toy_fresh_inputs_batch3():
     _run_case("swin_toy", 3, seed=5)
 
 
+def test_swin_single_image_and_empty_batch():
+    _run_case("swin_toy", 1, seed=6)
+    cfg, state, _ = load_swin_case("swin_toy")
+    plan = FrozenSwinPlan(cfg, state, "cuda")
+    out = plan.forward(torch.zeros((0, 3, cfg.img_size, cfg.img_size), device="cuda"))
+    torch.cuda.synchronize()
+    assert tuple(out.shape) == (0, cfg.num_classes)
+
+
 def test_swin_tiny_configs3():
     """BASELINE.json configs[3]: Swin-Tiny INT8 window attention (shifted windows), 224x224."""
     _, _, logits, fix, ntaps = _run_case("swin_tiny", 2)
