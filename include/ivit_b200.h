@@ -27,6 +27,9 @@ extern "C" {
 
 /* Library / device probe.  ivit_abi_version() needs no GPU. */
 int ivit_abi_version(void);
+/* Programmatic dependent launch of the hot kernels (GEMM, attention, LayerNorm, GELU table): their prologues
+ * overlap the predecessor's tail inside a stream / CUDA graph.  Returns the previous setting.  Process-wide. */
+int ivit_set_pdl(int on);
 int ivit_device_sm(int* major, int* minor);           /* cudaGetDeviceProperties of current device */
 const char* ivit_last_error(void);
 

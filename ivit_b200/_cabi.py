@@ -72,6 +72,7 @@ class WindowAttentionParams(C.Structure):
 
 _SIGS = {
     "ivit_abi_version": (C.c_int, []),
+    "ivit_set_pdl": (C.c_int, [C.c_int]),
     "ivit_device_sm": (C.c_int, [C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "ivit_last_error": (C.c_char_p, []),
     "ivit_quantize_f32_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_int64, C.c_void_p]),
@@ -145,6 +146,8 @@ def load(build_if_missing: bool = True):
         fn = getattr(lib, name)   # AttributeError if the header and the library disagree
         fn.restype = res
         fn.argtypes = args
+    if os.environ.get("IVIT_PDL") is not None:          # A/B switch for programmatic dependent launch
+        lib.ivit_set_pdl(int(os.environ["IVIT_PDL"] != "0"))
     _LIB = lib
     return lib
 

@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libivit_b200.so")
 SOURCES = ["rowwise.cu", "rowwise16.cu", "swin.cu", "gemm_i8.cu", "attention.cu"]
-HEADERS = ["ptx.cuh", "intmath.cuh"]
+HEADERS = ["ptx.cuh", "intmath.cuh", "launch.cuh"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC",

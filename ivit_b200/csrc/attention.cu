@@ -15,6 +15,7 @@
 
 #include "intmath.cuh"
 #include "ivit_b200.h"
+#include "launch.cuh"
 #include "ptx.cuh"
 
 namespace ivit {
@@ -172,6 +173,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                   // programmatic dependent launch: qkv is the predecessor's output
 
   if (threadIdx.x == 0) {
     mbar_arrive_expect_tx(&bars[0], 128 * HD + a.NKP * HD);
@@ -426,6 +428,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         *reinterpret_cast<int4*>(op + 16 * j) = make_int4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
     }
   }
+  pdl_launch_dependents();      // late: the grid has more CTAs than fit, the successor must not crowd them out
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, 256);
@@ -489,7 +492,8 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
     dim3 grid(B * H, (N + 127) / 128);
-    kernel<<<grid, 128 * tpr, smem, st>>>(tq, tk, tv, a);
+    e = launch_kernel(kernel, grid, dim3(128 * tpr), smem, st, tq, tk, tv, a);
+    if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
     return 0;
   };
   if (p16) {

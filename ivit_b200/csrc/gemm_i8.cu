@@ -15,6 +15,7 @@
 
 #include "intmath.cuh"
 #include "ivit_b200.h"
+#include "launch.cuh"
 #include "ptx.cuh"
 
 namespace ivit {
@@ -534,6 +535,10 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // programmatic dependent launch: everything above overlapped the predecessor's tail; the grid is one
+  // CTA per SM and fully resident, so the successor may be scheduled as soon as CTAs here retire
+  pdl_wait();
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ===================================================== TMA producer (channel block fastest:
@@ -938,7 +943,9 @@ static int launch_cl(const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& ar
   }
   const int ntiles = ((args.M + Cfg::TB - 1) / Cfg::TB) * ((args.N + Cfg::CB - 1) / Cfg::CB);
   const int grid = ntiles < sm_count() ? ntiles : sm_count();
-  gemm_i8_cl_kernel<TB, MODE, CHECKED><<<grid, Cfg::THREADS, Cfg::SMEM, st>>>(tmA, tmW, args);
+  cudaError_t le = launch_kernel(gemm_i8_cl_kernel<TB, MODE, CHECKED>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM, st, tmA,
+                                 tmW, args);
+  if (le != cudaSuccess) return fail(static_cast<int>(le), cudaGetErrorString(le));
   return check_launch("gemm_i8_cl_kernel");
 }
 

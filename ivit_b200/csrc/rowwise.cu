@@ -4,6 +4,8 @@
 // access, shuffle reductions.  All arithmetic through intmath.cuh (bit-exact replay).
 #include "intmath.cuh"
 #include "ivit_b200.h"
+#include "launch.cuh"
+#include "ptx.cuh"
 
 namespace ivit {
 
@@ -323,6 +325,7 @@ layernorm_ivit_requant4_kernel(const int8_t* __restrict__ x, long long ldx, int8
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
+  pdl_wait();                   // programmatic dependent launch: the rows are the predecessor's output
   prefetch(blockIdx.x * 8 + warp, 0);
   __syncthreads();
   int buf = 0;
@@ -431,6 +434,7 @@ layernorm_ivit_requant4_kernel(const int8_t* __restrict__ x, long long ldx, int8
     }
     __syncwarp();                 // the staged rows are overwritten by the prefetch two iterations on
   }
+  pdl_launch_dependents();
 }
 
 // ibert_modules.py:112-158 followed by QuantAct.  shift_pow = 2^shift, inv_shift_pow = 2^-shift.
@@ -538,6 +542,7 @@ gelu_lut_apply_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, co
                       int rows, int C) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
+  pdl_wait();                   // programmatic dependent launch: x is the predecessor's output
   if (row >= rows) return;
   const int4* xr = reinterpret_cast<const int4*>(x + static_cast<long long>(row) * C);
   int4* orow = reinterpret_cast<int4*>(out + static_cast<long long>(row) * C);
@@ -691,6 +696,16 @@ extern "C" int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float i
 }
 
 // 0: packed-lane kernel where C % 128 == 0 (default); 1: strided-lane kernel always (A/B, tests)
+static int g_pdl = 0;
+namespace ivit {
+int pdl_enabled() { return g_pdl; }
+}
+extern "C" int ivit_set_pdl(int on) {
+  const int prev = g_pdl;
+  g_pdl = on != 0;
+  return prev;
+}
+
 static int g_ln_variant = 0;
 extern "C" int ivit_layernorm_set_variant(int variant) {
   const int prev = g_ln_variant;
@@ -709,8 +724,9 @@ static int launch_ln(int kind, const int8_t* x, long long ldx, int8_t* out, int 
     const int pgrid = min((groups + 7) / 8, 148 * 4);     // persistent: a few CTAs per SM
     if constexpr (NPL % 4 == 0) {
       if (g_ln_variant == 0) {
-        layernorm_ivit_requant4_kernel<NPL / 4, R, 2><<<pgrid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult,
-                                                                            qmin, qmax);
+        cudaError_t le = launch_kernel(layernorm_ivit_requant4_kernel<NPL / 4, R, 2>, dim3(pgrid), dim3(256), 0, st, x, ldx,
+                                       out, rows, s_in, bias_int, sf, mult, qmin, qmax);
+        if (le != cudaSuccess) return fail(static_cast<int>(le), cudaGetErrorString(le));
         return check_launch("layernorm_requant4_kernel");
       }
     }
@@ -794,7 +810,11 @@ extern "C" int ivit_gelu_lut_apply_i8(const int8_t* x, int8_t* out, const int8_t
   if (rows <= 0) return 0;
   if (C % 16 != 0 || C > 6144) return fail(IVIT_ERR_UNSUPPORTED, "gelu: C % 16 == 0 and C <= 6144 required");
   if (C <= 3072)
-    gelu_lut_apply_kernel<6><<<(rows + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, out, lut, rows, C);
+  {
+    cudaError_t le = launch_kernel(gelu_lut_apply_kernel<6>, dim3((rows + 7) / 8), dim3(256), 0,
+                                   static_cast<cudaStream_t>(stream), x, out, lut, rows, C);
+    if (le != cudaSuccess) return fail(static_cast<int>(le), cudaGetErrorString(le));
+  }
   else      // ViT-L / Swin-B hidden widths (4096), Swin-L (6144)
     gelu_lut_apply_kernel<12><<<(rows + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, out, lut, rows, C);
   return check_launch("gelu_lut_apply_kernel");

@@ -181,6 +181,11 @@ def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=Non
     return out
 
 
+def set_pdl(on: bool) -> int:
+    """Programmatic dependent launch of the hot kernels.  Returns the old value."""
+    return _cabi.load().ivit_set_pdl(int(bool(on)))
+
+
 def set_layernorm_variant(variant: int) -> int:
     """0: packed-lane I-ViT LayerNorm kernel where C % 128 == 0; 1: strided-lane kernel always."""
     return _cabi.load().ivit_layernorm_set_variant(int(variant))
