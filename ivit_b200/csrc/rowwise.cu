@@ -67,6 +67,29 @@ quantize_patches_kernel(const float* __restrict__ x, int8_t* __restrict__ out, f
   }
 }
 
+// Small patches (Swin's 4 x 4 stem: a 48-byte output row): one float4 of an image row per thread, fully
+// coalesced reads; the float4 is row i of patch (y / P, x / P), i.e. 4 bytes at k = c P^2 + (y % P) P + x % P.
+__global__ void __launch_bounds__(256)
+quantize_patches_small_kernel(const float* __restrict__ x, int8_t* __restrict__ out, float inv_s, int B, int Cin, int H,
+                              int W, int P) {
+  const int W4 = W / 4, gw = W / P, gh = H / P, K = Cin * P * P;
+  const long long total = static_cast<long long>(B) * Cin * H * W4;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int x4 = static_cast<int>(t % W4);
+    const int y = static_cast<int>((t / W4) % H);
+    const int c = static_cast<int>((t / (static_cast<long long>(W4) * H)) % Cin);
+    const int b = static_cast<int>(t / (static_cast<long long>(W4) * H * Cin));
+    const float4 v = __ldg(reinterpret_cast<const float4*>(x) + t);
+    const int xx = 4 * x4;
+    const long long row = (static_cast<long long>(b) * gh + y / P) * gw + xx / P;
+    const int k = c * P * P + (y % P) * P + xx % P;
+    const int q0 = quant8(v.x, inv_s), q1 = quant8(v.y, inv_s), q2 = quant8(v.z, inv_s), q3 = quant8(v.w, inv_s);
+    *reinterpret_cast<uint32_t*>(out + row * K + k) =
+        (q0 & 0xff) | ((q1 & 0xff) << 8) | ((q2 & 0xff) << 16) | (static_cast<uint32_t>(q3) << 24);
+  }
+}
+
 // Plain elementwise quantiser (QuantAct without a predecessor scale on an arbitrary tensor).
 __global__ void quantize_kernel(const float* __restrict__ x, int8_t* __restrict__ out, float inv_s, long long n) {
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < n;
@@ -688,6 +711,13 @@ extern "C" int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float i
   const int k4 = Cin * P * P / 4;
   const int threads = k4 >= 256 ? 256 : (k4 + 31) / 32 * 32;      // one pass over a row where it fits
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (P <= 8) {          // short patch rows: the per-patch-row CTA walk leaves most lanes idle
+    const long long total = static_cast<long long>(B) * Cin * H * (W / 4);
+    const long long g = (total + 255) / 256;
+    quantize_patches_small_kernel<<<static_cast<int>(g < 148LL * 32 ? g : 148LL * 32), 256, 0, st>>>(x, out, inv_scale, B,
+                                                                                                 Cin, H, W, P);
+    return check_launch("quantize_patches_small_kernel");
+  }
   if (P == 16) quantize_patches_kernel<4><<<grid, threads, 0, st>>>(x, out, inv_scale, B, Cin, H, W, P);
   else if (P == 8) quantize_patches_kernel<3><<<grid, threads, 0, st>>>(x, out, inv_scale, B, Cin, H, W, P);
   else if (P == 4) quantize_patches_kernel<2><<<grid, threads, 0, st>>>(x, out, inv_scale, B, Cin, H, W, P);

@@ -411,19 +411,23 @@ window_attention_tc_kernel(const WinAttnArgs a) {
 
 // PatchMerging gather (swin_quant.py:339-344): [B, res, res, C] -> [B, (res/2)^2, 4C], channel block k
 // of output token (i, j) = input token (2 i + k % 2, 2 j + k / 2).
+// One 16-byte vector per thread (VEC elements); C % VEC == 0.
 template <typename T>
 __global__ void patch_merge_gather_kernel(const T* __restrict__ x, T* __restrict__ out, int B, int res, int C) {
-  const int r2 = res / 2;
-  const long long total = static_cast<long long>(B) * r2 * r2 * 4 * C;
+  constexpr int VEC = 16 / sizeof(T);
+  const int r2 = res / 2, cv = C / VEC;
+  const long long total = static_cast<long long>(B) * r2 * r2 * 4 * cv;
+  const int4* xin = reinterpret_cast<const int4*>(x);
+  int4* o = reinterpret_cast<int4*>(out);
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
        t += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int c = static_cast<int>(t % C);
-    const int k = static_cast<int>((t / C) % 4);
-    const long long tokq = t / (4LL * C);
+    const int c = static_cast<int>(t % cv);
+    const int k = static_cast<int>((t / cv) % 4);
+    const long long tokq = t / (4LL * cv);
     const int j = static_cast<int>(tokq % r2), i = static_cast<int>((tokq / r2) % r2);
     const int b = static_cast<int>(tokq / (r2 * r2));
-    const long long src = ((static_cast<long long>(b) * res + 2 * i + (k & 1)) * res + 2 * j + (k >> 1)) * C + c;
-    out[t] = x[src];
+    const long long src = ((static_cast<long long>(b) * res + 2 * i + (k & 1)) * res + 2 * j + (k >> 1)) * cv + c;
+    o[t] = __ldg(xin + src);
   }
 }
 
@@ -503,7 +507,11 @@ extern "C" int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t*
 
 extern "C" int ivit_patch_merge_gather(const void* x, void* out, int elem_bits, int B, int res, int C, void* stream) {
   if (res % 2 != 0) return fail(IVIT_ERR_BAD_ARG, "patch merge: resolution must be even");
-  const long long total = static_cast<long long>(B) * res * res * C;
+  if (elem_bits != 8 && elem_bits != 16) return fail(IVIT_ERR_BAD_ARG, "patch merge: elem_bits must be 8 or 16");
+  if ((static_cast<long long>(C) * elem_bits / 8) % 16 != 0 || (reinterpret_cast<uintptr_t>(x) & 15) ||
+      (reinterpret_cast<uintptr_t>(out) & 15))
+    return fail(IVIT_ERR_UNSUPPORTED, "patch merge: rows of a multiple of 16 bytes, 16-byte aligned buffers");
+  const long long total = static_cast<long long>(B) * res * res * C * (elem_bits / 8) / 16;
   if (total <= 0) return 0;
   long long g = (total + 255) / 256;
   if (g > 148LL * 16) g = 148LL * 16;
