@@ -359,11 +359,15 @@ window_attention_tc_kernel(const WinAttnArgs a) {
   }
   __syncthreads();
   // probabilities -> the u8 A operand (rows of 64 bytes; columns past the window are zero)
-  for (int t = threadIdx.x; t < N * 64; t += blockDim.x) {
-    const int i = t >> 6, j = t & 63;
-    sP[sw64_off(i, j)] =
-        j < N ? static_cast<uint8_t>(__float_as_uint(__fadd_rz(__fmul_rn(sx[i][j], srow[i]), 8388608.f)) & 0xffu)
-              : uint8_t(0);
+  for (int t = threadIdx.x; t < N * 16; t += blockDim.x) {       // four codes = one 32-bit store per step
+    const int i = t >> 4, j0 = (t & 15) << 2;
+    const float fs = srow[i];
+    uint32_t word = 0;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (j0 + u < N)
+        word |= (__float_as_uint(__fadd_rz(__fmul_rn(sx[i][j0 + u], fs), 8388608.f)) & 0xffu) << (8 * u);
+    *reinterpret_cast<uint32_t*>(sP + sw64_off(i, j0)) = word;
   }
   fence_proxy_async_smem();
   __syncthreads();
