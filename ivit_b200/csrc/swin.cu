@@ -211,7 +211,7 @@ __device__ __forceinline__ int sw64_off(int r, int byte) {       // 64-byte rows
 }
 
 template <bool TABLE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 window_attention_tc_kernel(const WinAttnArgs a) {
   __shared__ __align__(1024) uint8_t tiles[8192 + 4096 + 8192 + 2048];
   __shared__ float sx[WMAX][WMAX + 1];
