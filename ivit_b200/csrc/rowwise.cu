@@ -771,8 +771,16 @@ static int launch_ln(int kind, const int8_t* x, long long ldx, int8_t* out, int 
         return check_launch("layernorm_requant4_kernel");
       }
     }
-    layernorm_ivit_requant_kernel<NPL, R, 2><<<pgrid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin,
-                                                                   qmax);
+    static int resident_s = 0;
+    if (resident_s == 0) {
+      int nb = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, layernorm_ivit_requant_kernel<NPL, R, 2>, 256, 0) != cudaSuccess ||
+          nb < 1)
+        nb = 2;
+      resident_s = nb;
+    }
+    layernorm_ivit_requant_kernel<NPL, R, 2><<<min(pgrid, 148 * resident_s), 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int,
+                                                                                          sf, mult, qmin, qmax);
   } else {
     const float sp = ldexpf(1.f, static_cast<int>(shift));
     layernorm_ibert_requant_kernel<NPL><<<grid, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp,

@@ -377,8 +377,15 @@ static int launch_ln16(int kind, const XT* x, int64_t ldx, int8_t* out, int rows
   if (outer && kind == 0 && C == 96 && strided_tokens % 32 == 0 && (ldx * sizeof(XT)) % 16 == 0 &&
       (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
     const int quads = (rows + 3) / 4;
+    static int resident = 0;          // persistent grid = the CTAs resident at once (one wave)
+    if (resident == 0) {
+      int nb = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, layernorm96_strided_kernel<XT>, 256, 0) != cudaSuccess || nb < 1)
+        nb = 3;
+      resident = nb;
+    }
     int g = (quads + 7) / 8;
-    if (g > 148 * 8) g = 148 * 8;
+    if (g > 148 * resident) g = 148 * resident;
     layernorm96_strided_kernel<XT><<<g, 256, 0, st>>>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax);
     return check_launch("layernorm96_strided_kernel");
   }
