@@ -211,7 +211,7 @@ __device__ __forceinline__ int sw64_off(int r, int byte) {       // 64-byte rows
 }
 
 template <bool TABLE>
-__global__ void __launch_bounds__(256, 4)
+__global__ void __launch_bounds__(256, 5)
 window_attention_tc_kernel(const WinAttnArgs a) {
   __shared__ __align__(1024) uint8_t tiles[8192 + 4096 + 8192 + 2048];
   __shared__ float sx[WMAX][WMAX + 1];
@@ -290,15 +290,15 @@ window_attention_tc_kernel(const WinAttnArgs a) {
     tc_fence_after();
     const int row = 32 * warp + lane;
     const uint32_t t_row = tmem_base + (static_cast<uint32_t>(32 * warp) << 16);
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      uint32_t v[32];
-      tmem_ld32(t_row + 32 * half, v);
+#pragma unroll 1
+    for (int q4 = 0; q4 < 4; ++q4) {           // 16-column chunks: the kernel has to live in 48 registers
+      uint32_t v[16];
+      tmem_ld16(t_row + 16 * q4, v);
       tmem_ld_wait();
       if (row < N) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (32 * half + j < N) sacc[row][32 * half + j] = static_cast<int>(v[j]);
+        for (int j = 0; j < 16; ++j)
+          if (16 * q4 + j < N) sacc[row][16 * q4 + j] = static_cast<int>(v[j]);
       }
     }
     tc_fence_before();
@@ -391,21 +391,21 @@ window_attention_tc_kernel(const WinAttnArgs a) {
     mbar_wait(&bars[1], 0);
     tc_fence_after();
     const int row = 32 * warp + lane;
-    uint32_t o[32];
-    tmem_ld32(tmem_base + (static_cast<uint32_t>(32 * warp) << 16), o);
-    tmem_ld_wait();
-    if (row < N && a.out != nullptr) {
-      uint32_t wds[8];
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+      uint32_t o[16];
+      tmem_ld16(tmem_base + (static_cast<uint32_t>(32 * warp) << 16) + 16 * half, o);
+      tmem_ld_wait();
+      if (row < N && a.out != nullptr) {
+        uint32_t wds[4] = {0, 0, 0, 0};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) wds[j] = 0;
-#pragma unroll
-      for (int d = 0; d < 32; ++d) {
-        const int c = clampi(requant_i32_fast(static_cast<int>(o[d]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
-        wds[d >> 2] |= (static_cast<uint32_t>(c) & 0xffu) << (8 * (d & 3));
+        for (int d = 0; d < 16; ++d) {
+          const int c = clampi(requant_i32_fast(static_cast<int>(o[d]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
+          wds[d >> 2] |= (static_cast<uint32_t>(c) & 0xffu) << (8 * (d & 3));
+        }
+        int4* op = reinterpret_cast<int4*>(a.out + (static_cast<long long>(b) * L + tok[row]) * C + h * hd);
+        op[half] = make_int4(wds[0], wds[1], wds[2], wds[3]);
       }
-      int4* op = reinterpret_cast<int4*>(a.out + (static_cast<long long>(b) * L + tok[row]) * C + h * hd);
-      op[0] = make_int4(wds[0], wds[1], wds[2], wds[3]);
-      op[1] = make_int4(wds[4], wds[5], wds[6], wds[7]);
     }
     tc_fence_before();
   }
