@@ -207,7 +207,7 @@ layernorm_x16_requant_kernel(int kind, const XT* __restrict__ x, long long ldx, 
 // rows come in as 32-byte and leave as 16-byte vectors without shared-memory staging, and the
 // per-channel constants live in registers across the grid-stride loop.  I-ViT kind only.
 template <typename XT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 layernorm96_strided_kernel(const XT* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows, float s_in,
                            const float* __restrict__ bias_int, const float* __restrict__ sf,
                            const double* __restrict__ mult, int qmin, int qmax) {
