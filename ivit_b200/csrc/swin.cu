@@ -1,8 +1,9 @@
 // Swin-specific kernels of the I-ViT integer path (swin_quant.py): window attention with the
 // quantised relative-position bias and the float shifted-window mask, the PatchMerging gather and
-// the token average pool.  First correct version: the window attention runs on the CUDA cores
-// (dp4a) -- a 49 x 49 x 32 window is 0.15 MMAC, ~15 % of Swin-T's MACs; moving it onto tcgen05
-// (two windows per 128-row tile, hd = 32 operands) is the next step for this row.
+// the token average pool.  The window attention exists twice: `window_attention_tc_kernel` (head_dim
+// 32, default) runs both QuantMatMul products on tcgen05 kind::i8 with hand-swizzled operand tiles,
+// `window_attention_i8_kernel` (any head_dim % 4 == 0, and the cross-check) on dp4a.  Either way the
+// kernel is bound by its per-score epilogue, not by the products.
 //
 // Roll and window partition / reverse (swin_quant.py:18-50, :258-289) are pure index maps: the
 // kernel reads q / k / v of window token (iy, ix) of window (wy, wx) at image token
