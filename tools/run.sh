@@ -1,0 +1,33 @@
+#!/bin/bash
+# One parameterised GPU-box runner (replaces the round-1 run_*.sh scratch launchers).
+#   tools/run.sh <tag> <steps...>    steps: noalloc tests smoke bench benchref launches case:<name>:<batch>
+mkdir -p gpurun_out
+T=${1:-r2}; shift
+for step in "$@"; do
+case $step in
+noalloc)
+  timeout 600 python -m pytest tests/test_zz_no_alloc.py -q -m gpu -p no:cacheprovider > gpurun_out/${T}_noalloc_alone.log 2>&1
+  echo "noalloc alone exit $?"; tail -n 3 gpurun_out/${T}_noalloc_alone.log ;;
+tests)
+  timeout 1800 python -m pytest tests -x -q -m gpu --timeout 400 -p no:cacheprovider > gpurun_out/${T}_tests.log 2>&1
+  echo "tests exit $?" | tee -a gpurun_out/${T}_tests.log; grep -v -i warning gpurun_out/${T}_tests.log | tail -n 6 ;;
+smoke)
+  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${T}_smoke.log 2>&1; echo "smoke exit $?"; tail -n 1 gpurun_out/${T}_smoke.log ;;
+bench)
+  timeout 600 python bench.py > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo "bench exit $?"
+  python tools/show_bench.py gpurun_out/${T}_bench.json ;;
+benchref)
+  timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${T}_bench_ref.json 2> gpurun_out/${T}_bench_ref.err; echo "ref exit $?"
+  tail -n 1 gpurun_out/${T}_bench_ref.json | cut -c1-400 ;;
+launches)
+  timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv \
+    python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/${T}_ncu.log 2>&1
+  echo "ncu exit $?" ;;
+case:*)
+  IFS=: read -r _ name batch <<< "$step"
+  timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --case $name --batch $batch > gpurun_out/${T}_bench_$name.json 2> gpurun_out/${T}_bench_$name.err
+  echo "bench $name $batch exit $?"; python tools/show_bench.py gpurun_out/${T}_bench_$name.json ;;
+*)
+  echo "running: $step"; bash -c "$step" ;;
+esac
+done
