@@ -66,6 +66,20 @@ int ivit_gelu_lut_build(int kind, int8_t* lut, float s_in, int output_bit, doubl
 int ivit_gelu_ivit_raw_table(float* out65536, float s_in, int output_bit, void* stream);
 int ivit_gelu_lut_apply_i8(const int8_t* x, int8_t* out, const int8_t* lut, int rows, int C, void* stream);
 
+/* ---- GELU without any allocation ----------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * ivit_gelu_lut_build(kind, lut, s_in, output_bit, mult_out, qmin, qmax) followed by
+ * ivit_gelu_lut_apply_i8(x, out, lut, rows, C), but the table and the per-row maximum codes live in a
+ * file-scope device array of the library (320 KB per GPU that loads it, held until exit), so the call
+ * allocates nothing: no cudaMalloc / cudaFree, no torch allocator.  rows > IVIT_GELU_NOALLOC_MAX_ROWS returns
+ * IVIT_ERR_UNSUPPORTED (ivit_last_error() says why).  All calls share that array: it keeps the previous
+ * call's contents (every entry a call reads is rewritten by that call first), and calls that overlap on
+ * the GPU -- different streams or host threads -- race; serialise them on one stream. */
+#define IVIT_GELU_NOALLOC_MAX_ROWS 65536
+int ivit_gelu_i8_noalloc(int kind, const int8_t* x, int8_t* out, int rows, int C, float s_in, int output_bit,
+                         double mult_out, int qmin, int qmax, float* s_gelu_out_host, void* stream);
+
 /* ---- stand-alone QuantAct on integer codes (un-fused module path) -----------------------
  * quant_utils.py:193-253.  z int32 accumulators (after QuantLinear / QuantMatMul) or int8 codes
  * (after a previous QuantAct) [rows, C]; s_in/mult have C entries if per_channel else 1;

@@ -85,6 +85,8 @@ _SIGS = {
                                       C.POINTER(C.c_float), C.c_void_p]),
     "ivit_gelu_ivit_raw_table": (C.c_int, [C.c_void_p, C.c_float, C.c_int, C.c_void_p]),
     "ivit_gelu_lut_apply_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "ivit_gelu_i8_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_int,
+                                       C.c_double, C.c_int, C.c_int, C.POINTER(C.c_float), C.c_void_p]),
     "ivit_requant_i32_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_double,
                                       C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "ivit_requant_i8_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_double,

@@ -902,3 +902,119 @@ extern "C" int ivit_fill_cls_rows_i8(int8_t* out, const int8_t* cls_row, int B, 
   fill_cls_rows_kernel<<<(B * C + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(out, cls_row, B, N, C);
   return check_launch("fill_cls_rows_kernel");
 }
+
+// =============================================================================== no-allocation GELU
+// ivit_gelu_i8_noalloc: the GELU table pass for callers that cannot allocate (CUDA-graph capture, tight serving
+// loops).  No counterpart in the reference.  The scratch the two-call
+// form (ivit_gelu_lut_build + ivit_gelu_lut_apply_i8) keeps in caller memory -- the layer's [256][256] table -- and
+// the per-row maximum codes live in ONE file-scope device array, so nothing is allocated here, by torch or by
+// the CUDA runtime.  Every GPU that loads the library holds the array (320 KB) until exit; every call shares it
+// and finds the previous call's contents: each call rewrites all 65536 table entries and the `rows` maxima it
+// reads before reading them (nothing has to start at zero), and two calls that overlap on the GPU (different
+// streams, or concurrent host threads) race on it.
+namespace ivit {
+constexpr int kNoallocMaxRows = IVIT_GELU_NOALLOC_MAX_ROWS;
+struct GeluNoallocScratch {
+  int8_t lut[65536];
+  int32_t rowmax[kNoallocMaxRows];
+};
+static __device__ __align__(256) unsigned char g_gelu_noalloc_scratch[sizeof(GeluNoallocScratch)];
+
+// pass 1: one warp per row, row-max int8 code -> scratch
+__global__ void __launch_bounds__(256)
+gelu_noalloc_rowmax_kernel(const int8_t* __restrict__ x, int32_t* __restrict__ rowmax, int rows, int C) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nv = C / 16;
+  for (int row = blockIdx.x * 8 + warp; row < rows; row += gridDim.x * 8) {
+    const int4* xr = reinterpret_cast<const int4*>(x + static_cast<long long>(row) * C);
+    uint32_t m = 0x80808080u;
+    for (int idx = lane; idx < nv; idx += 32) {
+      const int4 v = __ldg(xr + idx);
+      m = __vmaxs4(m, v.x); m = __vmaxs4(m, v.y); m = __vmaxs4(m, v.z); m = __vmaxs4(m, v.w);
+    }
+    int mx = max(max(static_cast<int8_t>(m), static_cast<int8_t>(m >> 8)),
+                 max(static_cast<int8_t>(m >> 16), static_cast<int8_t>(m >> 24)));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) rowmax[row] = mx;
+  }
+}
+
+// pass 2: the row's 256-byte table line staged per warp, byte lookups (as gelu_lut_apply_kernel)
+__global__ void __launch_bounds__(256)
+gelu_noalloc_apply_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, const int8_t* __restrict__ lut,
+                          const int32_t* __restrict__ rowmax, int rows, int C) {
+  __shared__ __align__(8) uint8_t srow[8][256];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nv = C / 16;
+  for (int row = blockIdx.x * 8 + warp; row < rows; row += gridDim.x * 8) {
+    const int mx = rowmax[row];
+    __syncwarp();
+    *reinterpret_cast<uint2*>(&srow[warp][8 * lane]) = *(reinterpret_cast<const uint2*>(lut + (mx + 128) * 256) + lane);
+    __syncwarp();
+    const uint8_t* trow = srow[warp];
+    const int4* xr = reinterpret_cast<const int4*>(x + static_cast<long long>(row) * C);
+    int4* orow = reinterpret_cast<int4*>(out + static_cast<long long>(row) * C);
+    auto look4 = [&](uint32_t w) -> uint32_t {
+      w ^= 0x80808080u;
+      return trow[w & 0xffu] | (trow[(w >> 8) & 0xffu] << 8) | (trow[(w >> 16) & 0xffu] << 16) | (trow[w >> 24] << 24);
+    };
+    for (int idx = lane; idx < nv; idx += 32) {
+      const int4 v = __ldg(xr + idx);
+      int4 o;
+      o.x = look4(v.x); o.y = look4(v.y); o.z = look4(v.z); o.w = look4(v.w);
+      orow[idx] = o;
+    }
+  }
+}
+
+// Device address of the scratch array, fetched once per device with that device current.  In host code the
+// array's name is only a handle for cudaGetSymbolAddress, never a pointer a kernel may be given.
+static GeluNoallocScratch* gelu_noalloc_scratch(int* err) {
+  constexpr int kMaxDev = 64;
+  static GeluNoallocScratch* ptrs[kMaxDev] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e == cudaSuccess && (dev < 0 || dev >= kMaxDev)) e = cudaErrorInvalidDevice;
+  if (e == cudaSuccess) {
+    GeluNoallocScratch* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+    if (p != nullptr) return p;
+    void* sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_gelu_noalloc_scratch);
+    if (e == cudaSuccess && sym != nullptr) {
+      __atomic_store_n(&ptrs[dev], static_cast<GeluNoallocScratch*>(sym), __ATOMIC_RELEASE);
+      return static_cast<GeluNoallocScratch*>(sym);
+    }
+    if (e == cudaSuccess) e = cudaErrorInvalidSymbol;
+  }
+  *err = fail(static_cast<int>(e), cudaGetErrorString(e));
+  return nullptr;
+}
+}  // namespace ivit
+
+extern "C" int ivit_gelu_i8_noalloc(int kind, const int8_t* x, int8_t* out, int rows, int C, float s_in, int output_bit,
+                                    double mult_out, int qmin, int qmax, float* s_gelu_out_host, void* stream) {
+  if (kind != 0 && kind != 1) return fail(IVIT_ERR_BAD_ARG, "gelu_noalloc: kind must be 0 (ivit) or 1 (ibert)");
+  if (rows < 0) return fail(IVIT_ERR_BAD_ARG, "gelu_noalloc: rows < 0");
+  if (rows > kNoallocMaxRows)
+    return fail(IVIT_ERR_UNSUPPORTED, "gelu_noalloc: rows exceeds IVIT_GELU_NOALLOC_MAX_ROWS (65536), the size of the "
+                                      "library's static scratch; use ivit_gelu_lut_build + ivit_gelu_lut_apply_i8");
+  if (C % 16 != 0 || C <= 0 || C > 6144) return fail(IVIT_ERR_UNSUPPORTED, "gelu: C % 16 == 0 and C <= 6144 required");
+  int err = 0;
+  GeluNoallocScratch* sc = gelu_noalloc_scratch(&err);
+  if (sc == nullptr) return err;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  GeluIvitParams gi = make_gelu_ivit(s_in, output_bit);
+  GeluIbertParams gb = make_gelu_ibert(s_in);
+  const float s_out = (kind == 0) ? s_in * (1.f / ldexpf(1.f, output_bit - 1)) : gb.s_out;   // as ivit_gelu_lut_build
+  if (s_gelu_out_host) *s_gelu_out_host = s_out;
+  gelu_lut_build_kernel<<<256, 256, 0, st>>>(sc->lut, kind, gi, gb, mult_out, s_out, qmin, qmax);
+  int rc = check_launch("gelu_lut_build_kernel (noalloc)");
+  if (rc != 0 || rows == 0) return rc;
+  const int grid = min((rows + 7) / 8, 148 * 8);
+  gelu_noalloc_rowmax_kernel<<<grid, 256, 0, st>>>(x, sc->rowmax, rows, C);
+  rc = check_launch("gelu_noalloc_rowmax_kernel");
+  if (rc != 0) return rc;
+  gelu_noalloc_apply_kernel<<<grid, 256, 0, st>>>(x, out, sc->lut, sc->rowmax, rows, C);
+  return check_launch("gelu_noalloc_apply_kernel");
+}
