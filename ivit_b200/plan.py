@@ -360,7 +360,7 @@ class FrozenVitPlan(GraphCaptureMixin):
         return bufs
 
     # ------------------------------------------------------------------ launch sequence
-    def _gemm(self, A, lin: _Linear, epilogue, out, name="gemm", **kw):
+    def _gemm(self, A, lin: _Linear, epilogue, out, name="other", **kw):
         r = ops.gemm(A, lin.w, epilogue, bias=lin.bias, mult=lin.mult, s_in=lin.b_scale, qmin=lin.qmin,
                      qmax=lin.qmax, mult2=lin.mult2, mult_id=lin.mult_id, qmin2=lin.qmin2, qmax2=lin.qmax2,
                      out=out, force_slow=lin.force_slow, z_bound_ok=lin.z_bound_ok, **kw)
@@ -369,7 +369,7 @@ class FrozenVitPlan(GraphCaptureMixin):
         idn = kw.get("identity")
         by = (M * K + Nn * K + M * Nn * out.element_size() + Nn * 16 +
               (M * Nn * idn.element_size() if epilogue == EPI_RESIDUAL and idn is not None else 0))
-        self._mark("gemm_i8_tc", 2.0 * M * Nn * K, by)
+        self._mark("gemm_" + name, 2.0 * M * Nn * K, by)
         return r
 
     def _ln(self, x, s_in, nm: _Norm, out):
@@ -397,7 +397,7 @@ class FrozenVitPlan(GraphCaptureMixin):
         ops.quantize_patches(images, self.inv_s_input, cfg.patch_size, out=bufs["patches"])
         self._mark("quantize_patches", 0, 5 * images.numel())
         x, x_mid = bufs["x"], bufs["x_mid"]
-        self._gemm(bufs["patches"], self.patch, EPI_RESIDUAL, x, identity=self.pos_codes, group=cfg.num_patches,
+        self._gemm(bufs["patches"], self.patch, EPI_RESIDUAL, x, name="patch", identity=self.pos_codes, group=cfg.num_patches,
                    out_group_stride=N, out_row_off=1, id_broadcast=True)
         ops.fill_cls_rows(x.view(B, N, C), self.cls_row)
         self._mark("fill_cls_rows", 0, B * C * x.element_size())
@@ -408,27 +408,27 @@ class FrozenVitPlan(GraphCaptureMixin):
             p = f"blocks.{i}."
             self._ln(x, b.s_in, b.norm1, bufs["ln"])
             tap(p + "qact1", bufs["ln"], (B, N, C))
-            self._gemm(bufs["ln"], b.qkv, EPI_REQUANT, bufs["qkv"])
+            self._gemm(bufs["ln"], b.qkv, EPI_REQUANT, bufs["qkv"], name="qkv")
             tap(p + "attn.qact1", bufs["qkv"], (B, N, 3 * C))
             ops.attention(bufs["qkv"], B, N, H, hd, b.attn, out=bufs["attn"])
             self._mark("attention_i8", 4.0 * B * H * N * N * hd, 4 * B * N * C)
             tap(p + "attn.qact2", bufs["attn"], (B, N, C))
-            self._gemm(bufs["attn"], b.proj, EPI_RESIDUAL, x_mid, identity=x)
+            self._gemm(bufs["attn"], b.proj, EPI_RESIDUAL, x_mid, name="proj", identity=x)
             tap(p + "qact2", x_mid, (B, N, C))
             self._ln(x_mid, b.s_mid, b.norm2, bufs["ln"])
             tap(p + "qact3", bufs["ln"], (B, N, C))
-            self._gemm(bufs["ln"], b.fc1, EPI_REQUANT, bufs["h1"])
+            self._gemm(bufs["ln"], b.fc1, EPI_REQUANT, bufs["h1"], name="fc1")
             tap(p + "mlp.qact_gelu", bufs["h1"], (B, N, -1))
             ops.gelu_lut_apply(bufs["h1"], b.gelu_lut, out=bufs["h2"])
             self._mark("gelu_lut_apply", 0, 2 * bufs["h1"].numel())
             tap(p + "mlp.qact1", bufs["h2"], (B, N, -1))
-            self._gemm(bufs["h2"], b.fc2, EPI_RESIDUAL, x, identity=x_mid)
+            self._gemm(bufs["h2"], b.fc2, EPI_RESIDUAL, x, name="fc2", identity=x_mid)
             tap(p + "qact4", x, (B, N, C))
             s_x = b.s_out
         # final norm on the class-token rows only (x[:, 0], vit_quant.py:302-304), then the head
         self._ln(x.view(B, N * C)[:, :C], s_x if nblk else self._act_scale("qact1")[0], self.norm, bufs["cls"])
         tap("qact2", bufs["cls"])
-        self._gemm(bufs["cls"], self.head, EPI_LOGITS, bufs["logits"], scale_out=self.head.b_scale)
+        self._gemm(bufs["cls"], self.head, EPI_LOGITS, bufs["logits"], name="head", scale_out=self.head.b_scale)
         return bufs["logits"]
 
     def forward(self, images: torch.Tensor, taps: dict | None = None, blocks: int | None = None) -> torch.Tensor:

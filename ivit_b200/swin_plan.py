@@ -248,7 +248,7 @@ class FrozenSwinPlan(GraphCaptureMixin):
         return bufs
 
     # ------------------------------------------------------------------ launch sequence
-    def _gemm(self, A, lin: _Linear, epilogue, out, **kw):
+    def _gemm(self, A, lin: _Linear, epilogue, out, name="other", **kw):
         r = ops.gemm(A, lin.w, epilogue, bias=lin.bias, mult=lin.mult, s_in=lin.b_scale, qmin=lin.qmin, qmax=lin.qmax,
                      mult2=lin.mult2, mult_id=lin.mult_id, qmin2=lin.qmin2, qmax2=lin.qmax2, out=out,
                      force_slow=lin.force_slow, z_bound_ok=lin.z_bound_ok, **kw)
@@ -257,7 +257,7 @@ class FrozenSwinPlan(GraphCaptureMixin):
         idn = kw.get("identity")
         by = (M * K + Nn * K + M * Nn * out.element_size() + Nn * 16 +
               (M * Nn * idn.element_size() if idn is not None else 0))
-        self._mark("gemm_i8_tc", 2.0 * M * Nn * K, by)
+        self._mark("gemm_" + name, 2.0 * M * Nn * K, by)
         return r
 
     def _ln(self, x, s_in, nm: _Norm, out, strided_tokens=0):
@@ -291,7 +291,7 @@ class FrozenSwinPlan(GraphCaptureMixin):
         M = B * L
         ops.quantize_patches(images, self.inv_s_input, cfg.patch_size, out=bufs["patches"])
         self._mark("quantize_patches", 0, 5 * images.numel())
-        self._gemm(bufs["patches"], self.patch, EPI_REQUANT, bufs["pe"])
+        self._gemm(bufs["patches"], self.patch, EPI_REQUANT, bufs["pe"], name="patch")
         tap("patch_embed.qact_before_norm", bufs["pe"], (B, L, C))
         self._ln(bufs["pe"], self.s_bn, self.patch_norm, bufs["pe2"], strided_tokens=L)
         tap("patch_embed.qact", bufs["pe2"], (B, L, C))
@@ -316,20 +316,20 @@ class FrozenSwinPlan(GraphCaptureMixin):
                 p = f"layers.{i}.blocks.{j}."
                 self._ln(x, b["s_in"], b["norm1"], ln, strided)
                 tap(p + "qact1", ln, (B, L, C))
-                self._gemm(ln, b["qkv"], EPI_REQUANT, qkv)
+                self._gemm(ln, b["qkv"], EPI_REQUANT, qkv, name="qkv")
                 ops.window_attention(qkv, B, res, b["ws"], b["shift"], nH, C // nH, b["attn"], out=attn)
                 self._mark("window_attention_i8", 4.0 * M * b["ws"] ** 2 * C, 4 * M * C)
                 tap(p + "attn.qact3.imgorder", attn, (B, L, C))
-                self._gemm(attn, b["proj"], EPI_RESIDUAL, x_mid, identity=x)
+                self._gemm(attn, b["proj"], EPI_RESIDUAL, x_mid, name="proj", identity=x)
                 tap(p + "qact2", x_mid, (B, L, C))
                 self._ln(x_mid, b["s_mid"], b["norm2"], ln, strided)
                 tap(p + "qact3", ln, (B, L, C))
-                self._gemm(ln, b["fc1"], EPI_REQUANT, h1)
+                self._gemm(ln, b["fc1"], EPI_REQUANT, h1, name="fc1")
                 tap(p + "mlp.qact_gelu", h1, (B, L, Hd))
                 ops.gelu_lut_apply(h1, b["gelu_lut"], out=h2)
                 self._mark("gelu_lut_apply", 0, 2 * h1.numel())
                 tap(p + "mlp.qact1", h2, (B, L, Hd))
-                self._gemm(h2, b["fc2"], EPI_RESIDUAL, x, identity=x_mid)
+                self._gemm(h2, b["fc2"], EPI_RESIDUAL, x, name="fc2", identity=x_mid)
                 tap(p + "qact4", x, (B, L, C))
             if "reduction" in st:
                 d = f"layers.{i}.downsample."
@@ -341,7 +341,7 @@ class FrozenSwinPlan(GraphCaptureMixin):
                 self._ln(xm, st["merge_s_in"], st["merge_norm"], ln4)
                 tap(d + "qact1", ln4, (B, L // 4, 4 * C))
                 nx = bufs[cur][:Mq * 2 * C].view(Mq, 2 * C)          # x is dead after the gather
-                self._gemm(ln4, st["reduction"], EPI_REQUANT, nx)    # 8-bit codes into the int16 stream
+                self._gemm(ln4, st["reduction"], EPI_REQUANT, nx, name="merge")    # 8-bit codes into the int16 stream
                 tap(d + "qact2", nx, (B, L // 4, 2 * C))
         C = self.stages[-1]["C"]
         L = self.stages[-1]["res"] ** 2
@@ -353,5 +353,5 @@ class FrozenSwinPlan(GraphCaptureMixin):
         ops.avgpool_requant(ln, B, L, C, self.pool_s_in, self.pool_mult, -128, 127, out=bufs["pool"])
         self._mark("avgpool_requant", 0, ln.numel() + B * C)
         tap("qact3", bufs["pool"], (B, C))
-        self._gemm(bufs["pool"], self.head, EPI_LOGITS, bufs["logits"], scale_out=self.head.b_scale)
+        self._gemm(bufs["pool"], self.head, EPI_LOGITS, bufs["logits"], name="head", scale_out=self.head.b_scale)
         return bufs["logits"]

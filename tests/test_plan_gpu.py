@@ -35,6 +35,52 @@ def _run_case(case, batch, seed=0):
     return cfg, plan, x, logits, fix
 
 
+def _run_case_at_batch(case, batch, idx, seed=0):
+    """The CUDA path at a bench-sized batch against the oracle: the plan runs all `batch` images (full-size tile
+    walks, the unchecked fast epilogues the host bound allows), the oracle runs the images `idx` of the same
+    batch (frozen inference has no cross-image statistic), and EVERY materialised boundary of those images is
+    compared bit for bit."""
+    cfg, state, fix = load_case(case)
+    x = synth_images(batch, cfg, seed=seed)
+    plan = FrozenVitPlan(cfg, state, "cuda")
+    taps = {}
+    logits = plan.forward(x.cuda(), taps=taps).cpu().numpy()
+    idx = np.asarray(idx)
+    o = VO.VitOracle(cfg, state)
+    exp_logits = o.forward(x.numpy()[idx], record=True)
+    bad = []
+    for name, t in taps.items():
+        got = t.cpu().numpy().astype(np.int64)[idx]
+        exp = VO.codes_of(o.taps[name]).astype(np.int64).reshape(got.shape)
+        n = int((got != exp).sum())
+        if n:
+            bad.append(f"{name}: {n}/{got.size}")
+    assert not bad, f"{case} @ batch {batch}: {len(bad)}/{len(taps)} boundaries differ:\n" + "\n".join(bad[:12])
+    assert np.array_equal(logits[idx], exp_logits)
+    return logits, fix, len(taps)
+
+
+def test_deit_small_b256_every_boundary_of_32_images():
+    """BASELINE.json configs[1] on the metric's own configuration (batch 256): 32 images spread over the batch
+    (SURVEY 8d asks for 32), every boundary against the oracle -- this is what runs the CHECKED=false fast
+    epilogues and the 256-token tile walk the bench times."""
+    idx = list(range(0, 12)) + list(range(122, 134)) + list(range(248, 256))
+    logits, fix, ntaps = _run_case_at_batch("deit_small_ivit", 256, idx)
+    assert ntaps >= 12 * 8 + 2
+    ref = fix["logits"]
+    assert np.allclose(logits[:len(ref)], ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
+@pytest.mark.parametrize("case,batch,idx", [
+    ("vit_base_mixed", 64, [0, 1, 2, 3, 30, 31, 32, 33, 60, 61, 62, 63]),           # configs[2] at bench size
+    ("deit_base_ibert_w16", 64, [0, 1, 2, 31, 32, 33, 62, 63]),                       # configs[4] at bench size
+])
+def test_base_models_at_bench_batch_every_boundary(case, batch, idx):
+    logits, fix, _ = _run_case_at_batch(case, batch, idx)
+    ref = fix["logits"]
+    assert np.allclose(logits[:len(ref)], ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
 @pytest.mark.parametrize("case", ["toy_ivit", "toy_ibert", "toy_mixed", "toy_ibert_intsqrt"])
 def test_toy_all_boundaries(case):
     _, _, _, logits, fix = _run_case(case, 2)
