@@ -70,6 +70,8 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=16, help="images in the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--attn-variant", type=int, default=None, help="A/B: ivit_attention_set_variant before capture")
+    ap.add_argument("--attn-tpr", type=int, default=None, help="A/B: ivit_attention_set_threads_per_row before capture")
     return ap.parse_args()
 
 
@@ -238,6 +240,12 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B = args.batch
+    if args.attn_variant is not None:
+        from ivit_b200 import ops as _ops
+        _ops.set_attention_variant(args.attn_variant)
+    if args.attn_tpr is not None:
+        from ivit_b200 import ops as _ops
+        _ops.set_attention_threads_per_row(args.attn_tpr)
     cfg, state, _ = load_any_case(args.case)
     sess = InferenceSession(cfg, state, B, dev, chunks=1)
     plan = sess.plan

@@ -200,6 +200,12 @@ typedef struct {
    * |acc| reaches 8e8 there, so attn.qact2 replays the float32 recovery round(fl32(acc*s)/s)
    * (quant_utils.py:220) before the dyadic multiply. */
   float s_pv;
+  /* optional, with exp_table / exp_table_1d: the table's saturation.  IntSoftmax clamps its argument
+   * (ivit_modules.py:155 max(x, n * x0); ibert_modules.py:288), so every entry whose row-max code exceeds the
+   * code by sat_k or more holds the same value sat_e.  The caller finds (sat_k, sat_e) by scanning the built
+   * table (bit for bit); the kernel then skips the lookup for those scores.  sat_k = 0: not used. */
+  int sat_k;
+  float sat_e;
 } ivit_attention_params_t;
 /* The integer-exp term of IntSoftmax depends only on (code, row-max code) of qact_attn1's int8
  * output: tabulate it once per frozen layer with the kernel's own arithmetic. */
@@ -213,6 +219,11 @@ int ivit_attention_i8(const int8_t* qkv, int8_t* out, int B, int N, int H, int h
 /* The kernel runs 2 or 4 threads per query row (8 or 16 warps per CTA; default 2).  Returns the
  * previous setting; other values are ignored.  Process-wide; for A/B timing and tests. */
 int ivit_attention_set_threads_per_row(int tpr);
+/* Two kernels for an 8-bit softmax output: thread = query row throughout (default; also the 16-bit kernel), or
+ * the softmax walking one query row per warp-step (every lane of a table lookup reads the same table row; more
+ * instructions, measured slower).  variant 0 = choose per call (the first), 1 = always the first, 2 = the second
+ * where it applies.  Returns the previous setting.  Process-wide; for A/B timing and tests. */
+int ivit_attention_set_variant(int variant);
 /* Debug taps of the same kernel: softmax codes [B,H,N,N] (what int_softmax emits): uint8, or
  * uint16 when output_bit = 16 (`probs` then points to uint16 storage). */
 int ivit_attention_probs_i8(const int8_t* qkv, uint8_t* probs, int B, int N, int H, int hd,

@@ -50,6 +50,8 @@ class AttentionParams(C.Structure):
         ("exp_table", C.c_void_p),
         ("exp_table_1d", C.c_void_p),
         ("s_pv", C.c_float),
+        ("sat_k", C.c_int),
+        ("sat_e", C.c_float),
     ]
 
 
@@ -116,6 +118,7 @@ _SIGS = {
     "ivit_gemm_set_layout": (C.c_int, [C.c_int]),
     "ivit_attention_set_threads_per_row": (C.c_int, [C.c_int]),
     "ivit_layernorm_set_variant": (C.c_int, [C.c_int]),
+    "ivit_attention_set_variant": (C.c_int, [C.c_int]),
     "ivit_gemm_i8_simple": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                       C.c_int64, C.POINTER(GemmEpilogue), C.c_void_p]),
     "ivit_attention_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,

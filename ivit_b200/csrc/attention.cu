@@ -12,6 +12,7 @@
 // scratch for the per-row intermediates between the three softmax passes.
 #include <cuda.h>
 #include <cstdio>
+#include <type_traits>
 
 #include "intmath.cuh"
 #include "ivit_b200.h"
@@ -28,6 +29,7 @@ struct AttnArgs {
   int B, N, H;
   int NKP;        // N rounded up to 16: columns of S (MMA1 N)
   int KP2;        // N rounded up to 32: K extent of P.V
+  int crow;       // rows kernel: byte stride of a code row in shared memory (odd multiple of 16)
   int8_t* out;
   uint8_t* probs;  // optional debug tap [B,H,N,N] (uint8, or uint16 for a 16-bit softmax)
   float s_pv;      // 16-bit softmax: float32 scale of the P.V accumulator (s_softmax * s_v)
@@ -215,78 +217,117 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const int my_chunks = (N - cbase + 31) / 32;
   const bool warp_active = mt * 128 + quarter * 32 < N; // warp-uniform: rows past the last token do no work
 
-  // pass 1: qact_attn1 requant, row max; codes go back to TMEM
-  int cmax = -(1 << 30);
+  // pass 1: row maximum of the RAW int32 scores (qact_attn1 is monotone: the row-max code is the requantised
+  // raw maximum), nothing is written back
+  int smax = -(1 << 30);
   if (warp_active) {
     chunk_pipeline<W>(t_row, my_chunks, [&](int ci, uint32_t (&v)[W]) {
       if (ci < nfull) {
 #pragma unroll
-        for (int j = 0; j < W; ++j) {
-          const int c = clampi(requant_i32_fast(static_cast<int>(v[j]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
-          cmax = max(cmax, c);
-          v[j] = static_cast<uint32_t>(c);
-        }
+        for (int j = 0; j < W; ++j) smax = max(smax, static_cast<int>(v[j]));
       } else {
 #pragma unroll
-        for (int j = 0; j < W; ++j) {
-          const int c = clampi(requant_i32_fast(static_cast<int>(v[j]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
-          if (ci * 32 + cbase + j < N) cmax = max(cmax, c);
-          v[j] = static_cast<uint32_t>(c);
-        }
+        for (int j = 0; j < W; ++j)
+          if (ci * 32 + cbase + j < N) smax = max(smax, static_cast<int>(v[j]));
       }
-      tmem_st_w(t_row + ci * 32, v);
     });
-    tmem_st_wait();
-    sMax[q * 128 + r_loc] = cmax;
+    sMax[q * 128 + r_loc] = smax;
   }
-  tc_fence_before();
   __syncthreads();
-  tc_fence_after();
+  int cmax = 0;
   float xmax = 0.f;
   const float* trow = nullptr;
   if (warp_active) {
 #pragma unroll
-    for (int t = 0; t < TPR; ++t) cmax = max(cmax, sMax[t * 128 + r_loc]);
+    for (int t = 0; t < TPR; ++t) smax = max(smax, sMax[t * 128 + r_loc]);
+    cmax = clampi(requant_i32_fast(smax, a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
     xmax = x_eff(static_cast<float>(cmax), a.p.s_attn);   // max of un-rounded x/s (monotone in code)
     if (TABLE == 1) trow = a.exp_table + (cmax + 128) * 256 + 128;
     if (TABLE == 2) trow = sT + cmax * 16 + (lane & 15);           // entry (cmax - c) of copy lane % 16
   }
+  // scores at least sat_k codes below the row maximum all hold the table's saturated value: no lookup (fewer
+  // distinct lines per gather: the L1 tag stage is what bounds this pass)
+  const int csat = a.p.sat_k > 0 ? cmax - a.p.sat_k : -1000;
   auto term = [&](int c) -> float {
-    if (TABLE == 1) return __ldg(trow + c);
+    if (TABLE == 1) return c > csat ? __ldg(trow + c) : a.p.sat_e;
     if (TABLE == 2) return trow[-16 * c];
     return softmax_term(c, xmax, a);
   };
+  // qact_attn1 of one raw score (vit_quant.py:74-76)
+  auto code = [&](uint32_t sraw) -> int {
+    return clampi(requant_i32_cvt(static_cast<int>(sraw), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
+  };
 
-  // pass 2: exp terms -> TMEM; float32 row sum in torch's CPU order: accumulator (col % 32) is
-  // acc[col % W] of thread (col % 32) / W, fed in ascending column order.
+  // pass 2: requant -> code -> exp term -> TMEM; float32 row sum in torch's CPU order: accumulator
+  // (col % 32) is acc[col % W] of thread (col % 32) / W, fed in ascending column order.
   const int nvec = N / 8, size_ilp = nvec / 4;           // size_ilp == nfull
-  float acc[W];
+  float2 acc2[W / 2];
 #pragma unroll
-  for (int j = 0; j < W; ++j) acc[j] = 0.f;
+  for (int j = 0; j < W / 2; ++j) acc2[j] = make_float2(0.f, 0.f);
   if (warp_active) {
-    chunk_pipeline<W>(t_row, size_ilp, [&](int ci, uint32_t (&v)[W]) {
+    // software pipeline: the table lookups of chunk ci + 1 are issued before the terms of chunk ci are summed
+    // and stored, so their latency hides behind the next chunk's requantisation (two register sets)
+    {
+      uint32_t s0[W], s1[W];
+      float e0[W], e1[W];
+      auto lookups = [&](const uint32_t (&sv)[W], float (&ev)[W]) {
 #pragma unroll
-      for (int j = 0; j < W; ++j) {
-        const float e = term(static_cast<int>(v[j]));
-        acc[j] = __fadd_rn(acc[j], e);
-        v[j] = __float_as_uint(e);
+        for (int j = 0; j < W; ++j) ev[j] = term(code(sv[j]));
+      };
+      auto consume = [&](int ci, const float (&ev)[W]) {
+        uint32_t v[W];
+#pragma unroll
+        for (int j = 0; j < W; j += 2) {
+          acc2[j >> 1] = __fadd2_rn(acc2[j >> 1], make_float2(ev[j], ev[j + 1]));
+          v[j] = __float_as_uint(ev[j]);
+          v[j + 1] = __float_as_uint(ev[j + 1]);
+        }
+        tmem_st_w(t_row + ci * 32, v);
+      };
+      const int n = size_ilp;
+      if (n > 0) {
+        tmem_ld_w(t_row, s0);
+        tmem_ld_wait();
+        if (n > 1) tmem_ld_w(t_row + 32, s1);
+        lookups(s0, e0);
       }
-      tmem_st_w(t_row + ci * 32, v);
-    });
+      for (int ci = 0; ci < n; ci += 2) {
+        if (ci + 1 < n) {
+          tmem_ld_wait();
+          if (ci + 2 < n) tmem_ld_w(t_row + (ci + 2) * 32, s0);
+          lookups(s1, e1);
+        }
+        consume(ci, e0);
+        if (ci + 1 < n) {
+          if (ci + 2 < n) {
+            tmem_ld_wait();
+            if (ci + 3 < n) tmem_ld_w(t_row + (ci + 3) * 32, s1);
+            lookups(s0, e0);
+          }
+          consume(ci + 1, e1);
+        }
+      }
+    }
     if (my_chunks > size_ilp) {        // partial chunk: exp terms only; its sum is thread 0's job below
       uint32_t v[W];
       tmem_ld_w(t_row + size_ilp * 32, v);
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < W; ++j)
-        v[j] = (size_ilp * 32 + cbase + j < N) ? __float_as_uint(term(static_cast<int>(v[j]))) : 0u;
+        v[j] = (size_ilp * 32 + cbase + j < N) ? __float_as_uint(term(code(v[j]))) : 0u;
       tmem_st_w(t_row + size_ilp * 32, v);
     }
     tmem_st_wait();
-    if (q > 0) {
+  }
+  float acc[W];
 #pragma unroll
-      for (int j = 0; j < W; ++j) sAcc[(cbase + j) * 128 + r_loc] = acc[j];
-    }
+  for (int j = 0; j < W / 2; ++j) {
+    acc[2 * j] = acc2[j].x;
+    acc[2 * j + 1] = acc2[j].y;
+  }
+  if (warp_active && q > 0) {
+#pragma unroll
+    for (int j = 0; j < W; ++j) sAcc[(cbase + j) * 128 + r_loc] = acc[j];
   }
   tc_fence_before();
   __syncthreads();
@@ -340,16 +381,19 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     };
     chunk_pipeline<W>(t_row, my_chunks, [&](int ci, uint32_t (&v)[W]) {
       uint32_t w[W / 4], wh[W / 4];
+      // :175 / :315 (terms past column N were stored as 0).  floor of a value in [0, 2^22) through the 2^23
+      // magic constant (round toward zero) instead of F2I (quarter-rate XU pipe); two scores per instruction
+      // (f32x2), the code bytes gathered by PRMT
+      const float2 fs2 = make_float2(fs, fs), magic2 = make_float2(8388608.f, 8388608.f);
 #pragma unroll
-      for (int j = 0; j < W / 4; ++j) w[j] = wh[j] = 0;
-#pragma unroll
-      for (int j = 0; j < W; ++j) {
-        // :175 / :315 (terms past column N were stored as 0).  floor of a value in [0, 2^22) through
-        // the 2^23 magic constant (round toward zero) instead of F2I (quarter-rate XU pipe)
-        const uint32_t pc = __float_as_uint(__fadd_rz(__fmul_rn(__uint_as_float(v[j]), fs), 8388608.f)) &
-                            (P16 ? 0x1ffffu : 0xffu);
-        w[j >> 2] |= (pc & 0xffu) << (8 * (j & 3));
-        if (P16) wh[j >> 2] |= (pc >> 8) << (8 * (j & 3));
+      for (int j = 0; j < W / 4; ++j) {
+        const float2 p01 = __fadd2_rz(__fmul2_rn(make_float2(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1])), fs2), magic2);
+        const float2 p23 = __fadd2_rz(__fmul2_rn(make_float2(__uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3])), fs2), magic2);
+        const uint32_t b0 = __float_as_uint(p01.x), b1 = __float_as_uint(p01.y), b2 = __float_as_uint(p23.x),
+                       b3 = __float_as_uint(p23.y);
+        w[j] = __byte_perm(__byte_perm(b0, b1, 0x0040), __byte_perm(b2, b3, 0x0040), 0x5410);
+        if (P16) wh[j] = __byte_perm(__byte_perm(b0, b1, 0x0051), __byte_perm(b2, b3, 0x0051), 0x5410);   // codes <= 32768
+        else wh[j] = 0;
       }
       if (TAP && a.probs != nullptr && row < N) {
         const long long po = ((static_cast<long long>(blockIdx.x) * N + row) * N) + ci * 32 + cbase;
@@ -409,19 +453,17 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     tmem_ld_wait();
     if (row < N && a.out != nullptr) {
       uint32_t w[OW / 4];
-#pragma unroll
-      for (int j = 0; j < OW / 4; ++j) w[j] = 0;
-#pragma unroll
-      for (int j = 0; j < OW; ++j) {
-        int c;
+      auto oc = [&](uint32_t acc) -> uint32_t {
         if (P16) {
-          const double r = requant_any(static_cast<int>(o[j]), a.s_pv, a.p.mult_out);
-          c = static_cast<int>(fmin(fmax(r, static_cast<double>(a.p.qmin_out)), static_cast<double>(a.p.qmax_out)));
-        } else {
-          c = clampi(requant_i32_fast(static_cast<int>(o[j]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
+          const double r = requant_any(static_cast<int>(acc), a.s_pv, a.p.mult_out);
+          return static_cast<uint32_t>(static_cast<int>(fmin(fmax(r, static_cast<double>(a.p.qmin_out)), static_cast<double>(a.p.qmax_out))));
         }
-        w[j >> 2] |= (static_cast<uint32_t>(c) & 0xffu) << (8 * (j & 3));
-      }
+        return static_cast<uint32_t>(clampi(requant_i32_cvt(static_cast<int>(acc), a.p.mult_out), a.p.qmin_out, a.p.qmax_out));
+      };
+#pragma unroll
+      for (int j = 0; j < OW / 4; ++j)
+        w[j] = __byte_perm(__byte_perm(oc(o[4 * j]), oc(o[4 * j + 1]), 0x0040),
+                           __byte_perm(oc(o[4 * j + 2]), oc(o[4 * j + 3]), 0x0040), 0x5410);
       int8_t* op = a.out + (static_cast<long long>(b) * N + row) * C + h * HD + q * OW;
 #pragma unroll
       for (int j = 0; j < OW / 16; ++j)
@@ -429,6 +471,267 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     }
   }
   pdl_launch_dependents();      // late: the grid has more CTAs than fit, the successor must not crowd them out
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 256);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// 8-bit softmax output, second kernel: the softmax runs ONE QUERY ROW PER WARP-STEP.
+//
+// The kernel above keeps thread = query row through the whole softmax, so the 32 lanes of a table lookup
+// carry 32 different row maxima and hit 32 different 1 KB table rows: 32 tag look-ups per request, and ncu
+// shows the L1 tag stage saturated during that pass (l1tex__t_output_wavefronts 52 % of peak over the whole
+// kernel).  Here the scores are requantised once with thread = row (phase A: TMEM -> int8 codes -> shared
+// memory, row maxima on packed bytes), and then each warp walks whole rows with lane = column % 32 (phase B):
+// every lane of a lookup reads the SAME table row (<= 8 lines), the 32 lanes ARE torch's 32 float32
+// accumulators (intmath.cuh / oracle torch_sum_lastdim), the exp terms stay in registers (no TMEM round
+// trips), and a row's probability bytes leave as 32 contiguous bytes of the swizzled P tile.
+template <int TABLE, bool TAP, int NCH, int NFIX>
+__global__ void __launch_bounds__(256, 2)
+attention_rows_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                      const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
+  constexpr int TPR = 2, W = 16, OW = HD / TPR;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sP = smem;                       // 2 x [128 rows x 128 B], SWIZZLE_128B (written by the lanes)
+  uint8_t* sQ = smem + 32768;               // [128 x 64 B]  SWIZZLE_64B (TMA)
+  uint8_t* sK = sQ + 8192;                  // [<=256 x 64 B]
+  uint8_t* sV = sK + 16384;                 // [<=256 x 64 B]
+  int8_t* sC = reinterpret_cast<int8_t*>(sV + 16384);            // [128][crow] qact_attn1 codes; crow = an odd number of
+  int* sMax = reinterpret_cast<int*>(sC + 128 * a.crow);         // 16-byte units: conflict-free 16-byte stores.  [2][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sMax + 256);      // qk, v, s, o
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = warp >> 2, quarter = warp & 3;
+  const int mt = blockIdx.y;
+  const int b = blockIdx.x / a.H, h = blockIdx.x % a.H;
+  const int C = a.H * HD;
+  // NFIX: the token count as a compile-time constant (197 = 224 x 224 / 16 x 16 + class token: every DeiT / ViT
+  // of the reference's factories), so that the chunk / tail predicates of phase B fold; 0 = run-time N
+  const int N = NFIX ? NFIX : a.N;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 4; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(&bars[0], 128 * HD + a.NKP * HD);
+    tma_load_2d(sQ, &tmQ, &bars[0], h * HD, b * N + mt * 128);
+    tma_load_2d(sK, &tmK, &bars[0], C + h * HD, b * N);
+    mbar_arrive_expect_tx(&bars[1], a.KP2 * HD);
+    tma_load_2d(sV, &tmV, &bars[1], 2 * C + h * HD, b * N);
+    mbar_wait(&bars[0], 0);
+    tc_fence_after();
+    const uint32_t idesc1 = make_idesc_i8(128, a.NKP, true, true, false, false);
+#pragma unroll
+    for (int k = 0; k < HD / 32; ++k) {
+      const uint64_t da = make_smem_desc(smem_u32(sQ) + k * 32, 16, 512, kLayoutSW64);
+      const uint64_t db = make_smem_desc(smem_u32(sK) + k * 32, 16, 512, kLayoutSW64);
+      mma_i8_ss(tmem_base, da, db, idesc1, k != 0 ? 1u : 0u);
+    }
+    tc_commit(&bars[2]);
+  }
+  __syncwarp();
+
+  // ---------------------------------------------------------------- phase A: thread = query row
+  mbar_wait(&bars[2], 0);
+  tc_fence_after();
+  const int CROW = a.crow;
+  const int r_loc = quarter * 32 + lane;
+  const int row = mt * 128 + r_loc;                     // token index within the image
+  const int cbase = q * W;
+  const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + cbase;
+  const int nfull = N / 32;                             // chunks with all 32 columns valid
+  const int nchunks = (N + 31) / 32;
+  const int my_chunks = (N - cbase + 31) / 32;          // chunks in which this thread's segment has a valid column
+  const int rows_here = min(128, N - mt * 128);
+  const bool warp_active = mt * 128 + quarter * 32 < N; // warp-uniform
+  auto code = [&](uint32_t sraw) -> uint32_t {          // qact_attn1 of one raw score (vit_quant.py:74-76)
+    return static_cast<uint32_t>(
+        clampi(requant_i32_cvt(static_cast<int>(sraw), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn));
+  };
+  if (warp_active) {
+    uint32_t m4 = 0x80808080u;                          // four int8 lanes of -128
+    const uint32_t crow = smem_u32(sC) + r_loc * CROW + cbase;
+    chunk_pipeline<W>(t_row, my_chunks, [&](int ci, uint32_t (&v)[W]) {
+      uint32_t w[4];
+      if (ci < nfull) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          w[j] = __byte_perm(__byte_perm(code(v[4 * j]), code(v[4 * j + 1]), 0x0040),
+                             __byte_perm(code(v[4 * j + 2]), code(v[4 * j + 3]), 0x0040), 0x5410);
+      } else {                                          // columns past the last key never win the maximum
+        uint32_t c[W];
+#pragma unroll
+        for (int j = 0; j < W; ++j) c[j] = (ci * 32 + cbase + j < N) ? code(v[j]) : 0x80u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          w[j] = __byte_perm(__byte_perm(c[4 * j], c[4 * j + 1], 0x0040), __byte_perm(c[4 * j + 2], c[4 * j + 3], 0x0040),
+                             0x5410);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) m4 = __vmaxs4(m4, w[j]);
+      sts_v4(crow + ci * 32, w[0], w[1], w[2], w[3]);
+    });
+    sts_s32(smem_u32(sMax) + 4 * (q * 128 + r_loc), max(max(static_cast<int>(static_cast<int8_t>(m4)), static_cast<int>(static_cast<int8_t>(m4 >> 8))),
+                                max(static_cast<int>(static_cast<int8_t>(m4 >> 16)), static_cast<int>(static_cast<int8_t>(m4 >> 24)))));
+  }
+  tc_fence_before();
+  __syncthreads();
+
+  // ---------------------------------------------------------------- phase B: warp = one query row per step
+  // rows warp, warp + 8, ...: (row & 7) is a constant of the warp, so is the XOR term of the SWIZZLE_128B
+  // address.  Two rows per iteration, branch-free (NCH = compile-time bound of the 32-column chunks; predicates
+  // are warp-uniform except the column guard), so the two rows' dependent chains interleave.
+  {
+    const int left = (N / 8) & 3;                       // whole 8-vectors of the partial chunk (torch's size_ilp rest)
+    const int ntail0 = left * 8, ntail1 = N - nfull * 32;
+    const uint32_t sw = static_cast<uint32_t>(warp & 7);
+    uint32_t poff[NCH];                                 // byte offset of column 32 i + lane in a P row (no row term)
+    const bool lane_tail = lane < ntail1;               // this lane's column of the partial chunk is a key
+    auto cvalid = [&](int i) -> bool { return i < nfull || (i == nfull && lane_tail); };
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const uint32_t col = 32u * i + lane;
+      poff[i] = smem_u32(sP) + (col >> 7) * 16384u + ((((col & 127u) >> 4) ^ sw) << 4) + (col & 15u);
+    }
+    const uint32_t sC32 = smem_u32(sC) + lane, sMax32 = smem_u32(sMax);
+    constexpr int U = 2;
+    for (int r0 = warp; r0 < rows_here; r0 += 8 * U) {
+      int rr[U];
+      bool rv[U];
+      float e[U][NCH], acc[U], elast[U], pl[U], sum[U], fs[U];
+      uint32_t tidx[U];                                 // element index of table entry (row max, code 0)
+      int csat[U];                                      // codes <= csat hold the table's saturated value
+      float xmax[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        rv[u] = r0 + 8 * u < rows_here;
+        rr[u] = rv[u] ? r0 + 8 * u : r0;
+        const int cmax = max(lds_s32(sMax32 + 4 * rr[u]), lds_s32(sMax32 + 4 * (128 + rr[u])));
+        xmax[u] = TABLE == 0 ? x_eff(static_cast<float>(cmax), a.p.s_attn) : 0.f;
+        tidx[u] = TABLE == 1 ? static_cast<uint32_t>((cmax + 128) * 256 + 128) : static_cast<uint32_t>(cmax);
+        csat[u] = a.p.sat_k > 0 ? cmax - a.p.sat_k : -1000;
+      }
+      // every lane loads unconditionally: a column past the last key reads a stale code byte (any int8 is a
+      // valid table index) and its term is zeroed afterwards -- no predicated address arithmetic
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint32_t crow = sC32 + rr[u] * CROW;
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
+          const int c = lds_s8(crow + 32 * i);
+          if (TABLE == 1) e[u][i] = c > csat[u] ? __ldg(a.exp_table + (tidx[u] + static_cast<uint32_t>(c))) : a.p.sat_e;
+          else if (TABLE == 2) e[u][i] = __ldg(a.exp_table_1d + ((tidx[u] - static_cast<uint32_t>(c)) & 255u));   // stale codes wrap
+          else e[u][i] = softmax_term(c, xmax[u], a);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int i = 0; i < NCH; ++i)
+          if (i >= NCH - 3) e[u][i] = cvalid(i) ? e[u][i] : 0.f;      // NCH - 3 <= nfull by the dispatch below
+      // float32 row sum in torch's CPU order: lane = accumulator (col % 32), ascending columns; then the
+      // cascade p8[l] = acc[l] (+ the partial chunk's whole vectors) + acc[l + 8] + acc[l + 16] + acc[l + 24],
+      // sum = tail scalars + p8[0] + ... + p8[7]
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        acc[u] = 0.f;
+        elast[u] = 0.f;
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
+          acc[u] = i < nfull ? __fadd_rn(acc[u], e[u][i]) : acc[u];
+          elast[u] = i == nfull ? e[u][i] : elast[u];
+        }
+        pl[u] = acc[u];
+#pragma unroll
+        for (int v = 0; v < 3; ++v) {
+          const float t = __shfl_sync(0xffffffffu, elast[u], (lane & 7) + 8 * v);
+          pl[u] = v < left ? __fadd_rn(pl[u], t) : pl[u];
+        }
+#pragma unroll
+        for (int k = 1; k < 4; ++k) pl[u] = __fadd_rn(pl[u], __shfl_sync(0xffffffffu, acc[u], (lane & 7) + 8 * k));
+        sum[u] = 0.f;
+#pragma unroll
+        for (int j = 0; j < 7; ++j) {
+          const float t = __shfl_sync(0xffffffffu, elast[u], (ntail0 + j) & 31);
+          sum[u] = ntail0 + j < ntail1 ? __fadd_rn(sum[u], t) : sum[u];
+        }
+#pragma unroll
+        for (int l = 0; l < 8; ++l) sum[u] = __fadd_rn(sum[u], __shfl_sync(0xffffffffu, pl[u], l));
+        if (a.p.kind == 0) sum[u] = fminf(sum[u], 2147483648.f);         // ivit_modules.py:173
+        const float factor = floorf(__fdiv_rn(a.num, sum[u]));            // :174 / ibert :314
+        fs[u] = __fmul_rn(factor, a.out_shift);                           // power-of-two scaling is exact
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint32_t prow = (rr[u] >> 3) * 1024 + (rr[u] & 7) * 128;
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
+          // :175 / :315: floor of a value in [0, 2^22) through the 2^23 magic constant (round toward zero)
+          const uint32_t pc = __float_as_uint(__fadd_rz(__fmul_rn(e[u][i], fs[u]), 8388608.f));
+          if (rv[u] && i < nchunks) sts_u8(prow + poff[i], pc);
+          if (TAP && a.probs != nullptr && rv[u] && cvalid(i))
+            a.probs[(static_cast<long long>(blockIdx.x) * N + mt * 128 + rr[u]) * N + 32 * i + lane] = static_cast<uint8_t>(pc);
+        }
+      }
+    }
+  }
+  fence_proxy_async_smem();     // generic-proxy smem writes -> visible to tcgen05.mma
+  __syncthreads();
+
+  // ---------------------------------------------------------------- O = P V
+  if (threadIdx.x == 0) {
+    mbar_wait(&bars[1], 0);
+    tc_fence_after();
+    const uint32_t idesc2 = make_idesc_i8(128, HD, false, true, false, true);   // A u8 K-major, B s8 MN-major
+    const int ksteps = a.KP2 / 32;
+    for (int k = 0; k < ksteps; ++k) {
+      const uint32_t pa = smem_u32(sP) + (k >> 2) * 16384 + (k & 3) * 32;
+      const uint64_t da = make_smem_desc(pa, 16, 1024, kLayoutSW128);
+      const uint64_t db = make_smem_desc(smem_u32(sV) + k * 32 * HD, 512, 512, kLayoutSW64);
+      mma_i8_ss(tmem_base, da, db, idesc2, k != 0 ? 1u : 0u);
+    }
+    tc_commit(&bars[3]);
+  }
+  __syncwarp();
+  mbar_wait(&bars[3], 0);
+  tc_fence_after();
+  if (warp_active) {
+    uint32_t o[OW];
+    tmem_ld_w(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + q * OW, o);
+    tmem_ld_wait();
+    if (row < N && a.out != nullptr) {
+      auto oc = [&](uint32_t acc) -> uint32_t {
+        return static_cast<uint32_t>(clampi(requant_i32_cvt(static_cast<int>(acc), a.p.mult_out), a.p.qmin_out, a.p.qmax_out));
+      };
+      uint32_t w[OW / 4];
+#pragma unroll
+      for (int j = 0; j < OW / 4; ++j)
+        w[j] = __byte_perm(__byte_perm(oc(o[4 * j]), oc(o[4 * j + 1]), 0x0040),
+                           __byte_perm(oc(o[4 * j + 2]), oc(o[4 * j + 3]), 0x0040), 0x5410);
+      int8_t* op = a.out + (static_cast<long long>(b) * N + row) * C + h * HD + q * OW;
+#pragma unroll
+      for (int j = 0; j < OW / 16; ++j)
+        *reinterpret_cast<int4*>(op + 16 * j) = make_int4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+    }
+  }
+  pdl_launch_dependents();
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, 256);
@@ -458,6 +761,9 @@ static void derive_softmax_consts(AttnArgs& a, const ivit_attention_params_t* p)
 // threads per query row: 2 (8 warps per CTA; default: measured 1.60 ms/step on DeiT-S) or 4 (16 warps
 // per CTA, 64 registers, no spills: 1.67 ms/step -- more warps do not help, the passes are throughput-bound)
 static int g_attn_tpr = 2;
+// 0 / 1: attention_i8_kernel (thread = query row; measured faster: 1.30 vs 1.58 ms per DeiT-S step);
+// 2: an 8-bit softmax output runs attention_rows_kernel
+static int g_attn_variant = 0;
 
 static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int N, int H, int hd,
                             const ivit_attention_params_t* p, cudaStream_t st) {
@@ -488,6 +794,34 @@ static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int 
   const size_t smem = 1024 + (p16 ? 65536 : 32768) + 8192 + 16384 + 16384 + (p16 ? 0 : 32 * 128 * 4) + 512 * 4 + 128 * 4 + 64 +
                       (table == 2 ? 256 * 16 * 4 : 0);
   const int tpr = p16 ? 2 : g_attn_tpr;
+  a.crow = a.NKP + (((a.NKP >> 4) & 1) ? 0 : 16);
+  if (!p16 && g_attn_variant == 2) {
+    // 8-bit softmax output: the row-per-warp-step kernel
+    const size_t smem2 = 1024 + 32768 + 8192 + 16384 + 16384 + 128 * static_cast<size_t>(a.crow) + 256 * 4 + 64;
+    auto launch2 = [&](auto kernel) -> int {
+      cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem2));
+      if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
+      e = launch_kernel(kernel, dim3(B * H, (N + 127) / 128), dim3(256), smem2, st, tq, tk, tv, a);
+      if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
+      return 0;
+    };
+    const int nch = (N + 31) / 32;
+    auto pick = [&](auto nchc, auto nfixc) -> int {
+      constexpr int NC = decltype(nchc)::value, NF = decltype(nfixc)::value;
+      if (table == 2) return tap ? launch2(attention_rows_kernel<2, true, NC, NF>) : launch2(attention_rows_kernel<2, false, NC, NF>);
+      if (table == 1) return tap ? launch2(attention_rows_kernel<1, true, NC, NF>) : launch2(attention_rows_kernel<1, false, NC, NF>);
+      return tap ? launch2(attention_rows_kernel<0, true, NC, NF>) : launch2(attention_rows_kernel<0, false, NC, NF>);
+    };
+    using I0 = std::integral_constant<int, 0>;
+    if (N == 197) rc = pick(std::integral_constant<int, 7>(), std::integral_constant<int, 197>());
+    else
+    if (nch <= 2) rc = pick(std::integral_constant<int, 2>(), I0());
+    else if (nch <= 4) rc = pick(std::integral_constant<int, 4>(), I0());
+    else if (nch <= 7) rc = pick(std::integral_constant<int, 7>(), I0());
+    else rc = pick(std::integral_constant<int, 8>(), I0());
+    if (rc) return rc;
+    return check_launch("attention_rows_kernel");
+  }
   auto launch = [&](auto kernel) -> int {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
@@ -520,6 +854,12 @@ using namespace ivit;
 extern "C" int ivit_attention_set_threads_per_row(int tpr) {
   const int prev = g_attn_tpr;
   if (tpr == 2 || tpr == 4) g_attn_tpr = tpr;
+  return prev;
+}
+
+extern "C" int ivit_attention_set_variant(int variant) {
+  const int prev = g_attn_variant;
+  if (variant >= 0 && variant <= 2) g_attn_variant = variant;
   return prev;
 }
 

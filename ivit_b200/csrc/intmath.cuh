@@ -36,6 +36,11 @@ __device__ __forceinline__ int requant_i32_fast(int z, double mult) {
                     4503601774854144.0;  // 2^52 + 2^31
   return __double2loint(__fma_rn(zd, mult, 6755399441055744.0));  // 1.5 * 2^52
 }
+// The same result with the int32 -> fp64 conversion done by I2F.F64 (one issue slot on the otherwise idle
+// conversion pipe instead of XOR + MOV + DADD): for kernels bound by issue slots, not by that pipe.
+__device__ __forceinline__ int requant_i32_cvt(int z, double mult) {
+  return __double2loint(__fma_rn(__int2double_rn(z), mult, 6755399441055744.0));  // 1.5 * 2^52
+}
 __device__ __forceinline__ bool fast_requant_ok(int z) {
   return static_cast<uint32_t>(z + (1 << 22)) < (1u << 23);
 }

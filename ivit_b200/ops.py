@@ -191,6 +191,11 @@ def set_layernorm_variant(variant: int) -> int:
     return _cabi.load().ivit_layernorm_set_variant(int(variant))
 
 
+def set_attention_variant(variant: int) -> int:
+    """0 / 1: the thread-per-row attention kernel (default); 2: an 8-bit softmax output runs the row-per-warp-step kernel."""
+    return _cabi.load().ivit_attention_set_variant(int(variant))
+
+
 def set_attention_threads_per_row(tpr: int) -> int:
     """2 or 4 threads per query row in the attention kernel.  Returns the old value."""
     return _cabi.load().ivit_attention_set_threads_per_row(int(tpr))
@@ -199,6 +204,21 @@ def set_attention_threads_per_row(tpr: int) -> int:
 def set_gemm_layout(layout: int) -> int:
     """0: ivit_gemm_i8 picks its kernel per call; 1: tokens-on-lanes kernel only.  Returns the old value."""
     return _cabi.load().ivit_gemm_set_layout(int(layout))
+
+
+def _table_saturation(table: torch.Tensor):
+    """(sat_k, sat_e) of a [256][256] (row-max code, code) table: every valid entry with row-max code - code >=
+    sat_k equals sat_e bit for bit (IntSoftmax clamps its argument, ivit_modules.py:155 / ibert_modules.py:288).
+    (0, 0.0) when the table has no such tail."""
+    t = table.view(256, 256).view(torch.int32)
+    idx = torch.arange(256, device=table.device)
+    k = idx[:, None] - idx[None, :]
+    e_sat = t[255, 0]
+    differs = (k >= 0) & (t != e_sat)
+    sat_k = int(k[differs].max().item()) + 1 if bool(differs.any()) else 1
+    if sat_k >= 255:
+        return 0, 0.0
+    return sat_k, float(table.view(256, 256)[255, 0].item())
 
 
 def softmax_table_build(params: AttentionParams, device, collapse: bool = True) -> torch.Tensor:
@@ -212,6 +232,7 @@ def softmax_table_build(params: AttentionParams, device, collapse: bool = True) 
     params.exp_table_1d = None
     check(lib.ivit_softmax_table_build(C.byref(params), ptr(buf), stream()), "ivit_softmax_table_build")
     params.exp_table = buf.data_ptr()
+    params.sat_k, params.sat_e = _table_saturation(buf[:65536])
     if collapse:
         flag = torch.zeros(1, dtype=torch.int32, device=device)
         check(lib.ivit_softmax_table_collapse(ptr(buf), buf.data_ptr() + 65536 * 4, ptr(flag), stream()),

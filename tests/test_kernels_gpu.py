@@ -324,12 +324,20 @@ def _attention_case(kind, B, N, H, seed, s_qkv=0.05, a_max=None, bits=8):
     return bool(p.exp_table_1d)
 
 
-@pytest.fixture(params=[4, 2], ids=["tpr4", "tpr2"])
+@pytest.fixture(params=["rows", 4, 2], ids=["rows", "tpr4", "tpr2"])
 def threads_per_row(request):
-    """Both thread layouts of the attention kernel (4 or 2 threads per query row)."""
+    """All three forms of the 8-bit attention kernel: the row-per-warp-step kernel, and the thread-per-row
+    kernel (default) with 4 or 2 threads per query row."""
+    if request.param == "rows":
+        prev = ops.set_attention_variant(2)
+        yield request.param
+        ops.set_attention_variant(prev)
+        return
+    pv = ops.set_attention_variant(1)
     prev = ops.set_attention_threads_per_row(request.param)
     yield request.param
     ops.set_attention_threads_per_row(prev)
+    ops.set_attention_variant(pv)
 
 
 @pytest.mark.parametrize("N", [197, 64, 49, 256, 130, 1, 33, 17])
