@@ -31,8 +31,19 @@ GOP_PER_IMAGE = {"deit_small": 9.198, "deit_tiny": 2.507, "deit_base": 35.128, "
                  "swin_tiny": 8.981, "swin_toy": 0.0}
 
 
+def load_case_only(case: str):
+    """(cfg, state) of a committed ViT/DeiT or Swin case -- the GPU arm: nothing under oracle/ is imported."""
+    if case.startswith("swin"):
+        from ivit_b200.synthetic import load_swin_case
+        cfg, state, _ = load_swin_case(case)
+    else:
+        from ivit_b200.synthetic import load_case
+        cfg, state, _ = load_case(case)
+    return cfg, state
+
+
 def load_any_case(case: str):
-    """(cfg, state, oracle class) of a committed ViT/DeiT or Swin case."""
+    """(cfg, state, oracle class) of a committed ViT/DeiT or Swin case (CPU arm / cpu_baseline leg only)."""
     if case.startswith("swin"):
         from ivit_b200.synthetic import load_swin_case
         from oracle import swin_oracle as SO
@@ -70,6 +81,11 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=16, help="images in the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --batch images per GPU; strong: --batch images in total, split over the GPUs")
+    ap.add_argument("--verify", action="store_true",
+                    help="SURVEY 8e: every rank runs its shard of ONE global batch, the gathered logits must equal "
+                         "bit for bit what rank 0 computes for the whole batch on its own GPU; prints a verify line")
     ap.add_argument("--attn-variant", type=int, default=None, help="A/B: ivit_attention_set_variant before capture")
     ap.add_argument("--attn-tpr", type=int, default=None, help="A/B: ivit_attention_set_threads_per_row before capture")
     return ap.parse_args()
@@ -84,6 +100,28 @@ def peaks():
             return {"hbm_gbs": d["hbm_gbs"], "bf16_burst": d["bf16_tflops"],
                     "bf16_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
     return {"hbm_gbs": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "source": "fallback"}
+
+
+def int8_peak(pk: dict, clocks: dict | None):
+    """INT8 tensor denominator (TOP/s) and where it comes from: min(measured kind::i8 issue rate,
+    2 x measured bf16) -- profiles/r2_int8_peak.json holds this pool's measurement (tools/micro/i8_mma_peak.cu:
+    back-to-back tcgen05.mma.kind::i8 from resident operands, 16384 ops/clk/SM).  The burst pair when the SM clock
+    sampled during the timed region stayed at its maximum, else the sustained pair."""
+    at_max = bool(clocks and clocks.get("sm_mhz") and clocks.get("sm_max_mhz") and
+                  clocks["sm_mhz"] >= 0.97 * clocks["sm_max_mhz"])
+    kind = "burst" if at_max else "sustained"
+    bf16 = pk["bf16_burst"] if at_max else pk["bf16_sustained"]
+    path = os.path.join(ROOT, "profiles", "r2_int8_peak.json")
+    measured = None
+    if os.path.isfile(path):
+        m = json.load(open(path))
+        measured = m["int8_tops_burst"] if at_max else m["int8_tops_sustained"]
+    peak = min(measured, 2.0 * bf16) if measured else 2.0 * bf16
+    src = (f"min(measured kind::i8 {kind} {measured:.0f} TOP/s [profiles/r2_int8_peak.json], 2 x bf16 {kind} "
+           f"{2.0 * bf16:.0f} [{pk['source']}, MEASURED_PEAKS.json]); SM clock during the timed region "
+           f"{'at' if at_max else 'below'} max" if measured else
+           f"2 x bf16 {kind} ({pk['source']}): no INT8 measurement found")
+    return peak, src, measured
 
 
 class ClockSampler:
@@ -224,6 +262,37 @@ def kernel_breakdown(plan, images, passes: int = 3):
     return agg
 
 
+def run_verify(args, cfg, plan, B, rank, world, dev):
+    """one global batch of world * B images (same seed on every rank); rank r runs rows
+    [r * B, (r + 1) * B), the logits are all-gathered, and rank 0 checks them bit for bit against its own
+    forward of the WHOLE batch (B images at a time on its GPU)."""
+    import torch
+    import torch.distributed as dist
+    from ivit_b200.synthetic import synth_images
+    full = synth_images(world * B, cfg, seed=12345)
+    mine = plan.forward(full[rank * B:(rank + 1) * B].to(dev)).clone()
+    if world > 1:
+        gathered = torch.empty((world * B, cfg.num_classes), dtype=torch.float32, device=dev)
+        dist.all_gather_into_tensor(gathered, mine)
+    else:
+        gathered = mine
+    ok, bad = True, 0
+    if rank == 0:
+        for r in range(world):
+            ref = plan.forward(full[r * B:(r + 1) * B].to(dev))
+            neq = int((ref.view(torch.int32) != gathered[r * B:(r + 1) * B].view(torch.int32)).sum().item())
+            bad += neq
+        ok = bad == 0
+        print(json.dumps({"verify": "ok" if ok else "MISMATCH", "n_gpus": world, "global_batch": world * B,
+                          "batch_per_gpu": B, "case": args.case, "mismatching_logits": bad,
+                          "what": "all-gathered logits of the batch-sharded run == rank 0's own forward of the whole "
+                                  "batch, compared as raw float32 bits"}), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0 if ok else 1
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -240,15 +309,21 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B = args.batch
+    if args.scaling == "strong":
+        if args.batch % world:
+            raise SystemExit("--scaling strong: --batch must divide by the number of GPUs")
+        B = args.batch // world
     if args.attn_variant is not None:
         from ivit_b200 import ops as _ops
         _ops.set_attention_variant(args.attn_variant)
     if args.attn_tpr is not None:
         from ivit_b200 import ops as _ops
         _ops.set_attention_threads_per_row(args.attn_tpr)
-    cfg, state, _ = load_any_case(args.case)
+    cfg, state = load_case_only(args.case)
     sess = InferenceSession(cfg, state, B, dev, chunks=1)
     plan = sess.plan
+    if args.verify:
+        return run_verify(args, cfg, plan, B, rank, world, dev)
     host = synth_images(B, cfg, seed=rank).pin_memory()      # every rank owns a different shard
     g = sess.slots[0]
     g.static_in.copy_(host)
@@ -289,7 +364,7 @@ def run_ours(args):
     e2e = None
     if not args.no_e2e:
         best = None
-        for chunks in (1, 2):          # 1: the next call's copy overlaps this call's forward (two slots)
+        for chunks in (1,):            # one session configuration for every N: the next call's copy overlaps this call's forward (two slots)
             if B % chunks:
                 continue
             s2 = sess if chunks == 1 else InferenceSession(cfg, state, B, dev, chunks=chunks)
@@ -320,13 +395,17 @@ def run_ours(args):
     total_ms = sum(a["ms"] for a in agg.values())
     dom = max(agg, key=lambda k: agg[k]["ms"])
     d = agg[dom]
-    int8_peak = 2.0 * pk["bf16_sustained"]
+    clk_all = None
+    if world > 1:
+        obj = [clk]
+        dist.broadcast_object_list(obj, src=0)
+        clk_all = obj[0]
+    i8_peak, i8_src, i8_measured = int8_peak(pk, clk if rank == 0 else clk_all)
     if d["ops"] > 0:
         ach = d["ops"] / (d["ms"] * 1e-3) / 1e12
-        roof = {"kernel": dom, "bound": "tensor", "achieved": ach, "peak": int8_peak, "unit": "TOP/s",
-                "frac": ach / int8_peak, "traffic": None,
-                "peak_source": f"2 x bf16_tflops_sustained ({pk['source']}, MEASURED_PEAKS.json): the driver measured "
-                               f"no INT8 peak; kind::i8 issues at twice the bf16 rate"}
+        roof = {"kernel": dom, "bound": "tensor", "achieved": ach, "peak": i8_peak, "unit": "TOP/s",
+                "frac": ach / i8_peak, "traffic": None, "peak_source": i8_src,
+                "frac_of_measured_int8": ach / i8_measured if i8_measured else None}
     else:
         ach = d["bytes"] / (d["ms"] * 1e-3) / 1e9
         roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
@@ -346,6 +425,18 @@ def run_ours(args):
     kernels = {k: {"launches": a["launches"], "ms": round(a["ms"], 4), "share": round(a["ms"] / total_ms, 4),
                    "TOP/s": round(a["ops"] / (a["ms"] * 1e-3) / 1e12, 2) if a["ops"] else None,
                    "GB/s": round(a["bytes"] / (a["ms"] * 1e-3) / 1e9, 1)} for k, a in agg.items()}
+    gk = [k for k in agg if k.startswith("gemm_")]
+    g_ops, g_ms, g_n = sum(agg[k]["ops"] for k in gk), sum(agg[k]["ms"] for k in gk), sum(agg[k]["launches"] for k in gk)
+    gemm_class = None
+    if g_ms > 0:
+        gemm_class = {"kernels": gk, "launches_per_step": g_n, "ms_per_step": g_ms, "share_of_step": g_ms / total_ms,
+                      "achieved": g_ops / (g_ms * 1e-3) / 1e12, "peak": i8_peak, "unit": "TOP/s",
+                      "frac": g_ops / (g_ms * 1e-3) / 1e12 / i8_peak}
+    for k, a in agg.items():
+        if a["ops"]:
+            kernels[k]["frac_int8_peak"] = round(a["ops"] / (a["ms"] * 1e-3) / 1e12 / i8_peak, 4)
+        else:
+            kernels[k]["frac_hbm_peak"] = round(a["bytes"] / (a["ms"] * 1e-3) / 1e9 / pk["hbm_gbs"], 4)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -355,7 +446,7 @@ def run_ours(args):
     line = {
         "metric": metric_name(args.case), "value": value, "unit": "images/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "int8", "data": "synthetic",
         "config": {"workload": f"{describe(args.case, cfg)}, batch {B} per GPU", "batch_per_gpu": B,
                    "global_batch": world * B,
                    "parallelism": f"batch-sharded x{world}, logits all-gather only",
@@ -364,7 +455,8 @@ def run_ours(args):
                          "126 MB L2)" if args.case == "deit_small_ivit" and B == 256 else ""),
                    "launch": "CUDA graph replay"},
         "images_per_s_per_gpu": value / world,
-        "tensor_frac_whole_step": value / world * gop * 1e9 / (int8_peak * 1e12),
+        "tensor_frac_whole_step": value / world * gop * 1e9 / (i8_peak * 1e12),
+        "roofline_gemm_class": gemm_class,
         "gpu_launches": int(g.launches * args.steps + (0 if args.no_e2e else sess.launches_per_infer * args.steps)),
         "clocks": clk, "e2e": e2e, "roofline": roof, "kernels": kernels,
     }

@@ -892,8 +892,16 @@ static int fill_args(GemmArgs& a, int M, int N, int K, void* out, int64_t ldo, c
 
 using namespace ivit;
 
+constexpr int kMaxDevices = 64;
+static int current_device_slot() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) dev = 0;
+  return dev;
+}
+
 static int sm_count() {
-  static int n = 0;
+  static int n_dev[kMaxDevices] = {};
+  int& n = n_dev[current_device_slot()];
   if (n == 0) {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess ||
@@ -912,7 +920,8 @@ static int launch_ws(const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& ar
   rc = make_tmap_2d_u8(&tmW, W, args.K, args.N, args.K, BK, BN, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
   args.stages = Cfg::STAGES;
-  static bool attr_set = false;
+  static bool attr_set_dev[kMaxDevices] = {};      // the attribute is per-device state
+  bool& attr_set = attr_set_dev[current_device_slot()];
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(gemm_i8_ws_kernel<BN, MODE, CHECKED>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(Cfg::SMEM));
@@ -934,7 +943,8 @@ static int launch_cl(const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& ar
   rc = make_tmap_2d_u8(&tmW, W, args.K, args.N, args.K, BK, Cfg::CB, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
   args.stages = Cfg::STAGES;
-  static bool attr_set = false;
+  static bool attr_set_dev[kMaxDevices] = {};      // the attribute is per-device state
+  bool& attr_set = attr_set_dev[current_device_slot()];
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(gemm_i8_cl_kernel<TB, MODE, CHECKED>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(Cfg::SMEM));

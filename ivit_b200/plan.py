@@ -102,6 +102,14 @@ def _layer_kind(name: str) -> int:
     raise NotImplementedError(f"layer type {name!r}: this plan covers the ivit|ibert registry entries")
 
 
+def _device_guard(device):
+    """Make the plan's device current for the duration of a build / launch sequence: the C ABI enqueues on the
+    CURRENT device's stream and caches per-device launch attributes (a plan may be built for cuda:1 while cuda:0 is
+    current).  No-op for the host-only plan."""
+    import contextlib
+    return torch.cuda.device(device) if torch.device(device).type == "cuda" else contextlib.nullcontext()
+
+
 class GraphCaptureMixin:
     """Launch accounting and CUDA-graph capture shared by the frozen plans (`_enqueue(images)` enqueues one
     forward on torch's current stream)."""
@@ -122,6 +130,10 @@ class GraphCaptureMixin:
         (replay them on one stream)."""
         if (B, slot) in self._graphs:
             return self._graphs[(B, slot)]
+        with _device_guard(self.device):
+            return self._capture(B, slot)
+
+    def _capture(self, B: int, slot: int) -> "GraphedForward":
         cfg = self.cfg
         static_in = torch.zeros((B, cfg.in_chans, cfg.img_size, cfg.img_size), dtype=torch.float32,
                                 device=self.device)
@@ -183,7 +195,8 @@ class FrozenVitPlan(GraphCaptureMixin):
         self._graphs = {}
         self.launches_per_forward = 0
         self.trace = None
-        self._build()
+        with _device_guard(self.device):        # constants, tables and launches on the plan's device, whatever is current
+            self._build()
 
     # ------------------------------------------------------------------ host constants
     def _act_scale(self, name: str, bits: int = 8) -> np.ndarray:
@@ -433,7 +446,8 @@ class FrozenVitPlan(GraphCaptureMixin):
 
     def forward(self, images: torch.Tensor, taps: dict | None = None, blocks: int | None = None) -> torch.Tensor:
         """Eager launch sequence.  Returns float32 logits [B, classes] (a view of the plan's buffer)."""
-        return self._enqueue(images, taps, blocks)
+        with _device_guard(self.device):
+            return self._enqueue(images, taps, blocks)
 
     __call__ = forward
 

@@ -31,7 +31,7 @@ import torch
 
 from . import _cabi, hostmath as hm, ops
 from ._cabi import EPI_LOGITS, EPI_REQUANT, EPI_RESIDUAL, AttentionParams, WindowAttentionParams
-from .plan import GraphCaptureMixin, _Linear, _Norm, _np
+from .plan import _device_guard, GraphCaptureMixin, _Linear, _Norm, _np
 from .synthetic import SwinConfig
 
 f32 = np.float32
@@ -71,7 +71,8 @@ class FrozenSwinPlan(GraphCaptureMixin):
         self._bufs, self._keep, self._graphs = {}, [], {}
         self.launches_per_forward = 0
         self.trace = None
-        self._build()
+        with _device_guard(self.device):        # constants, tables and launches on the plan's device, whatever is current
+            self._build()
 
     # ------------------------------------------------------------------ host constants
     def _act_scale(self, name: str, bits: int = 8) -> np.ndarray:
@@ -271,7 +272,8 @@ class FrozenSwinPlan(GraphCaptureMixin):
 
     def forward(self, images: torch.Tensor, taps: dict | None = None) -> torch.Tensor:
         """Eager launch sequence.  Returns float32 logits [B, classes] (a view of the plan's buffer)."""
-        return self._enqueue(images, taps)
+        with _device_guard(self.device):
+            return self._enqueue(images, taps)
 
     __call__ = forward
 
