@@ -160,12 +160,22 @@ typedef struct {
    * RESIDUAL identity is int16 (ld_id in int16 elements).  0 or 8 = int8.  RESIDUAL's first clamp
    * (qmin, qmax) may then be a 16-bit range too (attention_out_bw / mlp_out_bw / patch_embed_bw). */
   int out_bits, id_bits;
+  /* REQUANT only, optional: the GELU that follows the QuantAct (layers_quant.py:145-154: mlp.fc1 -> qact_gelu ->
+   * act -> qact1), fused into the launch.  gelu_lut = the layer's [256][256] table of ivit_gelu_lut_build
+   * (ShiftGELU ivit_modules.py:89-126 or I-BERT GELU ibert_modules.py:203-235, + mlp.qact1); the QuantAct codes
+   * still go to `out`, GELU(codes) to gelu_out (int8 [M, N], row stride ldo; may be `out` itself).  One kernel
+   * when the activation-stationary GEMM applies (K <= 768, int8 codes, z_bound_ok), else the GEMM followed by
+   * the table pass.  NULL: no GELU. */
+  const int8_t* gelu_lut;
+  int8_t* gelu_out;
 } ivit_gemm_epilogue_t;
 int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M, int N, int K, void* out, int64_t ldo,
                  const ivit_gemm_epilogue_t* epi, void* stream);
-/* ivit_gemm_i8 has two tcgen05 kernels: tokens on TMEM lanes (every epilogue) and channels on
- * TMEM lanes (REQUANT / RESIDUAL hot shapes).  layout 0 = choose per call (default), 1 = always
- * the first.  Returns the previous setting.  Process-wide; for A/B timing and tests. */
+/* ivit_gemm_i8 has three tcgen05 kernels: tokens on TMEM lanes (every epilogue), channels on TMEM lanes
+ * (REQUANT / RESIDUAL hot shapes), and the activation-stationary form of the latter (REQUANT, K <= 768: a CTA
+ * keeps a token tile in shared memory for all channel blocks; carries the fused GELU).  layout 0 = choose per
+ * call (default), 1 = always the first, 2 = never the third.  Returns the previous setting.  Process-wide; for
+ * A/B timing and tests. */
 int ivit_gemm_set_layout(int layout);
 /* Straightforward CUDA-core int8 GEMM with the same epilogues: on-device cross-check for
  * the tcgen05 kernel at sizes the CPU oracle cannot reach.  Not used by the product path. */

@@ -33,6 +33,7 @@ class GemmEpilogue(C.Structure):
         ("force_slow", C.c_int),
         ("z_bound_ok", C.c_int),
         ("out_bits", C.c_int), ("id_bits", C.c_int),
+        ("gelu_lut", C.c_void_p), ("gelu_out", C.c_void_p),
     ]
 
 

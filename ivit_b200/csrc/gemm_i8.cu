@@ -788,6 +788,305 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
 }
 
+// ------------------------------------------------------------------ activation-stationary kernel
+// QuantLinear -> QuantAct (REQUANT) for K <= 768, optionally with the GELU that follows it (mlp.fc1 ->
+// qact_gelu -> ShiftGELU | I-BERT GELU -> mlp.qact1: layers_quant.py:145-154) fused into the same launch.
+//
+// The channels-on-lanes kernel above walks (channel block, token tile) pairs, so every 128 x 256 output tile
+// pulls its own (128 + 256) x K operand bytes through L2 -> shared memory: at K = 384 that feed, not the tensor
+// pipe, bounds it.  Here a CTA owns a TOKEN tile (TB tokens) for ALL channel blocks: the activation tile is
+// loaded once and stays in shared memory (KB slabs of TB x 128 B), only the 128-channel weight slabs stream
+// through the ring -- (TB + ncb * 128) x K bytes per token tile instead of ncb * (128 + TB) x K.  TB = 176
+// gives 287 token tiles for 256 DeiT images = 1.94 rounds of 148 CTAs.
+//
+// Because all channels of a token pass through one CTA, the ShiftGELU row maximum (ivit_modules.py:110, over
+// the whole hidden dimension) is available inside the launch: when the last channel block of a token tile has
+// been stored, the epilogue warps re-read the tile's rows (L2 hits), take the row maximum, apply the layer's
+// (row max, code) table -- GELU + mlp.qact1, built at freeze time -- and write the fc2 operand.  The separate
+// GELU launch and its HBM round trip are gone; gelu_out may alias out (in place).
+template <int TB_, int KB_>
+struct AsCfg {
+  static constexpr int CB = 128;
+  static constexpr int TB = TB_;
+  static constexpr int KB = KB_;                                 // K slabs of 128 bytes held for the token tile
+  static constexpr int A_SLAB = TB * BK;
+  static constexpr int W_BYTES = CB * BK;
+  static constexpr int STAGES = KB <= 3 ? 8 : 4;
+  static constexpr int ACC_STRIDE = 256;
+  static constexpr uint32_t TMEM_COLS = 512;
+  static constexpr int PART = 64;
+  static constexpr int NPARTS = (TB + PART - 1) / PART;
+  static constexpr int EPI_WARPS = 4 * NPARTS;
+  static constexpr int THREADS = 64 + 32 * EPI_WARPS;
+  static constexpr int NBAR = 2 * KB + 2 * STAGES + 4 + 1;
+  static constexpr size_t SMEM = KB * A_SLAB + STAGES * W_BYTES + 8 * NBAR + 64 + EPI_WARPS * 512;
+  static_assert(TB % 16 == 0 && TB <= 256 && A_SLAB % 1024 == 0, "token tile: UMMA N, whole swizzle atoms");
+};
+
+template <int TB, int KB, bool GELU>
+__global__ void __launch_bounds__(AsCfg<TB, KB>::THREADS, 1)
+gemm_i8_as_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                  const GemmArgs args) {
+  using Cfg = AsCfg<TB, KB>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* sA = smem;                                            // KB slabs [TB x 128 B], SWIZZLE_128B
+  uint8_t* sW = smem + KB * Cfg::A_SLAB;                         // STAGES x [128 x 128 B]
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(sW + STAGES * Cfg::W_BYTES);
+  uint64_t* a_empty = a_full + KB;
+  uint64_t* w_full = a_empty + KB;
+  uint64_t* w_empty = w_full + STAGES;
+  uint64_t* tfull_bar = w_empty + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint64_t* tile_done = tempty_bar + 2;                          // GELU: every channel block of a token tile is stored
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tile_done + 1);
+  uint8_t* srow = reinterpret_cast<uint8_t*>(tmem_slot) + 64;    // GELU: [EPI_WARPS][2][256] table lines
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+  const int ncb = (args.N + Cfg::CB - 1) / Cfg::CB;
+  const int ntt = (args.M + TB - 1) / TB;
+  const int kblocks = (args.K + BK - 1) / BK;                    // <= KB (host-checked)
+  const ivit_gemm_epilogue_t& e = args.e;
+
+  if (threadIdx.x == 0) {
+    for (int k = 0; k < KB; ++k) {
+      mbar_init(&a_full[k], 1);
+      mbar_init(&a_empty[k], 1);
+    }
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&w_full[s], 1);
+      mbar_init(&w_empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], Cfg::EPI_WARPS);
+    }
+    mbar_init(tile_done, Cfg::EPI_WARPS);
+    fence_mbar_init();
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+  pdl_launch_dependents();
+
+  if (warp == 0) {
+    // ===================================================== TMA producer
+    if (elect_one()) {
+      int it = 0, ti = 0;
+      for (int tt = blockIdx.x; tt < ntt; tt += gridDim.x, ++ti) {
+        // the token tile: slab kb is free once the LAST channel block of the previous tile has consumed it
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&a_empty[kb], (ti & 1) ^ 1);
+          mbar_arrive_expect_tx(&a_full[kb], Cfg::A_SLAB);
+          tma_load_2d(sA + kb * Cfg::A_SLAB, &tmA, &a_full[kb], kb * BK, tt * TB);
+        }
+        for (int cb = 0; cb < ncb; ++cb) {
+          for (int kb = 0; kb < kblocks; ++kb, ++it) {
+            const int s = it % STAGES;
+            mbar_wait(&w_empty[s], ((it / STAGES) & 1) ^ 1);
+            mbar_arrive_expect_tx(&w_full[s], Cfg::W_BYTES);
+            tma_load_2d(sW + s * Cfg::W_BYTES, &tmW, &w_full[s], kb * BK, cb * Cfg::CB);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_i8(Cfg::CB, TB, true, true, false, false);
+      int it = 0, ci = 0, ti = 0;
+      for (int tt = blockIdx.x; tt < ntt; tt += gridDim.x, ++ti) {
+        for (int cb = 0; cb < ncb; ++cb, ++ci) {
+          const int a = ci & 1;
+          mbar_wait(&tempty_bar[a], ((ci >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + a * Cfg::ACC_STRIDE;
+          for (int kb = 0; kb < kblocks; ++kb, ++it) {
+            const int s = it % STAGES;
+            if (cb == 0) mbar_wait(&a_full[kb], ti & 1);
+            mbar_wait(&w_full[s], (it / STAGES) & 1);
+            tc_fence_after();
+            const uint32_t sw = smem_u32(sW + s * Cfg::W_BYTES);
+            const uint32_t sa = smem_u32(sA + kb * Cfg::A_SLAB);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              const uint64_t dw = make_smem_desc(sw + k * UMMA_K, 16, 1024, kLayoutSW128);
+              const uint64_t da = make_smem_desc(sa + k * UMMA_K, 16, 1024, kLayoutSW128);
+              mma_i8_ss(d_tmem, dw, da, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            tc_commit(&w_empty[s]);
+            if (cb == ncb - 1) tc_commit(&a_empty[kb]);
+          }
+          tc_commit(&tfull_bar[a]);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp < 2 + Cfg::EPI_WARPS) {
+    // ===================================================== epilogue (thread = output channel)
+    const int ew = warp - 2;
+    const int quarter = warp & 3;
+    const int part = ew >> 2;
+    const int nch = min(4, (TB - part * Cfg::PART) / 16);          // 16-token chunks of this warp's part
+    const uint32_t sel1 = (lane & 1) ? 0x3715u : 0x6240u;
+    const uint32_t sel2 = (lane & 2) ? 0x3276u : 0x5410u;
+    const int qi = lane & 3;                 // after the transpose: this lane's token within a group of 4
+    const int qc = (lane >> 2) * 4;          //                      and its first channel within the warp's 32
+    int pb = 0;
+    double pm = 0.0;
+    auto fetch_params = [&](int cb) {
+      const int n = cb * Cfg::CB + quarter * 32 + lane;
+      pb = (e.bias != nullptr && n < args.N) ? __ldg(e.bias + n) : 0;
+      pm = n < args.N ? __ldg(e.mult + n) : 0.0;
+    };
+    fetch_params(0);
+    int8_t* const outp = static_cast<int8_t*>(args.out);
+    const uint32_t ldo = static_cast<uint32_t>(args.ldo);
+    int ci = 0;
+    for (int tt = blockIdx.x; tt < ntt; tt += gridDim.x) {
+      const int tok_w = tt * TB + part * Cfg::PART;              // the warp's first token
+      for (int cb = 0; cb < ncb; ++cb, ++ci) {
+        const int a = ci & 1;
+        const int c0 = cb * Cfg::CB + quarter * 32;              // the warp's first channel
+        const double mult = pm;
+        const double kb = kMagicInt - static_cast<double>(pb);
+        fetch_params(cb + 1 < ncb ? cb + 1 : 0);
+        const int nq = c0 + qc;                                  // channels nq..nq+3 after the transpose
+        const bool nq_ok = nq < args.N;                          // N % 4 == 0 (host-checked)
+        const bool all_ok = tok_w + 16 * nch <= args.M && c0 + 32 <= args.N;   // warp-uniform: no guards
+        const uint32_t off_o = static_cast<uint32_t>(tok_w + qi) * ldo + nq;
+        const uint32_t t_row = tmem_base + a * Cfg::ACC_STRIDE + part * Cfg::PART +
+                               (static_cast<uint32_t>(quarter * 32) << 16);
+        auto process = [&](auto full_tag) {
+          constexpr bool FULL = decltype(full_tag)::value;
+          auto store_chunk = [&](int ch, const uint32_t (&packed)[4]) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              const uint32_t w = quad_transpose(packed[g], sel1, sel2);
+              if (FULL || (nq_ok && tok_w + ch * 16 + 4 * g + qi < args.M))
+                *reinterpret_cast<uint32_t*>(outp + (off_o + (ch * 16 + 4 * g) * ldo)) = w;
+            }
+          };
+          mbar_wait(&tfull_bar[a], (ci >> 1) & 1);
+          tc_fence_after();
+          uint32_t acc[2][16];
+          uint32_t packed[4];
+          tmem_ld16(t_row, acc[0]);
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch) {
+            if (ch < nch) {
+              tmem_ld_wait();
+              if (ch + 1 < nch) {
+                tmem_ld16(t_row + (ch + 1) * 16, acc[(ch + 1) & 1]);
+              } else {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty_bar[a]);
+              }
+              const uint32_t(&z)[16] = acc[ch & 1];      // rows past M are TMA zero fill: harmless, stores are guarded
+              int c[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const double zd = __hiloint2double(0x43300000, static_cast<int>(z[j] ^ 0x80000000u)) - kb;
+                c[j] = __double2loint(__fma_rn(zd, mult, kMagicRnd));
+              }
+              if (ch > 0) store_chunk(ch - 1, packed);
+#pragma unroll
+              for (int g = 0; g < 4; ++g) packed[g] = pack4_sat_s8(c[4 * g], c[4 * g + 1], c[4 * g + 2], c[4 * g + 3]);
+            }
+          }
+          store_chunk(nch - 1, packed);
+        };
+        if (all_ok) process(std::true_type{});
+        else process(std::false_type{});
+      }
+      if (GELU) {
+        // every channel block of this token tile is stored (by all epilogue warps): GELU + mlp.qact1 over the tile's
+        // rows (L2 hits) -- row maximum (ivit_modules.py:110), then byte lookups in the row's 256-byte line of the
+        // layer's (row max, code) table.  Two rows per warp-step, loads first.  (Measured: a dedicated group of four
+        // tail warps is slower, 1.56 vs 1.13 ms per DeiT-S step: the pass needs many warps to hide its latencies.)
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * Cfg::EPI_WARPS) : "memory");
+        const int nv = args.N / 16;
+        uint8_t* trow0 = srow + ew * 512;
+        const int rows_here = min(TB, args.M - tt * TB);
+        for (int r0 = 2 * ew; r0 < rows_here; r0 += 2 * Cfg::EPI_WARPS) {
+        const bool two = r0 + 1 < rows_here;
+        int4 v[2][6];
+        uint32_t m[2] = {0x80808080u, 0x80808080u};
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const long long ro = static_cast<long long>(tt * TB + r0 + (two ? u : 0)) * args.ldo;
+          const int4* xr = reinterpret_cast<const int4*>(outp + ro);
+#pragma unroll
+          for (int i = 0; i < 6; ++i) {
+            const int idx = i * 32 + lane;
+            if (idx < nv) v[u][i] = __ldcg(xr + idx);      // written by the epilogue warps a moment ago: L2, not L1
+          }
+        }
+        int mx[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+#pragma unroll
+          for (int i = 0; i < 6; ++i) {
+            if (i * 32 + lane < nv) {
+              m[u] = __vmaxs4(m[u], v[u][i].x); m[u] = __vmaxs4(m[u], v[u][i].y);
+              m[u] = __vmaxs4(m[u], v[u][i].z); m[u] = __vmaxs4(m[u], v[u][i].w);
+            }
+          }
+          mx[u] = max(max(static_cast<int8_t>(m[u]), static_cast<int8_t>(m[u] >> 8)),
+                      max(static_cast<int8_t>(m[u] >> 16), static_cast<int8_t>(m[u] >> 24)));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          mx[0] = max(mx[0], __shfl_xor_sync(0xffffffffu, mx[0], o));
+          mx[1] = max(mx[1], __shfl_xor_sync(0xffffffffu, mx[1], o));
+        }
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+          *reinterpret_cast<uint2*>(trow0 + u * 256 + 8 * lane) =
+              __ldg(reinterpret_cast<const uint2*>(e.gelu_lut + (mx[u] + 128) * 256) + lane);
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (u == 1 && !two) break;
+          const uint8_t* trow = trow0 + u * 256;
+          auto look4 = [&](uint32_t w) -> uint32_t {
+            w ^= 0x80808080u;
+            const uint32_t b0 = trow[w & 0xffu], b1 = trow[(w >> 8) & 0xffu], b2 = trow[(w >> 16) & 0xffu], b3 = trow[w >> 24];
+            return __byte_perm(__byte_perm(b0, b1, 0x0040), __byte_perm(b2, b3, 0x0040), 0x5410);
+          };
+          int4* orow = reinterpret_cast<int4*>(e.gelu_out + static_cast<long long>(tt * TB + r0 + u) * args.ldo);
+#pragma unroll
+          for (int i = 0; i < 6; ++i) {
+            const int idx = i * 32 + lane;
+            if (idx < nv) {
+              int4 o;
+              o.x = look4(v[u][i].x); o.y = look4(v[u][i].y); o.z = look4(v[u][i].z); o.w = look4(v[u][i].w);
+              orow[idx] = o;
+            }
+          }
+        }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
 // ------------------------------------------------------------------ simple cross-check kernel
 __global__ void gemm_i8_simple_kernel(const int8_t* __restrict__ A, long long lda, const int8_t* __restrict__ W,
                                       const GemmArgs args) {
@@ -959,6 +1258,31 @@ static int launch_cl(const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& ar
   return check_launch("gemm_i8_cl_kernel");
 }
 
+template <int TB, int KB, bool GELU>
+static int launch_as(const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& args, cudaStream_t st) {
+  using Cfg = AsCfg<TB, KB>;
+  CUtensorMap tmA, tmW;
+  int rc = make_tmap_2d_u8(&tmA, A, args.K, args.M, lda, BK, TB, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  rc = make_tmap_2d_u8(&tmW, W, args.K, args.N, args.K, BK, Cfg::CB, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  args.stages = Cfg::STAGES;
+  static bool attr_set_dev[kMaxDevices] = {};
+  bool& attr_set = attr_set_dev[current_device_slot()];
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_i8_as_kernel<TB, KB, GELU>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(Cfg::SMEM));
+    if (e != cudaSuccess) return fail(static_cast<int>(e), cudaGetErrorString(e));
+    attr_set = true;
+  }
+  const int ntt = (args.M + TB - 1) / TB;
+  const int grid = ntt < sm_count() ? ntt : sm_count();
+  cudaError_t le = launch_kernel(gemm_i8_as_kernel<TB, KB, GELU>, dim3(grid),
+                                 dim3(Cfg::THREADS), Cfg::SMEM, st, tmA, tmW, args);
+  if (le != cudaSuccess) return fail(static_cast<int>(le), cudaGetErrorString(le));
+  return check_launch("gemm_i8_as_kernel");
+}
+
 // 0: pick per call (default); 1: keep every GEMM on the row-major-epilogue kernel (A/B timing, tests)
 static int g_gemm_layout = 0;
 extern "C" int ivit_gemm_set_layout(int layout) {
@@ -966,7 +1290,8 @@ extern "C" int ivit_gemm_set_layout(int layout) {
   g_gemm_layout = layout;
   return prev;
 }
-static bool channels_on_lanes_enabled() { return g_gemm_layout == 0; }
+static bool channels_on_lanes_enabled() { return g_gemm_layout != 1; }
+static bool activation_stationary_enabled() { return g_gemm_layout == 0 || g_gemm_layout == 3; }   // 3: also without GELU
 
 template <int BN>
 static int launch_mode(int mode, bool checked, const int8_t* A, int64_t lda, const int8_t* W, GemmArgs& args,
@@ -1013,6 +1338,28 @@ extern "C" int ivit_gemm_i8(const int8_t* A, int64_t lda, const int8_t* W, int M
       fabs(epi->mult_id) < 65536.0 && static_cast<int64_t>(M) * ldo + N < (1ll << 31) &&
       static_cast<int64_t>(M) * epi->ld_id + N < (1ll << 31) && channels_on_lanes_enabled())
     return checked ? launch_cl<192, 4, true>(A, lda, W, args, st) : launch_cl<192, 4, false>(A, lda, W, args, st);
+  // REQUANT with K <= 768 and a proven accumulator bound: the activation-stationary kernel (and the fused GELU)
+  const bool gelu = req && epi->gelu_lut != nullptr;
+  if (gelu && (epi->gelu_out == nullptr || N % 16 != 0))
+    return fail(IVIT_ERR_BAD_ARG, "gemm: fused GELU needs gelu_out and N % 16 == 0");
+  {
+    const int64_t span = static_cast<int64_t>(M) * ldo + N;
+    if (mode == 1 && !checked && epi->group <= 0 && N % 4 == 0 && ldo % 16 == 0 && span < (1ll << 31) && K <= 768 &&
+        (gelu || g_gemm_layout == 3) && activation_stationary_enabled() && (!gelu || (N <= 3072 && (reinterpret_cast<uintptr_t>(epi->gelu_out) & 15) == 0))) {
+      if (K <= 384) return gelu ? launch_as<176, 3, true>(A, lda, W, args, st) : launch_as<176, 3, false>(A, lda, W, args, st);
+      return gelu ? launch_as<176, 6, true>(A, lda, W, args, st) : launch_as<176, 6, false>(A, lda, W, args, st);
+    }
+  }
+  if (gelu) {
+    // not eligible: the plain GEMM, then the table pass (same results, two launches)
+    ivit_gemm_epilogue_t plain = *epi;
+    plain.gelu_lut = nullptr;
+    plain.gelu_out = nullptr;
+    rc = ivit_gemm_i8(A, lda, W, M, N, K, out, ldo, &plain, stream);
+    if (rc) return rc;
+    if (ldo != N) return fail(IVIT_ERR_UNSUPPORTED, "gemm: the two-launch GELU fallback needs contiguous rows");
+    return ivit_gelu_lut_apply_i8(static_cast<const int8_t*>(out), epi->gelu_out, epi->gelu_lut, M, N, stream);
+  }
   // Hot shapes: channels-on-lanes kernel (per-channel constants in registers).  Needs 4-byte
   // aligned output / identity rows and no row remap.
   const int64_t span_o = static_cast<int64_t>(M) * ldo + N, span_i = static_cast<int64_t>(M) * epi->ld_id + N;

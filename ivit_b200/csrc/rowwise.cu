@@ -559,10 +559,15 @@ __global__ void gelu_ivit_raw_kernel(float* __restrict__ out, GeluIvitParams gi)
 }
 
 // One warp per row: row max (needed by ShiftGELU, ivit_modules.py:110), then table lookup.
+// The row's 256-byte table line is staged per warp in shared memory, 256-byte aligned and rotated by 128, so
+// that the shared address of a code's entry is (line base | code byte): ONE PRMT builds it from the packed
+// word, one LDS.U8 fetches it, three PRMTs re-pack four results -- 2.75 instructions per byte (the pass runs
+// in place on L2-resident rows, so instructions, not HBM, bound it).
 template <int NV>                   // 16-byte vectors per lane: C <= NV * 512
 __global__ void __launch_bounds__(256)
 gelu_lut_apply_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, const int8_t* __restrict__ lut,
                       int rows, int C) {
+  __shared__ __align__(256) uint8_t srow[8][256];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   pdl_wait();                   // programmatic dependent launch: x is the predecessor's output
@@ -584,20 +589,18 @@ gelu_lut_apply_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, co
                max(static_cast<int8_t>(m >> 16), static_cast<int8_t>(m >> 24)));
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  // the row's 256-byte table line, staged per warp: byte gathers from shared memory (<= 2 lanes per
-  // bank on average) instead of 8-sector global gathers
-  __shared__ __align__(8) uint8_t srow[8][256];
-  *reinterpret_cast<uint2*>(&srow[warp][8 * lane]) =
+  // entry of code c at byte (c & 0xff): the line rotated by 128
+  *reinterpret_cast<uint2*>(&srow[warp][(8 * lane + 128) & 255]) =
       __ldg(reinterpret_cast<const uint2*>(lut + (mx + 128) * 256) + lane);
   __syncwarp();
-  const uint8_t* trow = srow[warp];            // indexed by the code as an unsigned byte ^ 0x80 (= code + 128)
+  const uint32_t tb = smem_u32(&srow[warp][0]);      // low byte zero
   auto look4 = [&](uint32_t w) -> uint32_t {
-    w ^= 0x80808080u;
-    const uint32_t b0 = trow[w & 0xffu];
-    const uint32_t b1 = trow[(w >> 8) & 0xffu];
-    const uint32_t b2 = trow[(w >> 16) & 0xffu];
-    const uint32_t b3 = trow[w >> 24];
-    return b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+    uint32_t r0, r1, r2, r3;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r0) : "r"(__byte_perm(w, tb, 0x7650)));
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r1) : "r"(__byte_perm(w, tb, 0x7651)));
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r2) : "r"(__byte_perm(w, tb, 0x7652)));
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r3) : "r"(__byte_perm(w, tb, 0x7653)));
+    return __byte_perm(__byte_perm(r0, r1, 0x0040), __byte_perm(r2, r3, 0x0040), 0x5410);
   };
 #pragma unroll
   for (int i = 0; i < NV; ++i) {

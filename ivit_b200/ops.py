@@ -145,7 +145,7 @@ def fill_cls_rows(out: torch.Tensor, cls_row: torch.Tensor):
 def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=None, s_in=None, qmin=-128, qmax=127,
          mult2=0.0, mult_id=0.0, qmin2=-128, qmax2=127, identity=None, scale_out=None, out=None, out_rows=None,
          group=0, out_group_stride=0, out_row_off=0, id_broadcast=False, force_slow=False,
-         z_bound_ok=False, simple=False, out_bits=8) -> torch.Tensor:
+         z_bound_ok=False, simple=False, out_bits=8, gelu_lut=None, gelu_out=None) -> torch.Tensor:
     """C = A[M,K] @ W[N,K]^T with a fused epilogue (see include/ivit_b200.h).  REQUANT / RESIDUAL store
     int16 codes when `out` is int16 (or out_bits = 16); an int16 `identity` is the 16-bit residual stream."""
     assert A.dtype == torch.int8 and W.dtype == torch.int8 and A.dim() == 2 and W.dim() == 2
@@ -173,6 +173,10 @@ def gemm(A: torch.Tensor, W: torch.Tensor, epilogue: int, *, bias=None, mult=Non
     e.id_bits = 16 if (identity is not None and identity.dtype == torch.int16) else 8
     if identity is not None:
         assert identity.dtype in (torch.int8, torch.int16) and identity.stride(-1) == 1
+    if gelu_lut is not None:           # REQUANT + the GELU table of the following mlp.act / mlp.qact1, one launch
+        assert epilogue == _cabi.EPI_REQUANT and not simple and gelu_out is not None and gelu_out.dtype == torch.int8
+        assert gelu_out.shape == out.shape and gelu_out.stride() == out.stride() and gelu_lut.numel() == 65536
+        e.gelu_lut, e.gelu_out = ptr(gelu_lut), ptr(gelu_out)
     lib = _cabi.load()
     fn = lib.ivit_gemm_i8_simple if simple else lib.ivit_gemm_i8
     ldo = out.stride(-2) if out.dim() >= 2 else N

@@ -26,6 +26,8 @@ and the in-tree library is present.
 """
 from __future__ import annotations
 
+import os
+
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -195,6 +197,7 @@ class FrozenVitPlan(GraphCaptureMixin):
         self._graphs = {}
         self.launches_per_forward = 0
         self.trace = None
+        self.fuse_gelu = os.environ.get("IVIT_FUSE_GELU", "0") == "1"      # fc1 + GELU table in one launch (ivit_gemm_epilogue_t.gelu_lut); False: separate pass
         with _device_guard(self.device):        # constants, tables and launches on the plan's device, whatever is current
             self._build()
 
@@ -430,12 +433,23 @@ class FrozenVitPlan(GraphCaptureMixin):
             tap(p + "qact2", x_mid, (B, N, C))
             self._ln(x_mid, b.s_mid, b.norm2, bufs["ln"])
             tap(p + "qact3", bufs["ln"], (B, N, C))
-            self._gemm(bufs["ln"], b.fc1, EPI_REQUANT, bufs["h1"], name="fc1")
-            tap(p + "mlp.qact_gelu", bufs["h1"], (B, N, -1))
-            ops.gelu_lut_apply(bufs["h1"], b.gelu_lut, out=bufs["h2"])
-            self._mark("gelu_lut_apply", 0, 2 * bufs["h1"].numel())
-            tap(p + "mlp.qact1", bufs["h2"], (B, N, -1))
-            self._gemm(bufs["h2"], b.fc2, EPI_RESIDUAL, x, name="fc2", identity=x_mid)
+            # the GELU table pass runs IN PLACE unless the boundary is tapped: most of fc1's 77 MB output is still in L2
+            # when the pass reads it, and fc2 finds the codes on the same lines (0.445 -> 0.365 ms per DeiT-S step).
+            # Splitting the MLP into L2-sized token ranges was measured and is slower (4.17 / 4.31 / 4.59 ms per step
+            # for 2 / 3 / 4 ranges against 4.04).
+            h2 = bufs["h2"] if taps is not None else bufs["h1"]
+            if self.fuse_gelu:
+                # mlp.fc1 -> qact_gelu -> act -> qact1 in ONE launch (layers_quant.py:145-154): the activation-
+                # stationary GEMM applies the table on each finished token tile (off by default: measured slower)
+                self._gemm(bufs["ln"], b.fc1, EPI_REQUANT, bufs["h1"], name="fc1_gelu", gelu_lut=b.gelu_lut, gelu_out=h2)
+                tap(p + "mlp.qact_gelu", bufs["h1"], (B, N, -1))
+            else:
+                self._gemm(bufs["ln"], b.fc1, EPI_REQUANT, bufs["h1"], name="fc1")
+                tap(p + "mlp.qact_gelu", bufs["h1"], (B, N, -1))
+                ops.gelu_lut_apply(bufs["h1"], b.gelu_lut, out=h2)
+                self._mark("gelu_lut_apply", 0, 2 * bufs["h1"].numel())
+            tap(p + "mlp.qact1", h2, (B, N, -1))
+            self._gemm(h2, b.fc2, EPI_RESIDUAL, x, name="fc2", identity=x_mid)
             tap(p + "qact4", x, (B, N, C))
             s_x = b.s_out
         # final norm on the class-token rows only (x[:, 0], vit_quant.py:302-304), then the head

@@ -204,13 +204,14 @@ def _gemm_case(M, N, K, seed, epilogue, group=0, bounded=False):
         kw.update(group=group, out_group_stride=group + 1, out_row_off=1, id_broadcast=True)
         out_rows = (M // group) * (group + 1)
     res = {}
-    for variant in ("simple", "rows", "auto"):       # CUDA-core cross-check, tokens-on-lanes, per-call choice
+    # CUDA-core cross-check, tokens-on-lanes, channels-on-lanes without the activation-stationary kernel, per-call choice
+    for variant in ("simple", "rows", "cl", "auto"):
         simple = variant == "simple"
         out = None
         if out_rows:
             odt = torch.int8
             out = torch.full((out_rows, N), 99, dtype=odt, device=DEV)
-        prev = ops.set_gemm_layout(1 if variant == "rows" else 0)
+        prev = ops.set_gemm_layout({"rows": 1, "cl": 2}.get(variant, 0))
         try:
             got = ops.gemm(_t(A, torch.int8), _t(W, torch.int8), epilogue, simple=simple, out=out,
                            z_bound_ok=(bounded and not simple), **kw).cpu().numpy()
@@ -248,6 +249,38 @@ def test_gemm_residual(shape):
 @pytest.mark.parametrize("shape", [(700, 384, 384), (394, 1152, 384), (40000, 1536, 384)])
 def test_gemm_requant_unchecked(shape):
     _gemm_case(*shape, seed=6, epilogue=_cabi.EPI_REQUANT, bounded=True)
+
+
+@pytest.mark.parametrize("shape", [(700, 384, 384), (394, 1152, 192), (30000, 1536, 384), (333, 3072, 768),
+                                   (40, 48, 64), (176, 128, 128), (177, 1536, 384)])
+@pytest.mark.parametrize("kind", [0, 1])
+def test_gemm_requant_fused_gelu(shape, kind):
+    """mlp.fc1 -> qact_gelu -> GELU -> mlp.qact1 in one launch (ivit_gemm_epilogue_t.gelu_lut): the activation-
+    stationary kernel's GELU tail against the two-launch form, out of place and in place; the QuantAct codes
+    themselves against the CUDA-core cross-check kernel."""
+    M, N, K = shape
+    rng = np.random.default_rng(100 + M + kind)
+    A = _t(rng.integers(-128, 128, size=(M, K)).astype(np.int8), torch.int8)
+    W = _t(rng.integers(-40, 41, size=(N, K)).astype(np.int8), torch.int8)
+    bias = _t(rng.integers(-20000, 20000, size=N).astype(np.int32), torch.int32)
+    mult = _t((rng.random(N) * 2e-4 + 2e-4), torch.float64)
+    s_in = _t((rng.random(N) * 2e-5 + 1e-5).astype(f32), torch.float32)
+    lut, _ = ops.gelu_lut_build(kind, 0.0431, 8, 0.37, -128, 127, DEV)
+    kw = dict(bias=bias, mult=mult, s_in=s_in)
+    codes = ops.gemm(A, W, _cabi.EPI_REQUANT, simple=True, **kw)
+    assert codes.unique().numel() > 16
+    want = ops.gelu_lut_apply(codes, lut)
+    h1 = torch.full((M, N), 7, dtype=torch.int8, device=DEV)
+    h2 = torch.full((M, N), 9, dtype=torch.int8, device=DEV)
+    ops.gemm(A, W, _cabi.EPI_REQUANT, z_bound_ok=True, out=h1, gelu_lut=lut, gelu_out=h2, **kw)
+    assert torch.equal(h1, codes), "QuantAct codes"
+    assert torch.equal(h2, want), "fused GELU, out of place"
+    ops.gemm(A, W, _cabi.EPI_REQUANT, z_bound_ok=True, out=h1, gelu_lut=lut, gelu_out=h1, **kw)
+    assert torch.equal(h1, want), "fused GELU, in place"
+    # not eligible for the one-launch kernel (no accumulator bound from the caller): GEMM + table pass, same result
+    h1.fill_(3)
+    ops.gemm(A, W, _cabi.EPI_REQUANT, z_bound_ok=False, out=h1, gelu_lut=lut, gelu_out=h2.fill_(5), **kw)
+    assert torch.equal(h1, codes) and torch.equal(h2, want)
 
 
 def test_gemm_residual_unchecked_many_tiles():

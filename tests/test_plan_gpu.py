@@ -191,3 +191,21 @@ def test_session_slots_rotate_across_calls(chunks, slots):
         sess.synchronize()
         for o, r in zip(outs, refs):
             assert torch.equal(o, r)
+
+
+@pytest.mark.parametrize("case", ["toy_ivit", "deit_tiny_ibert", "deit_tiny_ivit_w16"])
+def test_fused_fc1_gelu_plan_equals_two_launch_plan(case):
+    """plan.fuse_gelu: mlp.fc1 + GELU table in one launch (activation-stationary GEMM) -- every boundary and the
+    logits equal the default two-launch plan's, with and without taps (in place)."""
+    cfg, state, _ = load_case(case)
+    x = synth_images(3, cfg, seed=5).cuda()
+    ref_plan = FrozenVitPlan(cfg, state, "cuda")
+    fused = FrozenVitPlan(cfg, state, "cuda")
+    fused.fuse_gelu = True
+    t0, t1 = {}, {}
+    want = ref_plan.forward(x, taps=t0).clone()
+    got = fused.forward(x, taps=t1).clone()
+    assert torch.equal(got, want)
+    for k in t0:
+        assert torch.equal(t0[k], t1[k]), k
+    assert torch.equal(fused.forward(x), want)
