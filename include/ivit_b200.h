@@ -42,6 +42,13 @@ int ivit_quantize_f32_i8(const float* x, int8_t* out, float inv_scale, int64_t n
 int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float inv_scale, int B, int Cin, int H, int W, int P,
                                  void* stream);
 
+/* The same for uint8 images: torchvision's ToTensor (x / 255) and Normalize ((x - mean[c]) / std[c]) of the data
+ * loader (scripts/inference.py builds them into its transform) followed by qact_input.  A pixel has 256 values
+ * per channel, so the caller tabulates all three steps in float32, in that order, as lut int8 [Cin][256]
+ * (device memory); the kernel gathers codes into the im2col layout.  x uint8 [B,Cin,H,W], 4-byte aligned. */
+int ivit_quantize_patches_u8_i8(const uint8_t* x, int8_t* out, const int8_t* lut, int B, int Cin, int H, int W, int P,
+                                void* stream);
+
 /* ---- IntLayerNorm + following QuantAct --------------------------------------------------
  * kind 0: ivit_modules.py:30-65 (IVITIntLayerNorm), kind 1: ibert_modules.py:112-158
  * (IBERTIntLayerNorm; shift = its `shift` buffer, use_int_sqrt as the ctor flag), then

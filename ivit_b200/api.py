@@ -16,10 +16,14 @@ from .synthetic import SwinConfig, VitConfig
 
 
 class InferenceSession:
-    def __init__(self, cfg: "VitConfig | SwinConfig", state: dict, batch: int, device="cuda", chunks: int = 1, slots: int = 2):
+    def __init__(self, cfg: "VitConfig | SwinConfig", state: dict, batch: int, device="cuda", chunks: int = 1, slots: int = 2,
+                 uint8_input=None):
         """batch images per call, processed as `chunks` equal forwards; `slots` staging slots (each a
         captured graph with its own input buffer) rotate across chunks AND calls, so with slots >= 2
         the host->device copy of the next chunk / next call overlaps the forward in flight."""
+        """uint8_input=(mean, std): the session takes uint8 images [batch,C,H,W] (0..255) and applies ToTensor +
+        Normalize(mean, std) + the input QuantAct on the device as one code table: a quarter of the float32 input bytes
+        over the host->device link, bit-identical logits to feeding the normalised float32 tensor (ViT plans)."""
         if batch % chunks != 0:
             raise ValueError("batch must be divisible by chunks")
         if slots < 1:
@@ -29,13 +33,19 @@ class InferenceSession:
         self.batch, self.chunks, self.cb = batch, chunks, batch // chunks
         self.compute = torch.cuda.Stream(device=self.device)
         self.copy = torch.cuda.Stream(device=self.device)
+        self.in_dtype = torch.float32
+        if uint8_input is not None:
+            if not isinstance(self.plan, FrozenVitPlan):
+                raise NotImplementedError("uint8 input: ViT / DeiT plans")
+            self.plan.set_uint8_input(*uint8_input)
+            self.in_dtype = torch.uint8
         with torch.cuda.device(self.device):
-            self.slots = [self.plan.capture(self.cb, slot=s) for s in range(slots)]
+            self.slots = [self.plan.capture(self.cb, slot=s, dtype=self.in_dtype) for s in range(slots)]
             self.ready = [torch.cuda.Event() for _ in self.slots]
             self.consumed = [torch.cuda.Event() for _ in self.slots]
         # two result buffers: the logits of call k stay valid while call k+1 is in flight
         self.out_hosts = [torch.empty((batch, cfg.num_classes), dtype=torch.float32).pin_memory() for _ in range(2)]
-        self.h2d_bytes = batch * cfg.in_chans * cfg.img_size * cfg.img_size * 4
+        self.h2d_bytes = batch * cfg.in_chans * cfg.img_size * cfg.img_size * (4 if uint8_input is None else 1)
         self.d2h_bytes = batch * cfg.num_classes * 4
         self.launches_per_infer = chunks * self.slots[0].launches
         self._seq = 0          # chunks enqueued so far (slot rotation)
@@ -49,6 +59,8 @@ class InferenceSession:
             raise ValueError("infer() takes host images; use FrozenVitPlan.forward for device tensors")
         if images.shape[0] != self.batch:
             raise ValueError(f"session was built for batch {self.batch}")
+        if images.dtype != self.in_dtype:
+            raise ValueError(f"session takes {self.in_dtype} images")
         out_host = self.out_hosts[self._calls % 2]
         self._calls += 1
         ns = len(self.slots)

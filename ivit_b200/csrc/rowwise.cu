@@ -90,6 +90,34 @@ quantize_patches_small_kernel(const float* __restrict__ x, int8_t* __restrict__ 
   }
 }
 
+// uint8 images (what a data loader holds before torchvision's ToTensor + Normalize): a pixel has 256 values per
+// channel, so ToTensor (/255), Normalize ((x - mean) / std) and the input QuantAct collapse into one [Cin][256]
+// code table built by the caller in float32 (the reference's op order); the kernel is a byte gather into the
+// im2col layout.  A quarter of the float32 path's input bytes: what the host->device link carries per step.
+__global__ void __launch_bounds__(256)
+quantize_patches_u8_kernel(const uint8_t* __restrict__ x, int8_t* __restrict__ out, const int8_t* __restrict__ lut, int B,
+                           int Cin, int H, int W, int P) {
+  extern __shared__ uint8_t slut[];                 // [Cin][256]
+  for (int i = threadIdx.x; i < Cin * 256; i += blockDim.x) slut[i] = static_cast<uint8_t>(lut[i]);
+  __syncthreads();
+  const int W4 = W / 4, gw = W / P, gh = H / P, K = Cin * P * P;
+  const long long total = static_cast<long long>(B) * Cin * H * W4;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int x4 = static_cast<int>(t % W4);
+    const int y = static_cast<int>((t / W4) % H);
+    const int c = static_cast<int>((t / (static_cast<long long>(W4) * H)) % Cin);
+    const int b = static_cast<int>(t / (static_cast<long long>(W4) * H * Cin));
+    const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(x) + t);
+    const uint8_t* l = slut + c * 256;
+    const int xx = 4 * x4;
+    const long long row = (static_cast<long long>(b) * gh + y / P) * gw + xx / P;
+    const int k = c * P * P + (y % P) * P + xx % P;
+    *reinterpret_cast<uint32_t*>(out + row * K + k) =
+        l[v & 0xffu] | (l[(v >> 8) & 0xffu] << 8) | (l[(v >> 16) & 0xffu] << 16) | (static_cast<uint32_t>(l[v >> 24]) << 24);
+  }
+}
+
 // Plain elementwise quantiser (QuantAct without a predecessor scale on an arbitrary tensor).
 __global__ void quantize_kernel(const float* __restrict__ x, int8_t* __restrict__ out, float inv_s, long long n) {
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < n;
@@ -726,6 +754,19 @@ extern "C" int ivit_quantize_patches_f32_i8(const float* x, int8_t* out, float i
   else if (P == 4) quantize_patches_kernel<2><<<grid, threads, 0, st>>>(x, out, inv_scale, B, Cin, H, W, P);
   else quantize_patches_kernel<-1><<<grid, threads, 0, st>>>(x, out, inv_scale, B, Cin, H, W, P);
   return check_launch("quantize_patches_kernel");
+}
+
+extern "C" int ivit_quantize_patches_u8_i8(const uint8_t* x, int8_t* out, const int8_t* lut, int B, int Cin, int H, int W,
+                                           int P, void* stream) {
+  if (P % 4 != 0 || H % P != 0 || W % P != 0) return fail(IVIT_ERR_BAD_ARG, "patch size must divide H, W; P % 4 == 0");
+  if (Cin < 1 || Cin > 16) return fail(IVIT_ERR_UNSUPPORTED, "quantize_patches_u8: 1..16 input channels");
+  if ((reinterpret_cast<uintptr_t>(x) & 3) != 0) return fail(IVIT_ERR_BAD_ARG, "quantize_patches_u8: 4-byte aligned images");
+  const long long total = static_cast<long long>(B) * Cin * H * (W / 4);
+  if (total <= 0) return 0;
+  const long long g = (total + 255) / 256;
+  quantize_patches_u8_kernel<<<static_cast<int>(g < 148LL * 16 ? g : 148LL * 16), 256, Cin * 256,
+                               static_cast<cudaStream_t>(stream)>>>(x, out, lut, B, Cin, H, W, P);
+  return check_launch("quantize_patches_u8_kernel");
 }
 
 // 0: packed-lane kernel where C % 128 == 0 (default); 1: strided-lane kernel always (A/B, tests)

@@ -47,6 +47,32 @@ def quantize_patches(x: torch.Tensor, inv_scale: float, patch: int, out: torch.T
     return out
 
 
+def quantize_patches_u8(x: torch.Tensor, lut: torch.Tensor, patch: int, out: torch.Tensor | None = None) -> torch.Tensor:
+    """uint8 images [B,Cin,H,W] -> int8 patch matrix through the [Cin][256] code table of `input_code_lut`."""
+    x = x.contiguous()
+    assert x.dtype == torch.uint8 and lut.dtype == torch.int8
+    B, Cin, H, W = x.shape
+    assert lut.numel() == Cin * 256
+    if out is None:
+        out = torch.empty((B * (H // patch) * (W // patch), Cin * patch * patch), dtype=torch.int8, device=x.device)
+    assert out.is_contiguous() and out.numel() == x.numel() and out.dtype == torch.int8
+    check(_cabi.load().ivit_quantize_patches_u8_i8(ptr(x), ptr(out), ptr(lut), B, Cin, H, W, patch, stream()),
+          "ivit_quantize_patches_u8_i8")
+    return out
+
+
+def input_code_lut(inv_scale: float, mean, std) -> np.ndarray:
+    """int8 [Cin][256]: qact_input(Normalize(ToTensor(u))) for every uint8 pixel value u, in float32 and in the
+    order torchvision applies them: u / 255, then (x - mean[c]) / std[c], then clamp(round(fl32(1/s) * x))
+    (quant_utils.py:49,93)."""
+    f32 = np.float32
+    u = np.arange(256, dtype=f32) / f32(255.0)
+    mean, std = np.asarray(mean, dtype=f32), np.asarray(std, dtype=f32)
+    xn = ((u[None, :] - mean[:, None]).astype(f32) / std[:, None]).astype(f32)
+    q = np.rint((f32(inv_scale) * xn).astype(f32))
+    return np.clip(q, -128, 127).astype(np.int8)
+
+
 def layernorm_requant(kind: int, x: torch.Tensor, s_in: float, bias_int: torch.Tensor, sf: torch.Tensor,
                       mult: torch.Tensor, qmin: int, qmax: int, shift: float = 0.0,
                       use_int_sqrt: bool = False, out: torch.Tensor | None = None) -> torch.Tensor:

@@ -126,19 +126,23 @@ class GraphCaptureMixin:
             ev.record()
             self.trace.append((kernel, float(ops_), float(bytes_), ev))
 
-    def capture(self, B: int, slot: int = 0) -> "GraphedForward":
+    def set_uint8_input(self, mean, std):
+        """Accept uint8 images [B,C,H,W] (0..255) as well: ToTensor + Normalize(mean, std) + the input QuantAct become
+        one [C][256] code table (ops.input_code_lut; float32, torchvision's op order), applied by the input kernel."""
+        self.input_lut = ops.dev(ops.input_code_lut(self.inv_s_input, mean, std), torch.int8, self.device)
+
+    def capture(self, B: int, slot: int = 0, dtype=torch.float32) -> "GraphedForward":
         """Capture the launch sequence for batch B into a CUDA graph over a static input buffer.
         Graphs of different ``slot`` have their own input buffer but share the activation buffers
         (replay them on one stream)."""
-        if (B, slot) in self._graphs:
-            return self._graphs[(B, slot)]
+        if (B, slot, dtype) in self._graphs:
+            return self._graphs[(B, slot, dtype)]
         with _device_guard(self.device):
-            return self._capture(B, slot)
+            return self._capture(B, slot, dtype)
 
-    def _capture(self, B: int, slot: int) -> "GraphedForward":
+    def _capture(self, B: int, slot: int, dtype) -> "GraphedForward":
         cfg = self.cfg
-        static_in = torch.zeros((B, cfg.in_chans, cfg.img_size, cfg.img_size), dtype=torch.float32,
-                                device=self.device)
+        static_in = torch.zeros((B, cfg.in_chans, cfg.img_size, cfg.img_size), dtype=dtype, device=self.device)
         side = torch.cuda.Stream(device=self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(side):           # warm-up: cudaFuncSetAttribute etc. outside capture
@@ -150,7 +154,7 @@ class GraphCaptureMixin:
         with torch.cuda.graph(g):
             out = self._enqueue(static_in)
         gf = GraphedForward(g, static_in, out, self.launches_per_forward)
-        self._graphs[(B, slot)] = gf
+        self._graphs[(B, slot, dtype)] = gf
         return gf
 
 
@@ -398,8 +402,10 @@ class FrozenVitPlan(GraphCaptureMixin):
         """Enqueue one forward on torch's current stream.  images: float32 [B,3,H,W] on the device.
         taps (tests): name -> int8 code tensor (cloned) under the reference's module names."""
         cfg = self.cfg
-        if self.host_only or not images.is_cuda or images.dtype != torch.float32:
-            raise _cabi.IvitKernelError("images must be a float32 CUDA tensor (there is no CPU fallback)")
+        u8 = images.dtype == torch.uint8 and getattr(self, "input_lut", None) is not None
+        if self.host_only or not images.is_cuda or (images.dtype != torch.float32 and not u8):
+            raise _cabi.IvitKernelError("images must be a float32 CUDA tensor, or uint8 after set_uint8_input "
+                                        "(there is no CPU fallback)")
         B = images.shape[0]
         N, C, H, hd = self.N, self.C, self.H, self.hd
         bufs = self._buffers(B)
@@ -410,8 +416,12 @@ class FrozenVitPlan(GraphCaptureMixin):
                 taps[name] = (t.reshape(shape) if shape else t).clone()
 
         # stem
-        ops.quantize_patches(images, self.inv_s_input, cfg.patch_size, out=bufs["patches"])
-        self._mark("quantize_patches", 0, 5 * images.numel())
+        if u8:
+            ops.quantize_patches_u8(images, self.input_lut, cfg.patch_size, out=bufs["patches"])
+            self._mark("quantize_patches_u8", 0, 2 * images.numel())
+        else:
+            ops.quantize_patches(images, self.inv_s_input, cfg.patch_size, out=bufs["patches"])
+            self._mark("quantize_patches", 0, 5 * images.numel())
         x, x_mid = bufs["x"], bufs["x_mid"]
         self._gemm(bufs["patches"], self.patch, EPI_RESIDUAL, x, name="patch", identity=self.pos_codes, group=cfg.num_patches,
                    out_group_stride=N, out_row_off=1, id_broadcast=True)

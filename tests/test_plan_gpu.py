@@ -209,3 +209,24 @@ def test_fused_fc1_gelu_plan_equals_two_launch_plan(case):
     for k in t0:
         assert torch.equal(t0[k], t1[k]), k
     assert torch.equal(fused.forward(x), want)
+
+
+def test_uint8_images_equal_normalised_float_path():
+    """InferenceSession(uint8_input=(mean, std)): uint8 images through the [C][256] code table == the float32 path fed
+    torchvision's ToTensor + Normalize of the same pixels (bit-identical logits), eager, graph and session."""
+    from ivit_b200.api import InferenceSession
+    cfg, state, _ = load_case("deit_tiny_ivit")
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    g = torch.Generator().manual_seed(3)
+    u8 = torch.randint(0, 256, (6, 3, cfg.img_size, cfg.img_size), generator=g, dtype=torch.uint8)
+    xn = u8.float().div(255)                                        # ToTensor
+    xn = xn.sub_(torch.tensor(mean).view(1, 3, 1, 1)).div_(torch.tensor(std).view(1, 3, 1, 1))   # Normalize
+    plan = FrozenVitPlan(cfg, state, "cuda")
+    want = plan.forward(xn.cuda()).clone()
+    plan.set_uint8_input(mean, std)
+    assert torch.equal(plan.forward(u8.cuda()), want)
+    sess = InferenceSession(cfg, state, batch=6, uint8_input=(mean, std))
+    for _ in range(2):
+        assert torch.equal(sess.infer(u8.pin_memory()), want.cpu())
+    with pytest.raises(ValueError):
+        sess.infer(xn)
