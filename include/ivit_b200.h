@@ -195,7 +195,8 @@ int ivit_gemm_i8_simple(const int8_t* A, int64_t lda, const int8_t* W, int M, in
  * -> QuantMatMul(attn, v) -> transpose(1,2).reshape -> attn.qact2.  Scores never leave the SM.
  * qkv int8 [B, N, 3, H, hd] (the layout QuantLinear(qkv)+qact1 produce); out int8 [B, N, H*hd]. */
 typedef struct {
-  int kind;                  /* 0 ivit, 1 ibert */
+  int kind;                  /* 0 ivit, 1 ibert, 2 ppoly (ppoly_modules.py:296-342: the exp term only from a caller-built
+                              * exp_table; 2^32 numerator, denominator clamped to >= 1) */
   int output_bit;            /* softmax output bits: 8, or 16 (softmax_bw = 16: codes up to 32768, u16 operand
                               * split into two u8 planes, two MMAs) */
   double mult_attn;          /* qact_attn1: m*2^-e of (s_q*s_k*scale)/s_attn */

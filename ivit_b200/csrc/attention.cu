@@ -361,6 +361,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
     for (int l = 0; l < 8; ++l) sum = __fadd_rn(sum, p8[l]);
     if (a.p.kind == 0) sum = fminf(sum, 2147483648.f);               // ivit_modules.py:173
+    if (a.p.kind == 2) sum = fmaxf(sum, 1.f);                        // ppoly_modules.py:318
     const float factor = floorf(__fdiv_rn(a.num, sum));              // :174 / ibert :314
     // floor(e*factor / 2^k) == floor(e * (factor / 2^k)): scaling by a power of two is exact
     sFac[r_loc] = __fmul_rn(factor, a.out_shift);
@@ -675,6 +676,7 @@ attention_rows_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 #pragma unroll
         for (int l = 0; l < 8; ++l) sum[u] = __fadd_rn(sum[u], __shfl_sync(0xffffffffu, pl[u], l));
         if (a.p.kind == 0) sum[u] = fminf(sum[u], 2147483648.f);         // ivit_modules.py:173
+        if (a.p.kind == 2) sum[u] = fmaxf(sum[u], 1.f);                  // ppoly_modules.py:318
         const float factor = floorf(__fdiv_rn(a.num, sum[u]));            // :174 / ibert :314
         fs[u] = __fmul_rn(factor, a.out_shift);                           // power-of-two scaling is exact
       }
@@ -768,6 +770,9 @@ static int g_attn_variant = 0;
 static int attention_launch(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int N, int H, int hd,
                             const ivit_attention_params_t* p, cudaStream_t st) {
   if (!p) return fail(IVIT_ERR_BAD_ARG, "attention: params NULL");
+  if (p->kind < 0 || p->kind > 2) return fail(IVIT_ERR_BAD_ARG, "attention: kind 0 (ivit), 1 (ibert) or 2 (ppoly)");
+  if (p->kind == 2 && p->exp_table == nullptr && p->exp_table_1d == nullptr)
+    return fail(IVIT_ERR_BAD_ARG, "attention: the ppoly softmax (kind 2) takes its exp term from a caller-built table");
   if (hd != HD) return fail(IVIT_ERR_UNSUPPORTED, "attention: head_dim must be 64");
   if (N < 1 || N > 256) return fail(IVIT_ERR_UNSUPPORTED, "attention: 1 <= N <= 256 tokens");
   if (p->output_bit < 2 || p->output_bit > 16)

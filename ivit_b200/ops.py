@@ -251,7 +251,7 @@ def _table_saturation(table: torch.Tensor):
     return sat_k, float(table.view(256, 256)[255, 0].item())
 
 
-def softmax_table_build(params: AttentionParams, device, collapse: bool = True) -> torch.Tensor:
+def softmax_table_build(params: AttentionParams, device, collapse: bool = True, host_table=None) -> torch.Tensor:
     """Tabulate the softmax exp term over (row-max code, code) and attach it to `params`; when the
     table depends on the code difference only (checked on the device, bit for bit) also attach the
     256-entry form the kernel keeps in shared memory.  The returned tensor owns the memory: keep
@@ -260,7 +260,10 @@ def softmax_table_build(params: AttentionParams, device, collapse: bool = True) 
     buf = torch.empty(65536 + 256, dtype=torch.float32, device=device)
     params.exp_table = None
     params.exp_table_1d = None
-    check(lib.ivit_softmax_table_build(C.byref(params), ptr(buf), stream()), "ivit_softmax_table_build")
+    if host_table is not None:        # kind 2 (ppoly): the term table comes from the module's stored coefficients
+        buf[:65536].copy_(torch.from_numpy(np.ascontiguousarray(host_table, dtype=np.float32)).reshape(-1))
+    else:
+        check(lib.ivit_softmax_table_build(C.byref(params), ptr(buf), stream()), "ivit_softmax_table_build")
     params.exp_table = buf.data_ptr()
     params.sat_k, params.sat_e = _table_saturation(buf[:65536])
     if collapse:

@@ -40,6 +40,10 @@ from .synthetic import VitConfig
 f32 = np.float32
 
 
+def _raw(v) -> np.ndarray:
+    return v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else np.asarray(v)
+
+
 def _np(v) -> np.ndarray:
     if isinstance(v, torch.Tensor):
         v = v.detach().cpu().numpy()
@@ -101,7 +105,9 @@ def _layer_kind(name: str) -> int:
         return 0
     if base == "ibert":
         return 1
-    raise NotImplementedError(f"layer type {name!r}: this plan covers the ivit|ibert registry entries")
+    if base == "ppoly":            # piecewise-polynomial GELU / softmax: per-layer tables from the stored coefficients
+        return 2
+    raise NotImplementedError(f"layer type {name!r}: this plan covers the ivit|ibert|ppoly registry entries")
 
 
 def _device_guard(device):
@@ -187,10 +193,17 @@ class FrozenVitPlan(GraphCaptureMixin):
         self.pos_dtype = torch.int16 if self.bw_pos > 8 else torch.int8
         if not host_only:
             _cabi.load()
-        self.sd = {k: _np(v) for k, v in state.items() if not k.endswith(("weight_integer", "bias_integer"))}
+        # ppoly coefficient buffers (`*.fixed_bounds`, `*.fixed_coeffs`) are int32: keep them exact
+        self.sd = {k: (_raw(v) if ".fixed_" in k else _np(v)) for k, v in state.items()
+                   if not k.endswith(("weight_integer", "bias_integer"))}
         self.gelu_kind = _layer_kind(cfg.gelu_type)
         self.softmax_kind = _layer_kind(cfg.softmax_type)
         self.ln_kind = _layer_kind(cfg.layernorm_type)
+        if self.ln_kind == 2:
+            raise NotImplementedError("there is no ppoly LayerNorm (layer_selection.py:132-136)")
+        from .quantization_utils.registry import parse_layer_name
+        self.gelu_args = parse_layer_name(cfg.gelu_type)[1]
+        self.softmax_args = parse_layer_name(cfg.softmax_type)[1]
         self.ln_int_sqrt = "use-int-sqrt_true" in cfg.layernorm_type
         self.C = cfg.embed_dim
         self.N = cfg.tokens
@@ -261,8 +274,15 @@ class FrozenVitPlan(GraphCaptureMixin):
         a.mult_attn = float(hm.dyadic_mult(s_scaled, s_attn).reshape(-1)[0])
         a.qmin_attn, a.qmax_attn = -128, 127
         a.s_attn = float(s_attn[0])
+        host_table = None
         if self.softmax_kind == 0:
             s_sm = np.array([1 / 2 ** (ob - 1)], dtype=f32)        # ivit_modules.py:177
+        elif self.softmax_kind == 2:
+            from .quantization_utils import ppoly as pp
+            s_sm = np.array([2 / 2 ** ob], dtype=f32)              # ppoly_modules.py:329
+            host_table = pp.softmax_term_table(s_attn, self.sd[p + "int_softmax.fixed_bounds"],
+                                               self.sd[p + "int_softmax.fixed_coeffs"],
+                                               int(self.softmax_args.get("exp_bits", 16)))
         else:
             s_sm = np.array([2 / 2 ** ob], dtype=f32)              # ibert_modules.py:317
             s16 = self._act_scale(p + "int_softmax.act", 16)       # inner QuantAct(16), :262,:310
@@ -275,7 +295,7 @@ class FrozenVitPlan(GraphCaptureMixin):
         a.mult_out = float(hm.dyadic_mult(s_mm2, s_out).reshape(-1)[0])
         a.qmin_out, a.qmax_out = -128, 127
         if not self.host_only:
-            self._tables.append(ops.softmax_table_build(a, self.device))
+            self._tables.append(ops.softmax_table_build(a, self.device, host_table=host_table))
         return a, s_out
 
     def _build(self):
@@ -315,7 +335,7 @@ class FrozenVitPlan(GraphCaptureMixin):
             s_g = self._act_scale(p + "mlp.qact_gelu")
             b.fc1 = self._linear(p + "mlp.fc1", s_n2, s_g)
             s_m1 = self._act_scale(p + "mlp.qact1")
-            b.gelu_lut, b.scales["gelu_out"] = self._gelu_lut(s_g, s_m1)
+            b.gelu_lut, b.scales["gelu_out"] = self._gelu_lut(s_g, s_m1, p + "mlp.act")
             s_m2 = self._act_scale(p + "mlp.qact2", self.bw_mlp_out)
             s_o = self._act_scale(p + "qact4", self.bw_block_out)
             b.fc2 = self._residual(self._linear(p + "mlp.fc2", s_m1, s_m2, self.bw_mlp_out), s_m2, s_mid, s_o,
@@ -332,11 +352,19 @@ class FrozenVitPlan(GraphCaptureMixin):
         if not self.host_only:
             torch.cuda.synchronize(self.device)
 
-    def _gelu_lut(self, s_in: np.ndarray, s_out: np.ndarray):
+    def _gelu_lut(self, s_in: np.ndarray, s_out: np.ndarray, name: str = ""):
         """mlp.act + mlp.qact1 tabulated over (row max code, code): built on device by the exact
         arithmetic (rowwise.cu gelu_lut_build_kernel).  The dyadic multiplier needs the GELU's own
         output scale first: ivit s/2^7 (ivit_modules.py:121-124), ibert s*s_erf/2 (:233)."""
         s = f32(s_in[0])
+        if self.gelu_kind == 2:        # ppoly: the module's stored coefficients, tabulated on the host
+            from .quantization_utils.ppolymods import gelu_lut_from_coeffs
+            s_g = np.asarray(self.sd[name + ".fixed_scaling_factor_out"], dtype=f32).reshape(1)
+            if self.host_only:
+                return None, s_g[0]
+            lut = gelu_lut_from_coeffs(s, self.sd[name + ".fixed_bounds"], self.sd[name + ".fixed_coeffs"], s_g,
+                                       int(self.gelu_args.get("scale_bits", 22)), s_out, 8, self.device)
+            return lut, s_g[0]
         if self.gelu_kind == 0:
             s_g = np.array([s * f32(1 / 2 ** 7)], dtype=f32)
         else:

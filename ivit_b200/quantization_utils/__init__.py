@@ -9,6 +9,7 @@ from .iostats import (attach_io_stat_hooks, clear_io_stats, disable_io_stats, en
                       save_io_stats_df)
 from .modules import (IBERTIntGELU, IBERTIntLayerNorm, IBERTIntSoftmax, IVITIntGELU, IVITIntLayerNorm,
                       IVITIntSoftmax, QuantAct, QuantConv2d, QuantLinear, QuantMatMul)
+from .ppolymods import PPolyIntGELU, PPolyIntSoftmax
 from .registry import get_gelu, get_layernorm, get_softmax
 
 IntLayerNorm, IntSoftmax, IntGELU = IVITIntLayerNorm, IVITIntSoftmax, IVITIntGELU
@@ -25,4 +26,4 @@ __all__ = ["QuantLinear", "QuantAct", "QuantConv2d", "QuantMatMul", "attach_io_s
            "enable_io_stats", "disable_io_stats", "clear_io_stats", "softmax", "IVITIntGELU", "IVITIntSoftmax",
            "IVITIntLayerNorm", "IBERTIntGELU", "IBERTIntSoftmax", "IBERTIntLayerNorm", "get_gelu", "get_softmax",
            "get_layernorm", "IntLayerNorm", "IntSoftmax", "IntGELU", "QTensor", "FloatGELU", "FloatSoftmax",
-           "FloatLayerNorm"]
+           "FloatLayerNorm", "PPolyIntGELU", "PPolyIntSoftmax"]

@@ -806,7 +806,7 @@ def _frozen_attention(p, view: QTensor, qact2: QuantAct, device):
         _, s_out_h, (lo2, hi2) = qact2._out_scale(device)
         a.mult_out = float(hm.dyadic_mult(p.s_h, s_out_h).reshape(-1)[0])
         a.qmin_out, a.qmax_out = lo2, hi2
-        table = ops.softmax_table_build(a, device)
+        table = ops.softmax_table_build(a, device, host_table=sm.mod.host_term_table(s_attn_h) if sm.mod._kind == 2 else None)
         cache[key] = (a, table)
     a, _ = cache[key]
     return ops.attention(base.reshape(B, N, 3 * C), B, N, H, hd, a)

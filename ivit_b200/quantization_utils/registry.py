@@ -1,18 +1,19 @@
 """--gelu / --softmax / --layernorm selection (layer_selection.py:116-236): the `ivit` and `ibert`
 entries and the `base_arg_val_arg_val` name grammar that injects constructor keywords
-(`ibert_use-int-sqrt_true` -> IBERTIntLayerNorm(use_int_sqrt=True)), and the `float` diagnostics
-(true float op + quantised output, torch ops in every mode).  The `ppoly` entries are outside this
-path and raise a clear error."""
+(`ibert_use-int-sqrt_true` -> IBERTIntLayerNorm(use_int_sqrt=True)), the `float` diagnostics
+(true float op + quantised output, torch ops in every mode) and the `ppoly` piecewise-polynomial
+GELU / softmax (`ppoly_scale-bits_20_seg_8` ...)."""
 from __future__ import annotations
 
 from .floatmods import FloatGELU, FloatLayerNorm, FloatSoftmax
+from .ppolymods import PPolyIntGELU, PPolyIntSoftmax
 from .modules import (IBERTIntGELU, IBERTIntLayerNorm, IBERTIntSoftmax, IVITIntGELU, IVITIntLayerNorm,
                       IVITIntSoftmax)
 
-GELU_REGISTRY = {"float": FloatGELU, "ivit": IVITIntGELU, "ibert": IBERTIntGELU}
-SOFTMAX_REGISTRY = {"float": FloatSoftmax, "ivit": IVITIntSoftmax, "ibert": IBERTIntSoftmax}
+GELU_REGISTRY = {"float": FloatGELU, "ivit": IVITIntGELU, "ibert": IBERTIntGELU, "ppoly": PPolyIntGELU}
+SOFTMAX_REGISTRY = {"float": FloatSoftmax, "ivit": IVITIntSoftmax, "ibert": IBERTIntSoftmax, "ppoly": PPolyIntSoftmax}
 LN_REGISTRY = {"float": FloatLayerNorm, "ivit": IVITIntLayerNorm, "ibert": IBERTIntLayerNorm}
-_NOT_BUILT = ("ppoly",)
+_NOT_BUILT = ()
 
 
 def _coerce(text: str):

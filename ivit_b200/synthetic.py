@@ -135,6 +135,10 @@ CASES = {
     "deit_tiny_ibert_w16": ("deit_tiny", "ibert", "ibert", "ibert", 0.0, (16,) * 8),
     "deit_tiny_ivit_w16": ("deit_tiny", "ivit", "ivit", "ivit", 0.0, (16,) * 8),
     "deit_base_ibert_w16": ("deit_base", "ibert", "ibert", "ibert", 0.0, (16,) * 8),    # BASELINE.json configs[4]
+    # the `ppoly` registry entries (layer_selection.py:116-131)
+    "toy_ppoly": ("toy", "ppoly", "ppoly", "ivit", 0.0),
+    "toy_ppoly_args": ("toy", "ppoly_scale-bits_20_seg_8_backend_float", "ppoly_exp-bits_12_seg_8", "ibert", 0.0),
+    "deit_tiny_ppoly": ("deit_tiny", "ppoly", "ppoly", "ivit", 0.0),
 }
 
 
@@ -157,6 +161,8 @@ def load_case(case: str):
     for k in fix.files:
         if k.startswith("range/"):
             state[k[len("range/"):]] = fix[k].astype(np.float32)
+        elif k.startswith("fixed/"):                    # ppoly layers: stored integer coefficients (state_dict buffers)
+            state[k[len("fixed/"):]] = fix[k]
     return cfg, state, fix
 
 
@@ -267,4 +273,6 @@ def load_swin_case(case: str):
     for k in fix.files:
         if k.startswith("range/"):
             state[k[len("range/"):]] = fix[k].astype(np.float32)
+        elif k.startswith("fixed/"):                    # ppoly layers: stored integer coefficients (state_dict buffers)
+            state[k[len("fixed/"):]] = fix[k]
     return cfg, state, fix

@@ -503,3 +503,48 @@ def ibert_softmax(x, scale, output_bit: int, act_x_min, act_x_max):
     out_int = np.floor(exp_int * factor / f32(2 ** (32 - output_bit + 1)))   # :315
     out_scale = np.array([2 / 2 ** output_bit], dtype=f32)    # :317
     return (out_int * out_scale).astype(f32), out_scale, out_int.astype(f32)
+
+
+# --------------------------------------------------------------------------
+# ppoly_modules.py / ppoly_backend.py (frozen: the stored integer coefficients are inputs)
+# --------------------------------------------------------------------------
+def ppoly_horner(x_int, bounds, coeffs):
+    """ppoly_backend.py:293-351 evaluate_piecewise_polynomial.  x_int integer-valued array; bounds int [S-1];
+    coeffs int [S, D+1] (highest power first).  Horner in int64, result WRAPPED to int32 like `.to(torch.int32)`."""
+    x = np.asarray(x_int).astype(np.int64)
+    bounds = np.asarray(bounds).reshape(-1).astype(np.int64)
+    coeffs = np.asarray(coeffs).astype(np.int64).reshape(len(bounds) + 1, -1)
+    seg = np.searchsorted(bounds, x, side="right")            # x < b0 -> 0; b_{i-1} <= x < b_i -> i; x >= b_last -> S-1
+    r = coeffs[seg, 0]
+    for d in range(1, coeffs.shape[1]):
+        r = r * x + coeffs[seg, d]
+    return r.astype(np.int32)                                 # wraps modulo 2^32
+
+
+def ppoly_gelu(x, scale, bounds, coeffs, scale_out, scale_bits: int = 22):
+    """ppoly_modules.py:110-136 PPolyIntGELU.forward with fixed coefficients.  Returns (y, scale_out)."""
+    x = _f32(x)
+    scale = _f32(scale)
+    scale_out = _f32(scale_out)
+    x_int = np.floor(x / scale)                                           # :114
+    y_int = ppoly_horner(x_int, bounds, coeffs)                           # :128
+    y_float = (y_int.astype(f32) / f32(2 ** scale_bits)).astype(f32)      # :134 (int32 / python int -> float32)
+    y = (scale_out * np.floor(y_float / scale_out)).astype(f32)           # :140
+    return y, scale_out
+
+
+def ppoly_softmax(x, scale, bounds, coeffs, output_bit: int = 8, exp_bits: int = 16):
+    """ppoly_modules.py:296-342 PPolyIntSoftmax.forward with fixed coefficients (the polynomial's own scale_bits only
+    enter through the stored coefficients).  Returns (y, scale_out, codes)."""
+    x = _f32(x)
+    scale = _f32(scale)
+    x_int = np.floor(x / scale).astype(np.int32)                          # :302
+    x_int = x_int - x_int.max(axis=-1, keepdims=True) + 127              # :305-306
+    exp_int = np.maximum(ppoly_horner(x_int, bounds, coeffs), 0)         # :309, :271
+    exp_f = np.floor(exp_int.astype(f32) / f32(2 ** (30 - exp_bits + 1)))   # :312
+    ssum = np.maximum(torch_sum_lastdim(exp_f), f32(1.0))                # :315-318
+    factor = np.floor(f32(2 ** 32) / ssum)                               # :322
+    out_int = np.floor(exp_f * factor / f32(2 ** (32 - output_bit + 1)))   # :323
+    s_out = np.array([2 / 2 ** output_bit], dtype=f32)                    # :329
+    y = (s_out * np.floor((out_int * s_out).astype(f32) / s_out)).astype(f32)   # :330-336
+    return y, s_out, out_int.astype(f32)

@@ -44,6 +44,10 @@ CASES = {
     "toy_ibert": ("toy", "ibert", "ibert", "ibert", None, 2, 0.0, ("blocks.0.attn.qact2", "blocks.1.qact4")),
     "toy_mixed": ("toy", "ivit", "ibert", "ivit", None, 2, 0.05, ("blocks.1.qact4",)),
     "toy_ibert_intsqrt": ("toy", "ibert", "ibert", "ibert_use-int-sqrt_true", None, 2, 0.0, ()),
+    # the `ppoly` registry entries (layer_selection.py:116-131): piecewise-polynomial GELU and softmax
+    "toy_ppoly": ("toy", "ppoly", "ppoly", "ivit", None, 2, 0.0, ("blocks.0.attn.qact2", "blocks.1.qact4")),
+    "toy_ppoly_args": ("toy", "ppoly_scale-bits_20_seg_8_backend_float", "ppoly_exp-bits_12_seg_8", "ibert", None, 2, 0.0, ()),
+    "deit_tiny_ppoly": ("deit_tiny", "ppoly", "ppoly", "ivit", None, 2, 0.0, ("qact2",)),
     # BASELINE.json configs[0]: DeiT-Tiny INT8 ivit, batch 8
     "deit_tiny_ivit": ("deit_tiny", "ivit", "ivit", "ivit", None, 8, 0.0, ("qact2",)),
     "deit_tiny_ibert": ("deit_tiny", "ibert", "ibert", "ibert", None, 2, 0.0, ("qact2",)),
@@ -96,6 +100,10 @@ def make_vit_case(name: str) -> dict:
                                                            cfg.layernorm_type, str(batch), str(neg)])}
     for k, v in ranges.items():
         out["range/" + k] = v
+    # ppoly layers: the integer coefficients the frozen modules fitted on their first batch (ppoly_modules.py:57-108)
+    for k, v in model.state_dict().items():
+        if ".fixed_" in k:
+            out["fixed/" + k] = v.detach().cpu().numpy()
     names, code_sha, scale_sha = [], [], []
     for k, (y, s) in taps.items():
         names.append(k)

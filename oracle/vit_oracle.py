@@ -25,12 +25,22 @@ def _np(t):
     return t.detach().cpu().numpy() if hasattr(t, "detach") else np.asarray(t)
 
 
+def _layer_kwargs(name: str) -> dict:
+    """'ppoly_scale-bits_20_seg_16' -> {'scale_bits': 20, 'seg': 16} (layer_selection.py:137-179)."""
+    parts = name.lower().split("_")
+    out = {}
+    if len(parts) >= 3:
+        for k, v in zip(parts[1:-1:2], parts[2::2]):
+            out[k.replace("-", "_")] = int(v) if v.isdigit() else v
+    return out
+
+
 class VitOracle:
     def __init__(self, cfg, state: dict):
         """cfg: ivit_b200.synthetic.VitConfig; state: name -> array (weights and x_min/x_max buffers)."""
         self.cfg = cfg
-        self.sd = {k: _np(v).astype(np.float32) for k, v in state.items()
-                   if not k.endswith(("weight_integer", "bias_integer"))}
+        self.sd = {k: (_np(v) if ".fixed_" in k else _np(v).astype(np.float32)) for k, v in state.items()
+                   if not k.endswith(("weight_integer", "bias_integer"))}       # ppoly coefficients stay integers
         self.taps: dict = {}
         self.record = False
 
@@ -66,6 +76,10 @@ class VitOracle:
     def _gelu(self, name, x, s):
         if self.cfg.gelu_type.startswith("ivit"):
             y, sc, yi = O.ivit_gelu(x, s)
+        elif self.cfg.gelu_type.startswith("ppoly"):
+            kw = _layer_kwargs(self.cfg.gelu_type)
+            y, sc = O.ppoly_gelu(x, s, self.sd[name + ".fixed_bounds"], self.sd[name + ".fixed_coeffs"],
+                                 self.sd[name + ".fixed_scaling_factor_out"], int(kw.get("scale_bits", 22)))
         else:
             y, sc, yi = O.ibert_gelu(x, s)
         self._tap(name, y, sc)
@@ -74,6 +88,10 @@ class VitOracle:
     def _softmax(self, name, x, s, bits):
         if self.cfg.softmax_type.startswith("ivit"):
             y, sc, yi = O.ivit_softmax(x, s, bits)
+        elif self.cfg.softmax_type.startswith("ppoly"):
+            kw = _layer_kwargs(self.cfg.softmax_type)
+            y, sc, yi = O.ppoly_softmax(x, s, self.sd[name + ".fixed_bounds"], self.sd[name + ".fixed_coeffs"], bits,
+                                        int(kw.get("exp_bits", 16)))
         else:
             y, sc, yi = O.ibert_softmax(x, s, bits, self.sd[name + ".act.x_min"], self.sd[name + ".act.x_max"])
         self._tap(name, y, sc)

@@ -29,8 +29,10 @@ def test_registry_grammar():
     cls = qu.get_layernorm("ibert_use-int-sqrt_true")
     assert issubclass(cls, qu.IBERTIntLayerNorm) and cls(64).use_int_sqrt is True
     assert qu.get_gelu("ivit") is qu.IVITIntGELU and qu.get_softmax("IBERT") is qu.IBERTIntSoftmax
-    with pytest.raises(NotImplementedError):
-        qu.get_gelu("ppoly_deg_2_seg_16")
+    pg = qu.get_gelu("ppoly_deg_2_seg_8")()
+    assert isinstance(pg, qu.PPolyIntGELU) and (pg.segments, pg.degree, pg.N, pg.backend) == (8, 2, 22, "ibert")
+    ps = qu.get_softmax("ppoly_exp-bits_12")(8)
+    assert isinstance(ps, qu.PPolyIntSoftmax) and (ps.exp_bitwidth, ps.N, ps.segments) == (12, 28, 16)
     assert qu.get_gelu("float") is qu.FloatGELU and qu.get_layernorm("FLOAT") is qu.FloatLayerNorm
     assert qu.get_softmax("float_bitwidth_16")().bitwidth == 16
     with pytest.raises(KeyError):
@@ -57,7 +59,7 @@ def test_frozen_path_refuses_cpu():
 
 
 @pytest.mark.reference
-@pytest.mark.parametrize("case", ["toy_ivit", "toy_ibert", "toy_mixed", "deit_tiny_ivit"])
+@pytest.mark.parametrize("case", ["toy_ivit", "toy_ibert", "toy_mixed", "deit_tiny_ivit", "toy_ppoly", "toy_ppoly_args"])
 def test_reference_vit_quant_runs_unchanged_and_calibrates_identically(case):
     from oracle.ref_shim import load_reference_callers_on
     vq, mu = load_reference_callers_on(qu)
@@ -85,6 +87,14 @@ def test_reference_vit_quant_runs_unchanged_and_calibrates_identically(case):
             assert np.array_equal(got, fix[k].astype(f32)), name
             n += 1
     assert n >= 40
+    # ppoly layers: the segment fit of the calibration pass leaves the reference's integer coefficients behind
+    nfix = 0
+    for k in fix.files:
+        if k.startswith("fixed/"):
+            name = k[len("fixed/"):]
+            assert np.array_equal(sd[name].numpy(), fix[k]), name
+            nfix += 1
+    assert nfix == (5 * cfg.depth if "ppoly" in case else 0)
     mu.freeze_model(model)
     assert model.qact_input.running_stat is False
     with pytest.raises(IvitKernelError):                    # frozen = integer kernels = CUDA only

@@ -19,6 +19,7 @@ def _build(case):
     model = VisionTransformer(cfg)
     sd = {k: torch.as_tensor(v).reshape(model.state_dict()[k].shape) for k, v in state.items()
           if k in model.state_dict()}
+    sd.update({k: torch.as_tensor(v) for k, v in state.items() if ".fixed_" in k})    # ppoly coefficient buffers
     missing, unexpected = model.load_state_dict(sd, strict=False)
     assert not unexpected
     assert not [k for k in missing if k.endswith((".weight", ".bias", ".x_min", ".x_max"))], missing
@@ -28,7 +29,7 @@ def _build(case):
 
 
 @pytest.mark.parametrize("case", ["toy_ivit", "toy_ibert", "toy_mixed", "deit_tiny_ivit", "toy_ivit_w16", "toy_ibert_w16",
-                                  "toy_mixed_bw", "toy_ivit_sm16"])
+                                  "toy_mixed_bw", "toy_ivit_sm16", "toy_ppoly", "toy_ppoly_args"])
 def test_frozen_modules_match_oracle(case):
     cfg, state, fix, model = _build(case)
     x = synth_images(2, cfg, seed=0)

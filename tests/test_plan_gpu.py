@@ -81,6 +81,16 @@ def test_base_models_at_bench_batch_every_boundary(case, batch, idx):
     assert np.allclose(logits[:len(ref)], ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
 
 
+@pytest.mark.parametrize("case", ["toy_ppoly", "toy_ppoly_args", "deit_tiny_ppoly"])
+def test_ppoly_layers_all_boundaries(case):
+    """--gelu ppoly --softmax ppoly (layer_selection.py:116-131): the stored integer coefficients become per-layer
+    tables; every boundary bit-exact against the oracle, logits against the reference fixture."""
+    _, _, _, logits, fix = _run_case(case, 2)
+    ref = fix["logits"]
+    assert np.array_equal(logits.argmax(1), ref.argmax(1))
+    assert np.allclose(logits, ref, rtol=1e-6, atol=1e-6 * np.abs(ref).max())
+
+
 @pytest.mark.parametrize("case", ["toy_ivit", "toy_ibert", "toy_mixed", "toy_ibert_intsqrt"])
 def test_toy_all_boundaries(case):
     _, _, _, logits, fix = _run_case(case, 2)
