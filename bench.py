@@ -435,13 +435,13 @@ def run_ours(args):
         roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
                 "frac": ach / pk["hbm_gbs"], "traffic": None, "peak_source": f"hbm_gbs ({pk['source']})"}
     # measured DRAM bytes per launch of that kernel class, from the committed `ncu --set full` capture
-    # (profiles/r1_traffic.json, written by tools/traffic_from_ncu.py); only valid for the workload it was taken on
-    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")
+    # (profiles/r2_traffic.json, written by tools/traffic_from_ncu.py); only valid for the workload it was taken on
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r2_traffic.json")
     if os.path.exists(tpath) and args.case == "deit_small_ivit" and B == 256:
         tj = json.load(open(tpath))
         if dom in tj:
             roof["traffic"] = tj[dom]["traffic_per_launch"]
-            roof["traffic_source"] = "profiles/r1_traffic.json (ncu --set full, dram read+write bytes, average over the step's launches)"
+            roof["traffic_source"] = "profiles/r2_traffic.json (ncu --set full, dram read+write bytes, average over the step's launches)"
             roof["algorithmic_bytes_per_launch"] = d["bytes"] / d["launches"]
     roof.update(launches_per_step=d["launches"], ms_per_step=d["ms"], share_of_step=d["ms"] / total_ms,
                 algorithmic_per_launch=(d["ops"] if d["ops"] > 0 else d["bytes"]) / d["launches"],

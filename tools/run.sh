@@ -1,6 +1,6 @@
 #!/bin/bash
 # One parameterised GPU-box runner (replaces the round-1 run_*.sh scratch launchers).
-#   tools/run.sh <tag> <steps...>    steps: noalloc tests smoke bench benchref launches case:<name>:<batch>
+#   tools/run.sh <tag> <steps...>    steps: noalloc tests smoke bench benchref launches ncufull case:<name>:<batch>
 mkdir -p gpurun_out
 T=${1:-r2}; shift
 for step in "$@"; do
@@ -23,6 +23,11 @@ launches)
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/${T}_ncu.log 2>&1
   echo "ncu exit $?" ;;
+ncufull)
+  # one DeiT-S block of the second forward (patch GEMM, LN, qkv, attention, proj, LN, fc1, GELU, fc2), full sections
+  timeout 900 ncu --set full --import-source on --clock-control none -k regex:"gemm_i8|layernorm|attention|gelu_lut" -s 99 -c 9 \
+    -o gpurun_out/${T}_block -f python tools/prof_step.py > gpurun_out/${T}_ncufull.log 2>&1
+  echo "ncu full exit $?" ;;
 case:*)
   IFS=: read -r _ name batch <<< "$step"
   timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --case $name --batch $batch > gpurun_out/${T}_bench_$name.json 2> gpurun_out/${T}_bench_$name.err

@@ -1,17 +1,17 @@
 #!/usr/bin/env python
 """DRAM traffic per launch of each kernel class from the `ncu --set full` capture of one block
-(tools/run_ncu_full.sh: patch GEMM, LN, qkv, attention, proj, LN, fc1, GELU, fc2), weighted by how
-often each launch occurs in one DeiT-S forward.  usage: traffic_from_ncu.py raw.csv > profiles/r1_traffic.json"""
+(tools/run.sh <tag> ncufull: patch GEMM, LN, qkv, attention, proj, LN, fc1, GELU, fc2), weighted by how
+often each launch occurs in one DeiT-S forward.  usage: traffic_from_ncu.py raw.csv > profiles/r2_traffic.json"""
 import csv, json, sys
 rows = list(csv.reader(open(sys.argv[1])))
 hdr, units = rows[0], rows[1]
 ki, ri, wi = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
 def to_bytes(v, u):
     return float(v) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
-seq = [("gemm_i8_tc", "patch", 1), ("layernorm_requant", "norm1", 12.5), ("gemm_i8_tc", "qkv", 12),
-       ("attention_i8", "attention", 12), ("gemm_i8_tc", "proj", 12), ("layernorm_requant", "norm2", 12.5),
-       ("gemm_i8_tc", "fc1", 12), ("gelu_lut_apply", "gelu", 12), ("gemm_i8_tc", "fc2", 12)]
-assert len(rows) - 2 == len(seq), "expected the 9-kernel capture of tools/run_ncu_full.sh"
+seq = [("gemm_patch", "patch", 1), ("layernorm_requant", "norm1", 12.5), ("gemm_qkv", "qkv", 12),
+       ("attention_i8", "attention", 12), ("gemm_proj", "proj", 12), ("layernorm_requant", "norm2", 12.5),
+       ("gemm_fc1", "fc1", 12), ("gelu_lut_apply", "gelu", 12), ("gemm_fc2", "fc2", 12)]
+assert len(rows) - 2 == len(seq), "expected the 9-kernel capture of tools/run.sh ncufull"
 out = {}
 for r, (cls, what, per_step) in zip(rows[2:], seq):
     b = to_bytes(r[ri], units[ri]) + to_bytes(r[wi], units[wi])
