@@ -197,7 +197,7 @@ class QuantAct(_FrozenCache, nn.Module):
         shape = tuple(x.shape)
         if identity is None and kind == "gemm" and x.is_canonical() and self.activation_bit <= 16:
             # QuantLinear / QuantConv2d -> QuantAct: requantisation fused into the GEMM epilogue
-            mult, mh = self._mult(("gemm", id(p.lin)), p.lin["b_scale_h"], device)
+            mult, mh = self._mult(("gemm", p.lin["b_scale_h"].tobytes()), p.lin["b_scale_h"], device)   # keyed by value, not id()
             out = ops.gemm(p.A, p.lin["w"], _cabi.EPI_REQUANT, bias=p.lin["bias"], mult=mult, s_in=p.lin["b_scale"],
                            qmin=qmin, qmax=qmax, z_bound_ok=p.lin["z_bound_ok"],
                            force_slow=p.lin["force_slow"] or bool(np.abs(mh).max() >= 256.0), out_bits=self._store_bits())
@@ -327,8 +327,12 @@ class QuantLinear(_FrozenCache, nn.Linear):
         if self.weight_bit != 8 or not self.per_channel:
             raise NotImplementedError("frozen QuantLinear: per-channel 8-bit weights")
         c = self._fz_get()
+        s_x = np.asarray(fz.eff_hscale(x), dtype=f32)
+        if "lin" in c and not np.array_equal(c["lin_s_x"], s_x):
+            c.pop("lin")          # a different producer scale than the constants were built for: rebuild, never reuse
         if "lin" not in c:
-            c["lin"], p = _linear_constants(self, self.weight, self.bias, fz.eff_hscale(x), x.device, self.bias_bit)
+            c["lin"], p = _linear_constants(self, self.weight, self.bias, s_x, x.device, self.bias_bit)
+            c["lin_s_x"] = s_x.copy()
             self.fc_scaling_factor = _dev(p["s_w"], torch.float32, x.device)
         lin = c["lin"]
         A = x.materialize()
@@ -396,8 +400,12 @@ class QuantConv2d(_FrozenCache, nn.Conv2d):
                 or self.groups != 1 or any(d != 1 for d in self.dilation)):
             raise NotImplementedError("frozen QuantConv2d: kernel == stride, no padding (ViT/Swin patch embedding)")
         c = self._fz_get()
+        s_x = np.asarray(fz.eff_hscale(x), dtype=f32)
+        if "lin" in c and not np.array_equal(c["lin_s_x"], s_x):
+            c.pop("lin")          # constants were built for another input scale: rebuild
         if "lin" not in c:
-            c["lin"], p = _linear_constants(self, self.weight, self.bias, fz.eff_hscale(x), x.device, self.bias_bit)
+            c["lin"], p = _linear_constants(self, self.weight, self.bias, s_x, x.device, self.bias_bit)
+            c["lin_s_x"] = s_x.copy()
             self.conv_scaling_factor = _dev(p["s_w"], torch.float32, x.device)
         lin = c["lin"]
         B, Cin, H, W = (int(v) for v in x.shape)

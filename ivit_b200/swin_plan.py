@@ -328,10 +328,11 @@ class FrozenSwinPlan(GraphCaptureMixin):
                 tap(p + "qact3", ln, (B, L, C))
                 self._gemm(ln, b["fc1"], EPI_REQUANT, h1, name="fc1")
                 tap(p + "mlp.qact_gelu", h1, (B, L, Hd))
-                ops.gelu_lut_apply(h1, b["gelu_lut"], out=h2)
+                g_out = h2 if taps is not None else h1          # in place unless tapped: fc1's rows are still in L2
+                ops.gelu_lut_apply(h1, b["gelu_lut"], out=g_out)
                 self._mark("gelu_lut_apply", 0, 2 * h1.numel())
-                tap(p + "mlp.qact1", h2, (B, L, Hd))
-                self._gemm(h2, b["fc2"], EPI_RESIDUAL, x, name="fc2", identity=x_mid)
+                tap(p + "mlp.qact1", g_out, (B, L, Hd))
+                self._gemm(g_out, b["fc2"], EPI_RESIDUAL, x, name="fc2", identity=x_mid)
                 tap(p + "qact4", x, (B, L, C))
             if "reduction" in st:
                 d = f"layers.{i}.downsample."

@@ -55,8 +55,10 @@ def load_reference():
     import torch
 
     _install_stubs()
-    # CPU run of code that hard-codes `.cuda(device=...)`.
-    torch.Tensor.cuda = lambda self, device=None, *a, **k: self  # type: ignore[assignment]
+    # CPU run of code that hard-codes `.cuda(device=...)`: only where there is no CUDA device, so that a box with
+    # both the reference and a GPU keeps the real method for the `-m gpu` tests of the same process.
+    if not torch.cuda.is_available():
+        torch.Tensor.cuda = lambda self, device=None, *a, **k: self  # type: ignore[assignment]
     # The reference's top-level package is called `models`; keep it from
     # colliding with anything of ours by importing it under its own sys.path entry.
     sys.path.insert(0, REFERENCE_ROOT)
