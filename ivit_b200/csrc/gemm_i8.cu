@@ -766,8 +766,9 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 const int j = 4 * g + b;
                 const int c1 = clampi(c[j], -128, 127);
                 const int id = static_cast<int8_t>(iw >> (8 * b));
-                const double cd = __hiloint2double(0x43300000, c1 ^ 0x80000000) - kMagicInt;
-                const double dd = __hiloint2double(0x43300000, id ^ 0x80000000) - kMagicInt;
+                // int8 codes -> fp64 through I2F.F64 (one slot on the idle conversion pipe each) instead of
+                // XOR + MOV + DADD: the epilogue is issue-bound (23 instructions per output before)
+                const double cd = __int2double_rn(c1), dd = __int2double_rn(id);
                 c[j] = __double2loint(__fma_rn(cd, m2, kMagicRnd)) + __double2loint(__fma_rn(dd, mi, kMagicRnd));
               }
             }

@@ -343,14 +343,16 @@ layernorm_ivit_requant4_kernel(const int8_t* __restrict__ x, long long ldx, int8
   constexpr int VPR = C / 16;
   __shared__ __align__(16) int8_t stage[8][2][R][C];     // input rows, cp.async double buffer
   __shared__ float lut_f[256];
-  __shared__ int lut_i[256];
+  // trunc(x_eff(code)) (:36-38) as int8, indexed by the code's UNSIGNED byte and 256-byte aligned: one PRMT builds the
+  // shared address of an element's entry from the packed word (line base | byte), one LDS.S8 fetches it
+  __shared__ __align__(256) int8_t lut_t[256];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   {
     const float xe = x_eff(static_cast<float>(static_cast<int>(threadIdx.x) - 128), s_in);   // :36
     lut_f[threadIdx.x] = xe;
-    lut_i[threadIdx.x] = static_cast<int>(xe);                                               // :38 trunc
+    lut_t[threadIdx.x ^ 0x80] = static_cast<int8_t>(static_cast<int>(xe));                   // :38 trunc; |.| <= 128
   }
-  const int* lut_i0 = lut_i + 128;                  // indexed by the signed code
+  const uint32_t tb = smem_u32(lut_t);
   float bia[NPL], mf[NPL];
 #pragma unroll
   for (int j = 0; j < NJ; ++j)
@@ -394,11 +396,11 @@ layernorm_ivit_requant4_kernel(const int8_t* __restrict__ x, long long ldx, int8
 #pragma unroll
       for (int j = 0; j < NJ; ++j) {
         const uint32_t w = *reinterpret_cast<const uint32_t*>(&stage[warp][buf][r][128 * j + 4 * lane]);
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          y[r][4 * j + b] = sext_byte(w, b);
-          S[r] += y[r][4 * j + b];
-        }
+        S[r] = __dp4a(static_cast<int>(w), 0x01010101, S[r]);              // sum of the four codes
+        y[r][4 * j + 0] = lds_s8(__byte_perm(w, tb, 0x7650));               // trunc(x_eff(code)) of each
+        y[r][4 * j + 1] = lds_s8(__byte_perm(w, tb, 0x7651));
+        y[r][4 * j + 2] = lds_s8(__byte_perm(w, tb, 0x7652));
+        y[r][4 * j + 3] = lds_s8(__byte_perm(w, tb, 0x7653));
       }
     }
 #pragma unroll
@@ -425,7 +427,7 @@ layernorm_ivit_requant4_kernel(const int8_t* __restrict__ x, long long ldx, int8
       int vr = 0;
 #pragma unroll
       for (int i = 0; i < NPL; ++i) {
-        y[r][i] = lut_i0[y[r][i]] - mean[r];                        // :38-40 (trunc, int32)
+        y[r][i] -= mean[r];                                         // :38-40 (trunc done by the table, int32)
         vr += y[r][i] * y[r][i];
       }
       var[r] = vr;
@@ -450,29 +452,33 @@ layernorm_ivit_requant4_kernel(const int8_t* __restrict__ x, long long ldx, int8
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       uint32_t slow = 0;
-      int code[NPL];
+      uint32_t lob[NPL];                  // 1.5 * 2^23 + code as float bits: the code is the low byte
+      const float fh = __fmul_rn(factor[r], 0.5f);                  // fl(y * factor) / 2 == fl(y * (factor / 2)): exact scaling
 #pragma unroll
       for (int i = 0; i < NPL; ++i) {
         const float yf = __fsub_rn(__int_as_float(0x4B400000 + y[r][i]), 12582912.f);
-        float v = floorf(__fmul_rn(__fmul_rn(yf, factor[r]), 0.5f));                            // :52
+        float v = floorf(__fmul_rn(yf, fh));                                                     // :52
         v = __fadd_rn(v, bia[i]);                                                               // :61
-        const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -200.f), 200.f);   // beyond +-130 both paths clamp
+        // clamp(rint(ra), -128, 127) == rint(clamp(ra, -128.4, 127.4)): the code then fits the low byte
+        const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -128.4f), 127.4f);
         const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);   // 1 - 2^-18
         const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);   // 1 + 2^-18
-        slow = slow * 2u + ((__float_as_uint(lo) ^ __float_as_uint(hi)) & 1u);   // consecutive integers differ in bit 0
-        code[i] = __float_as_int(lo) - 0x4B400000;
+        slow |= __float_as_uint(lo) ^ __float_as_uint(hi);                   // consecutive integers differ in bit 0
+        lob[i] = __float_as_uint(lo);
       }
-      if (!fast_ok) slow = 0xffffffffu;
-      if (slow != 0) {
+      if (!fast_ok) slow = 1u;
+      if (slow & 1u) {                      // some element sits within 2^-18 of a rounding tie (~1e-3 of them): exact replay
 #pragma unroll
         for (int i = 0; i < NPL; ++i) {
-          if ((slow >> (NPL - 1 - i)) & 1u) {
-            const int c = 128 * (i >> 2) + 4 * lane + (i & 3);
-            const float yf = static_cast<float>(y[r][i]);
-            float v = floorf(__fmul_rn(__fmul_rn(yf, factor[r]), 0.5f));                        // :52
-            v = __fadd_rn(v, bia[i]);                                                           // :61
-            code[i] = ln_requant_exact(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax);
-          }
+          const int c = 128 * (i >> 2) + 4 * lane + (i & 3);
+          const float yf = static_cast<float>(y[r][i]);
+          float v = floorf(__fmul_rn(__fmul_rn(yf, factor[r]), 0.5f));                          // :52
+          v = __fadd_rn(v, bia[i]);                                                             // :61
+          const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -128.4f), 127.4f);
+          const uint32_t l2 = __float_as_uint(__fmaf_rn(ra, 0.999996185302734375f, 12582912.f));
+          const uint32_t h2 = __float_as_uint(__fmaf_rn(ra, 1.000003814697265625f, 12582912.f));
+          if (((l2 ^ h2) & 1u) || !fast_ok)
+            lob[i] = static_cast<uint32_t>(ln_requant_exact(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax)) & 0xffu;
         }
       }
       if (r < nr) {
@@ -480,7 +486,7 @@ layernorm_ivit_requant4_kernel(const int8_t* __restrict__ x, long long ldx, int8
 #pragma unroll
         for (int j = 0; j < NJ; ++j)
           *reinterpret_cast<uint32_t*>(orow + 128 * j) =
-              pack_sat_s8_ln(code[4 * j + 1], code[4 * j], pack_sat_s8_ln(code[4 * j + 3], code[4 * j + 2], 0u));
+              __byte_perm(__byte_perm(lob[4 * j], lob[4 * j + 1], 0x0040), __byte_perm(lob[4 * j + 2], lob[4 * j + 3], 0x0040), 0x5410);
       }
     }
     __syncwarp();                 // the staged rows are overwritten by the prefetch two iterations on
