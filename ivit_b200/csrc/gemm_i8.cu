@@ -96,6 +96,12 @@ __device__ __forceinline__ uint32_t pack_sat_s8(int a, int b, uint32_t hi16) {
 __device__ __forceinline__ uint32_t pack4_sat_s8(int v0, int v1, int v2, int v3) {
   return pack_sat_s8(v1, v0, pack_sat_s8(v3, v2, 0u));
 }
+// first requant of the channels-on-lanes epilogue: 0 = XOR + DADD + DFMA (default); 1 = I2F.F64 + DFMA -- one FP64 slot
+// less per output, but the conversion pipe (16 lanes / clk / SM) then bounds the epilogue: measured slower
+// (qkv 0.436 -> 0.459 ms, fc1 0.546 -> 0.584 ms per DeiT-S step)
+#ifndef IVIT_CL_I2F
+#define IVIT_CL_I2F 0
+#endif
 constexpr double kMagicInt = 4503601774854144.0;      // 2^52 + 2^31
 constexpr double kMagicRnd = 6755399441055744.0;      // 1.5 * 2^52
 
@@ -724,7 +730,9 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           if (fast) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
-              const double zd = __hiloint2double(0x43300000, static_cast<int>(z[j] ^ 0x80000000u)) - kb;
+              // int32 -> fp64 by I2F.F64 (conversion pipe) + one DFMA, or XOR + DADD + DFMA (two FP64 slots)
+              const double zd = IVIT_CL_I2F ? __int2double_rn(static_cast<int>(z[j]) + bias_now)
+                                            : __hiloint2double(0x43300000, static_cast<int>(z[j] ^ 0x80000000u)) - kb;
               c[j] = __double2loint(__fma_rn(zd, mult, kMagicRnd));
             }
           } else {
