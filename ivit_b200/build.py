@@ -22,7 +22,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "--fmad=false",            # the exact-replay arithmetic must never be contracted into FMAs
     "-I" + os.path.join(ROOT, "include"), "-I" + CSRC,
-]
+] + os.environ.get("IVIT_NVCC_EXTRA", "").split()          # e.g. -DIVIT_ATTN_TIMING for the per-phase clock probe
 
 
 def _newest(paths):

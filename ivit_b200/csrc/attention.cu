@@ -46,6 +46,14 @@ struct AttnArgs {
 
 constexpr int HD = 64;
 
+#ifdef IVIT_ATTN_TIMING
+// debug probe: clock64 deltas between the phases of attention_i8_kernel, summed over CTAs by thread 0
+__device__ unsigned long long g_attn_t[16];
+#define ATTN_STAMP(i) do { if (threadIdx.x == 0) { const long long t_ = clock64(); atomicAdd(&g_attn_t[i], static_cast<unsigned long long>(t_ - t_prev)); t_prev = t_; } } while (0)
+#else
+#define ATTN_STAMP(i) do { } while (0)
+#endif
+
 // exp term of one score, to be summed over the row.  c, cmax: int8 codes of qact_attn1.
 __device__ __forceinline__ float softmax_term(int c, float xmax, const AttnArgs& a) {
   const float xi = x_eff(static_cast<float>(c), a.p.s_attn);       // x / s, un-rounded
@@ -114,6 +122,23 @@ __device__ __forceinline__ void chunk_pipeline(uint32_t t_row, int n, F&& body) 
   }
 }
 
+// for ci in [0, n): body(ci, v), D chunks' tcgen05.ld in flight at once (one wait per D chunks): for the passes whose
+// per-chunk work is far shorter than a TMEM round trip (raw maximum, probability scaling), where the two-deep
+// pipeline above pays one load latency per chunk (the clock probe: 1760 cycles for pass 1 of a 7-chunk row).
+template <int W, int D, class F>
+__device__ __forceinline__ void chunk_batches(uint32_t t_row, int n, F&& body) {
+  uint32_t v[D][W];
+  for (int c0 = 0; c0 < n; c0 += D) {
+#pragma unroll
+    for (int d = 0; d < D; ++d)
+      if (c0 + d < n) tmem_ld_w(t_row + (c0 + d) * 32, v[d]);
+    tmem_ld_wait();
+#pragma unroll
+    for (int d = 0; d < D; ++d)
+      if (c0 + d < n) body(c0 + d, v[d]);
+  }
+}
+
 // CTA = one (image, head, 128-query tile); TPR threads per query row (2 or 4): thread q of a row
 // (warps 4q .. 4q+3) owns columns [32i + q W, 32i + (q+1) W), W = 32 / TPR, of every 32-column
 // chunk.  That split keeps torch's float32 summation order (accumulator e % 32 lives in exactly one
@@ -153,6 +178,9 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = warp >> 2;                  // which of the row's TPR threads
   const int quarter = warp & 3;             // TMEM lane quarter
+  // the TPR threads of a query row sit in warps quarter, quarter + 4, ...: the row-max / row-sum exchanges only
+  // need THOSE warps in step (named barrier 1 + quarter), not the whole CTA
+  auto row_sync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(1 + quarter), "n"(32 * TPR) : "memory"); };
   // grid (image*head, query tile): every full 128-query tile is dispatched before the ragged last
   // tiles (69 of 197 rows), so the short CTAs fill the tail of the launch
   const int mt = blockIdx.y;
@@ -174,8 +202,12 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+#ifdef IVIT_ATTN_TIMING
+  long long t_prev = clock64();
+#endif
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();                   // programmatic dependent launch: qkv is the predecessor's output
+  ATTN_STAMP(0);                 // barrier init, TMEM allocation, first CTA barrier
 
   if (threadIdx.x == 0) {
     mbar_arrive_expect_tx(&bars[0], 128 * HD + a.NKP * HD);
@@ -204,6 +236,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
   // ---------------------------------------------------------------- softmax
   mbar_wait(&bars[2], 0);
+  ATTN_STAMP(1);                 // TMA of Q / K + S MMA latency
   tc_fence_after();
   const int r_loc = quarter * 32 + lane;
   const int row = mt * 128 + r_loc;                     // token index within the image
@@ -221,7 +254,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   // raw maximum), nothing is written back
   int smax = -(1 << 30);
   if (warp_active) {
-    chunk_pipeline<W>(t_row, my_chunks, [&](int ci, uint32_t (&v)[W]) {
+    chunk_batches<W, 64 / W>(t_row, my_chunks, [&](int ci, uint32_t (&v)[W]) {
       if (ci < nfull) {
 #pragma unroll
         for (int j = 0; j < W; ++j) smax = max(smax, static_cast<int>(v[j]));
@@ -233,7 +266,8 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     });
     sMax[q * 128 + r_loc] = smax;
   }
-  __syncthreads();
+  if (TABLE == 2) __syncthreads();      // also publishes the replicated 1-D table written by all warps above
+  else row_sync();
   int cmax = 0;
   float xmax = 0.f;
   const float* trow = nullptr;
@@ -258,6 +292,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     return clampi(requant_i32_cvt(static_cast<int>(sraw), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
   };
 
+  ATTN_STAMP(2);                 // pass 1 (raw maximum) + exchange
   // pass 2: requant -> code -> exp term -> TMEM; float32 row sum in torch's CPU order: accumulator
   // (col % 32) is acc[col % W] of thread (col % 32) / W, fed in ascending column order.
   const int nvec = N / 8, size_ilp = nvec / 4;           // size_ilp == nfull
@@ -329,8 +364,9 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
     for (int j = 0; j < W; ++j) sAcc[(cbase + j) * 128 + r_loc] = acc[j];
   }
+  ATTN_STAMP(3);                 // pass 2 (requant, lookups, sum, TMEM store)
   tc_fence_before();
-  __syncthreads();
+  row_sync();
   tc_fence_after();
   if (warp_active && q == 0) {
     // torch keeps 4 rows of 8 accumulators (e % 32 = 8 k + l): ps[0] (row 0) += left-over whole
@@ -366,8 +402,9 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     // floor(e*factor / 2^k) == floor(e * (factor / 2^k)): scaling by a power of two is exact
     sFac[r_loc] = __fmul_rn(factor, a.out_shift);
   }
-  __syncthreads();
+  row_sync();
 
+  ATTN_STAMP(4);                 // row sums, factor
   // pass 3: probabilities -> u8 operand tile in shared memory (K-major, SWIZZLE_128B)
   if (warp_active) {
     const float fs = sFac[r_loc];
@@ -380,7 +417,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (W == 16) *reinterpret_cast<int4*>(dst) = make_int4(w[0], w[1], w[W / 4 - 2], w[W / 4 - 1]);
       else *reinterpret_cast<uint2*>(dst) = make_uint2(w[0], w[1]);
     };
-    chunk_pipeline<W>(t_row, my_chunks, [&](int ci, uint32_t (&v)[W]) {
+    chunk_batches<W, 48 / W>(t_row, my_chunks, [&](int ci, uint32_t (&v)[W]) {
       uint32_t w[W / 4], wh[W / 4];
       // :175 / :315 (terms past column N were stored as 0).  floor of a value in [0, 2^22) through the 2^23
       // magic constant (round toward zero) instead of F2I (quarter-rate XU pipe); two scores per instruction
@@ -419,6 +456,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   tc_fence_before();
   __syncthreads();
 
+  ATTN_STAMP(5);                 // pass 3 + CTA barrier
   // ---------------------------------------------------------------- O = P V
   if (threadIdx.x == 0) {
     mbar_wait(&bars[1], 0);
@@ -438,6 +476,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   }
   __syncwarp();
   mbar_wait(&bars[3], 0);
+  ATTN_STAMP(6);                 // P.V MMA + commit latency
   tc_fence_after();
   if (warp_active) {
     // O tile: columns [0,64); thread q stores head-dims [q OW, (q+1) OW).  The TMEM load is
@@ -471,6 +510,7 @@ attention_i8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         *reinterpret_cast<int4*>(op + 16 * j) = make_int4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
     }
   }
+  ATTN_STAMP(7);                 // epilogue (TMEM load, requant, store)
   pdl_launch_dependents();      // late: the grid has more CTAs than fit, the successor must not crowd them out
   tc_fence_before();
   __syncthreads();
@@ -861,6 +901,17 @@ extern "C" int ivit_attention_set_threads_per_row(int tpr) {
   if (tpr == 2 || tpr == 4) g_attn_tpr = tpr;
   return prev;
 }
+
+#ifdef IVIT_ATTN_TIMING
+extern "C" int ivit_debug_attn_timing(unsigned long long* out16, int reset) {
+  cudaError_t e = cudaMemcpyFromSymbol(out16, g_attn_t, sizeof(unsigned long long) * 16);
+  if (e == cudaSuccess && reset) {
+    unsigned long long z[16] = {};
+    e = cudaMemcpyToSymbol(g_attn_t, z, sizeof(z));
+  }
+  return static_cast<int>(e);
+}
+#endif
 
 extern "C" int ivit_attention_set_variant(int variant) {
   const int prev = g_attn_variant;
