@@ -276,6 +276,11 @@ typedef struct {
   /* optional int32 [nH, ws*ws, ws*ws]: the identity branch of qact2 evaluated once per layer,
    * rint(float64(bias_codes) * mult_bias) (quant_utils.py:232-245; batch independent).  NULL: per score. */
   const int32_t* bias_terms;
+  /* 0: qkv / out in image token order [B, res*res, .] (roll, partition and reverse are index maps in the kernel).
+   * 1: qkv / out already in window order [B*nW, ws*ws, .], i.e. what WindowAttention.forward itself receives and
+   *    returns (swin_quant.py:121-169) after the caller's torch.roll + window_partition (:258-272); the shift mask is
+   *    still generated from (res, ws, shift).  The module-by-module frozen path uses this form. */
+  int windowed;
 } ivit_window_attention_params_t;
 int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int res, int ws, int shift, int nH,
                              int hd, const ivit_window_attention_params_t* p, void* stream);

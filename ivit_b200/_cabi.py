@@ -70,6 +70,7 @@ class WindowAttentionParams(C.Structure):
         ("exp_table", C.c_void_p),
         ("mask_clamps", C.c_int),
         ("bias_terms", C.c_void_p),
+        ("windowed", C.c_int),
     ]
 
 

@@ -96,7 +96,9 @@ window_attention_i8_kernel(const WinAttnArgs a) {
   if (threadIdx.x < N) {
     const int iy = threadIdx.x / ws, ix = threadIdx.x % ws;
     const int ry = wy * ws + iy, rx = wx * ws + ix;                        // rolled coordinates
-    tok[threadIdx.x] = ((ry + a.shift) % res) * res + (rx + a.shift) % res;
+    // window order (module path: roll + window_partition already applied by the caller): row w * N + i of the image
+    tok[threadIdx.x] = a.p.windowed ? w * N + static_cast<int>(threadIdx.x)
+                                    : ((ry + a.shift) % res) * res + (rx + a.shift) % res;
     lab[threadIdx.x] = 3 * mask_region(ry, res, ws, a.shift) + mask_region(rx, res, ws, a.shift);
   }
   __syncthreads();
@@ -246,7 +248,9 @@ window_attention_tc_kernel(const WinAttnArgs a) {
   if (threadIdx.x < N) {
     const int iy = threadIdx.x / ws, ix = threadIdx.x % ws;
     const int ry = wy * ws + iy, rx = wx * ws + ix;                        // rolled coordinates
-    tok[threadIdx.x] = ((ry + a.shift) % res) * res + (rx + a.shift) % res;
+    // window order (module path: roll + window_partition already applied by the caller): row w * N + i of the image
+    tok[threadIdx.x] = a.p.windowed ? w * N + static_cast<int>(threadIdx.x)
+                                    : ((ry + a.shift) % res) * res + (rx + a.shift) % res;
     lab[threadIdx.x] = 3 * mask_region(ry, res, ws, a.shift) + mask_region(rx, res, ws, a.shift);
   }
   tc_fence_before();

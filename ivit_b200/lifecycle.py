@@ -27,10 +27,10 @@ _FREEZABLE = (_m.QuantAct, _m.QuantLinear, _m.QuantConv2d, _m.QuantMatMul, _m.IV
 class _FusedPlanForward:
     """``model.forward`` of a frozen Swin model: the integer forward as the fused static plan.
 
-    The frozen module path exchanges integer-code carriers between modules and recognises the call
-    patterns of vit_quant.py; swin_quant.py's glue (torch.roll, window partition, the bias gather, the float
-    mask add) has no carrier form, so a frozen ``SwinTransformer`` runs as ``FrozenSwinPlan`` instead: the
-    same kernels, bit-identical logits, built once per device from the model's own ``state_dict``."""
+    The frozen module path carries swin_quant.py's glue too (torch.roll, window partition, the bias gather,
+    the float mask add: ``carrier.py``), but it launches per module and moves the window permutations with copy
+    kernels; ``FrozenSwinPlan`` folds them into index maps of the window-attention kernel.  Same kernels,
+    bit-identical logits (tests/test_swin_gpu.py), built once per device from the model's own ``state_dict``."""
 
     def __init__(self, model: nn.Module):
         self._model = model
@@ -54,21 +54,25 @@ def _is_swin(model: nn.Module) -> bool:
         all(hasattr(st, "blocks") for st in model.layers)
 
 
-def freeze_model(model: nn.Module) -> nn.Module:
+def freeze_model(model: nn.Module, fused_plan: bool = True) -> nn.Module:
     """model_utils.py ``freeze_model``: every module that has ``fix()`` stops updating its running
     statistics; from here on the forward is the integer path.  A Swin model additionally gets its
-    forward routed to the fused plan (see ``_FusedPlanForward``); ``unfreeze_model`` undoes it."""
-    for mod in model.modules():
-        if isinstance(mod, _FREEZABLE) and hasattr(mod, "fix"):
+    forward routed to the fused plan (see ``_FusedPlanForward``, the fast path: ~90 launches instead of
+    one or more per module); ``fused_plan=False`` -- or the reference's own ``freeze_model``, which only
+    calls ``fix()`` -- leaves ``swin_quant.py``'s forward in place and it runs module by module on the
+    integer carriers, bit-identical.  ``unfreeze_model`` undoes either."""
+    model.eval()
+    for mod in model.modules():                 # model_utils.py:13-15: every sub-module that provides fix()
+        if hasattr(mod, "fix") and callable(mod.fix):
             mod.fix()
-    if _is_swin(model):
+    if _is_swin(model) and fused_plan:
         model.__dict__["forward"] = _FusedPlanForward(model)
     return model
 
 
 def unfreeze_model(model: nn.Module) -> nn.Module:
     """model_utils.py ``unfreeze_model``: back to running-stat (calibration / QAT) mode."""
-    for mod in model.modules():
+    for mod in model.modules():                 # (ppoly modules keep their fitted coefficients: model_utils.py:23)
         if isinstance(mod, _FREEZABLE) and hasattr(mod, "unfix"):
             mod.unfix()
     if isinstance(model.__dict__.get("forward"), _FusedPlanForward):

@@ -84,17 +84,33 @@ def _cat_codes(q: QTensor) -> torch.Tensor:
     """int32 codes of a pending cat: carrier parts contribute their codes; raw float parts the integer
     the next QuantAct would recover, round(x / s) (quant_utils.py:220), un-clamped."""
     p = q.pending
-    out = torch.empty(q.canon_shape, dtype=torch.int32, device=q.device)
+    # carriers only (PatchMerging's four strided slices, swin_quant.py:339-344): the codes keep their storage type
+    parts = [t.materialize() if isinstance(t, QTensor) else None for t in p.parts]
+    kinds = {c.dtype for c in parts if c is not None}
+    dtype = kinds.pop() if all(c is not None for c in parts) and len(kinds) == 1 else torch.int32
+    out = torch.empty(q.canon_shape, dtype=dtype, device=q.device)
     off = 0
     s = q.scale
-    for t in p.parts:
+    for t, codes in zip(p.parts, parts):
         n = int(t.shape[p.dim])
         dst = out.narrow(p.dim, off, n)
         if isinstance(t, QTensor):
-            if not np.array_equal(t.hscale, q.hscale):
+            if not np.array_equal(t.hscale, q.hscale) or t.factor != q.factor:
                 raise NotImplementedError("torch.cat of carriers with different scales")
-            dst.copy_(t.materialize())
+            dst.copy_(codes)
         else:
             dst.copy_(torch.round(t.detach().float() / s.view(*([1] * (t.dim() - 1)), -1)))
         off += n
     return out
+
+
+def avgpool1d(x: QTensor, output_size):
+    """nn.AdaptiveAvgPool1d(1) on the [B, C, L] transpose of an int8 token carrier (swin_quant.py:554): deferred, the
+    QuantAct that follows launches ivit_avgpool_requant_i8 (torch's summation order over the tokens)."""
+    one = output_size == 1 or (isinstance(output_size, (tuple, list)) and tuple(output_size) == (1,))
+    if not (one and x.dim() == 3 and x.codes is not None and x.codes.dtype == torch.int8
+            and x.transpose(1, 2).is_canonical()):
+        return torch.nn.functional.adaptive_avg_pool1d(x.dequantize(), output_size)
+    B, Cc, L = (int(v) for v in x.shape)
+    return QTensor(pending=Pending("avgpool", x=x.codes.reshape(B, L, Cc), s_in_h=eff_hscale(x)), canon_shape=(B, Cc, 1),
+                   scale=x.scale, hscale=x.hscale, factor=x.factor, device=x.device)

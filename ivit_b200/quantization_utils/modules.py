@@ -146,9 +146,9 @@ class QuantAct(_FrozenCache, nn.Module):
             raise NotImplementedError("frozen QuantAct: at most 16-bit activations")
         return 16 if self.activation_bit > 8 else 8
 
-    def _wrap(self, codes, shape, device):
+    def _wrap(self, codes, shape, device, layout=0):
         s, h, _ = self._out_scale(device)
-        q = QTensor(codes, scale=s, hscale=h)
+        q = QTensor(codes, scale=s, hscale=h, layout=layout)
         return q.reshape(*shape), s
 
     def _mult(self, key, s_in_h, device):
@@ -195,19 +195,34 @@ class QuantAct(_FrozenCache, nn.Module):
         p = x.pending if x.codes is None else None
         kind = p.kind if p is not None else None
         shape = tuple(x.shape)
+        # memory layout of the reference's result (hazard H11): elementwise ops keep their input's layout, and
+        # fixedpoint_mul adds the identity branch first (quant_utils.py:245), so the identity's layout wins
+        lay = identity.layout if isinstance(identity, QTensor) else x.layout
         if identity is None and kind == "gemm" and x.is_canonical() and self.activation_bit <= 16:
             # QuantLinear / QuantConv2d -> QuantAct: requantisation fused into the GEMM epilogue
             mult, mh = self._mult(("gemm", p.lin["b_scale_h"].tobytes()), p.lin["b_scale_h"], device)   # keyed by value, not id()
             out = ops.gemm(p.A, p.lin["w"], _cabi.EPI_REQUANT, bias=p.lin["bias"], mult=mult, s_in=p.lin["b_scale"],
                            qmin=qmin, qmax=qmax, z_bound_ok=p.lin["z_bound_ok"],
                            force_slow=p.lin["force_slow"] or bool(np.abs(mh).max() >= 256.0), out_bits=self._store_bits())
-            return self._wrap(out, shape, device)
+            return self._wrap(out, shape, device, lay)
         if identity is None and kind == "ln":
-            return self._wrap(p.mod._frozen_ln_requant(p, x, self, device), shape, device)
+            return self._wrap(p.mod._frozen_ln_requant(p, x, self, device), shape, device, lay)
         if identity is None and kind == "gelu":
             return self._wrap(p.mod._frozen_gelu_requant(p, self, device), shape, device)
         if identity is None and kind == "mm2":
             return self._wrap(_frozen_attention(p, x, self, device), shape, device)
+        if identity is None and kind == "avgpool" and self.activation_bit <= 8:
+            # avgpool(x.transpose(1, 2)) -> qact3 (swin_quant.py:554-555): one kernel, torch's summation order
+            _, mh = self._mult(("avgpool", p.s_in_h.tobytes()), p.s_in_h, device)
+            B, L, C = (int(v) for v in p.x.shape)
+            out = ops.avgpool_requant(p.x, B, L, C, float(p.s_in_h[0]), float(mh[0]), qmin, qmax)
+            return self._wrap(out, shape, device)
+        if kind == "qattn" and isinstance(identity, QTensor):
+            # WindowAttention.qact2(attn, s, relative_position_bias, s_table) (swin_quant.py:147): stays symbolic
+            q = QTensor(pending=Pending("qattn_bias", qattn=p, s_in_h=fz.eff_hscale(x), qact=self, identity=identity,
+                                        mask=None), canon_shape=x.canon_shape, scale=s_out, hscale=s_out_h, meta=x.meta,
+                        device=device)
+            return q, s_out
         if identity is None and kind == "mm1":
             # qact_attn1: stays symbolic, the softmax / second matmul / qact2 complete the chain
             q = QTensor(pending=Pending("qattn", mm1=p, s_in_h=fz.eff_hscale(x), qact=self), canon_shape=x.canon_shape,
@@ -236,7 +251,7 @@ class QuantAct(_FrozenCache, nn.Module):
             _, mh = self._mult(("id", fz.eff_hscale(identity).tobytes()), fz.eff_hscale(identity), device)
             mult_id = float(mh[0])
         out = ops.requant(z, s_in_d, mult, qmin, qmax, idc, mult_id, out_bits=self._store_bits())
-        return self._wrap(out, shape, device)
+        return self._wrap(out, shape, device, lay)
 
     def forward(self, x, pre_act_scaling_factor=None, identity=None, identity_scaling_factor=None,
                 specified_min=None, specified_max=None):
@@ -420,8 +435,9 @@ class QuantConv2d(_FrozenCache, nn.Conv2d):
         # canonical storage [B, gh, gw, Cout]; the module's logical output is [B, Cout, gh, gw]
         meta = torch.empty((B, gh, gw, Cout), device="meta", dtype=torch.int8).permute(0, 3, 1, 2)
         scale4 = lin["b_scale"].view(1, -1, 1, 1)
+        # layout: the reference's NCHW result read as [B, L, C] tokens is channel-strided (layers_quant.py:198)
         q = QTensor(pending=Pending("gemm", A=patches, lin=lin), canon_shape=(B, gh, gw, Cout), scale=lin["b_scale"],
-                    hscale=lin["b_scale_h"], meta=meta, device=x.device)
+                    hscale=lin["b_scale_h"], meta=meta, device=x.device, layout=gh * gw)
         return q, scale4
 
 
@@ -487,7 +503,7 @@ class _IntLayerNormBase(_FrozenCache):
                 self.bias_integer = c["bias_int"]
         s_in = fz.eff_hscale(x)
         q = QTensor(pending=Pending("ln", x=x, mod=self, s_in=float(s_in[0])), canon_shape=tuple(x.shape),
-                    scale=c["sf"], hscale=c["sf_h"], device=x.device)
+                    scale=c["sf"], hscale=c["sf_h"], device=x.device, layout=x.layout)
         return q, c["sf"]
 
     def _frozen_ln_requant(self, p, view: QTensor, qact: "QuantAct", device):
@@ -506,8 +522,18 @@ class _IntLayerNormBase(_FrozenCache):
             rows2 = rows.contiguous().reshape(-1, C)
         mult, _ = qact._mult(("ln", id(self)), c["sf_h"], device)
         _, _, (qmin, qmax) = qact._out_scale(device)
+        if p.x.layout:
+            # the reference's input is channel-strided (Swin stage 0, hazard H11): outer-reduction summation order
+            if self._kind != 0 or not view.is_canonical() or rows.dim() != 3 or int(rows.shape[-2]) != p.x.layout:
+                raise NotImplementedError("IntLayerNorm on a channel-strided carrier: ivit LayerNorm over whole [B, L, C]")
+            return ops.layernorm_requant_strided(0, rows.reshape(-1, C), p.x.layout, p.s_in, c["bias_int"], c["sf"], mult,
+                                                 qmin, qmax)
         shift = float(self.shift.item()) if self._kind == 1 and "shift_h" not in c else c.get("shift_h", 0.0)
         c["shift_h"] = shift
+        if rows2.dtype == torch.int8 and C not in (96, 128, 192, 384, 768, 1024):
+            # the int8 row kernel is specialised per width; other widths (Swin-B stage 1: 256, a merged 512) take
+            # the 16-bit-code kernel, same integer arithmetic on widened codes (what FrozenSwinPlan's stream does)
+            rows2 = rows2.to(torch.int16)
         return ops.layernorm_requant(self._kind, rows2, p.s_in, c["bias_int"], c["sf"], mult, qmin, qmax, shift=shift,
                                      use_int_sqrt=bool(getattr(self, "use_int_sqrt", False)))
 
@@ -700,8 +726,9 @@ class _IntSoftmaxBase(_FrozenCache):
     def _frozen_forward(self, x: QTensor):
         """Deferred: the softmax is computed on the score tile inside the attention kernel."""
         fz.require_cuda(x, type(self).__name__)
-        if x.codes is not None or x.pending.kind != "qattn":
-            raise NotImplementedError("frozen IntSoftmax outside the attention chain of vit_quant.py:72-82")
+        if x.codes is not None or x.pending.kind not in ("qattn", "qattn_bias"):
+            raise NotImplementedError("frozen IntSoftmax outside the attention chains of vit_quant.py:72-82 / "
+                                      "swin_quant.py:131-156")
         if not 2 <= self.output_bit <= 16:
             raise NotImplementedError("frozen IntSoftmax: output_bit in [2, 16]")
         c = self._fz_get()
@@ -778,6 +805,8 @@ def _frozen_attention(p, view: QTensor, qact2: QuantAct, device):
     -> matmul_2(attn, v) -> transpose/reshape -> qact2  ==>  ivit_attention_i8 on the qkv buffer."""
     sm, v = p.P, p.v
     qattn = sm.qattn
+    if qattn.kind == "qattn_bias":
+        return _frozen_window_attention(p, view, qact2, device)
     mm1 = qattn.mm1
     q, kT = mm1.a, mm1.b
     base = q.codes
@@ -818,3 +847,92 @@ def _frozen_attention(p, view: QTensor, qact2: QuantAct, device):
         cache[key] = (a, table)
     a, _ = cache[key]
     return ops.attention(base.reshape(B, N, 3 * C), B, N, H, hd, a)
+
+
+def _frozen_window_attention(p, view: QTensor, qact3: QuantAct, device):
+    """swin_quant.py:131-160 recognised as one unit: matmul_1(q, k^T) * scale -> qact_attn1 -> qact2 with the
+    gathered relative-position-bias codes as identity -> (+ shifted-window mask) -> IntSoftmax -> matmul_2(attn, v)
+    -> transpose/reshape -> qact3  ==>  ivit_window_attention_i8 in window order (the caller has already rolled and
+    partitioned the tokens: swin_quant.py:258-272)."""
+    from ..swin_plan import mask_always_clamps, shift_window_mask
+    sm, v = p.P, p.v
+    chain = sm.qattn                       # qact2 + identity (+ mask)
+    qattn = chain.qattn                    # qact_attn1
+    mm1 = qattn.mm1
+    q, kT = mm1.a, mm1.b
+    base = q.codes
+    if base is None or kT.codes is not base or v.codes is not base or base.dtype != torch.int8:
+        raise NotImplementedError("QuantMatMul operands must be slices of one int8 qkv carrier (swin_quant.py:127-129)")
+    Bw, H, N, hd = (int(s) for s in q.shape)
+    C = H * hd
+    want = torch.empty((Bw, N, 3, H, hd), device="meta", dtype=torch.int8).permute(2, 0, 3, 1, 4)
+
+    def same(mt, ref):
+        return tuple(mt.shape) == tuple(ref.shape) and tuple(mt.stride()) == tuple(ref.stride()) and \
+            mt.storage_offset() == ref.storage_offset()
+    if not (same(q.meta, want[0]) and same(kT.meta, want[1].transpose(-2, -1)) and same(v.meta, want[2])):
+        raise NotImplementedError("QuantMatMul operand layout differs from qkv.reshape(B_,N,3,H,hd).permute(2,0,3,1,4)")
+    if not view.is_canonical():
+        raise NotImplementedError("window attention output must be consumed as x.transpose(1,2).reshape(B_,N,C)")
+    if sm.mod._kind != 0:
+        raise NotImplementedError("frozen window attention: the ivit softmax only (swin_quant.py:11 imports no other)")
+    ws = int(round(N ** 0.5))
+    if ws * ws != N:
+        raise NotImplementedError("window attention: square windows")
+    # geometry: without a mask every window is independent (one window per 'image'); with one, the mask must be the
+    # shifted-window mask of (res, ws, ws // 2) -- checked once per mask tensor against the reference construction
+    B, res, shift = Bw, ws, 0
+    mask = chain.mask
+    cache = qact3._fz_get()
+    if mask is not None:
+        nW = mask.numel() // (N * N) if tuple(mask.shape[-2:]) == (N, N) else 0    # [1, nW, 1, N, N] at the add (:150)
+        n = int(round(nW ** 0.5))
+        if n * n != nW or nW == 0 or Bw % nW:
+            raise NotImplementedError("window attention mask: [nW, N, N] with a square number of windows")
+        res, shift, B = n * ws, ws // 2, Bw // nW
+        mkey = ("mask_ok", mask.data_ptr(), tuple(mask.shape), mask._version)
+        if mkey not in cache:
+            want_mask = torch.from_numpy(shift_window_mask(res, ws, shift)).to(mask.device)
+            cache[mkey] = bool(torch.equal(mask.detach().float().reshape(nW, N, N), want_mask))
+        if not cache[mkey]:
+            raise NotImplementedError("window attention mask differs from SwinTransformerBlock's 0 / -100 shifted-window "
+                                      "mask for shift = window_size // 2 (swin_quant.py:223-247)")
+    ident = chain.identity
+    bias = ident.materialize()
+    if bias.dtype != torch.int8 or tuple(bias.shape)[-3:] != (H, N, N) or bias.numel() != H * N * N:
+        raise NotImplementedError("qact2 identity must be the int8 bias codes [1, nH, N, N] (swin_quant.py:142-147)")
+    key = ("wattn", id(sm.mod), id(chain.qact), id(qattn.qact))
+    s_tab_h = fz.eff_hscale(ident)
+    if key in cache and not np.array_equal(cache[key][2], s_tab_h):
+        cache.pop(key)
+    if key not in cache:
+        a = _cabi.WindowAttentionParams()
+        _, s_a1_h, (lo, hi) = qattn.qact._out_scale(device)
+        a.mult_attn = float(hm.dyadic_mult(qattn.s_in_h, s_a1_h).reshape(-1)[0])
+        a.qmin_attn, a.qmax_attn = lo, hi
+        _, s2_h, (lo2, hi2) = chain.qact._out_scale(device)
+        a.mult2 = float(hm.dyadic_mult(s_a1_h, s2_h).reshape(-1)[0])
+        a.mult_bias = float(hm.dyadic_mult(s_tab_h, s2_h).reshape(-1)[0])
+        a.qmin2, a.qmax2 = lo2, hi2
+        a.s2 = float(s2_h[0])
+        a.output_bit = int(sm.mod.output_bit)
+        a.mask_clamps = int(mask_always_clamps(s2_h[0], lo2, hi2))
+        keep = []
+        if -128 <= lo2 and hi2 <= 127:
+            tp = _cabi.AttentionParams()
+            tp.kind, tp.output_bit, tp.s_attn = 0, int(sm.mod.output_bit), float(s2_h[0])
+            keep.append(ops.softmax_table_build(tp, device, collapse=False))
+            a.exp_table = tp.exp_table
+        _, s3_h, (lo3, hi3) = qact3._out_scale(device)
+        a.mult_out = float(hm.dyadic_mult(p.s_h, s3_h).reshape(-1)[0])
+        a.qmin_out, a.qmax_out = lo3, hi3
+        a.windowed = 1
+        cache[key] = (a, keep, s_tab_h.copy())
+    a = cache[key][0]
+    if qact3.activation_bit > 8 or not 2 <= int(sm.mod.output_bit) <= 8:
+        raise NotImplementedError("frozen window attention: 8-bit qact3 and softmax output (swin_quant.py:108-109)")
+    bias = bias.contiguous()
+    a.bias_codes = bias.data_ptr()                       # re-gathered by the caller every forward: pass this call's codes
+    a.bias_terms = None
+    out = ops.window_attention(base.reshape(B, res * res, 3 * C), B, res, ws, shift, H, hd, a)
+    return out.reshape(Bw, N, C)

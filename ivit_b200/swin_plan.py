@@ -47,6 +47,16 @@ def relative_position_index(ws: int) -> np.ndarray:
     return rel.sum(-1)
 
 
+def shift_window_mask(res: int, ws: int, shift: int) -> np.ndarray:
+    """float32 [nW, ws*ws, ws*ws] of 0 / -100: SwinTransformerBlock.attn_mask (swin_quant.py:223-247) -- region labels
+    of the rolled image (three bands per axis), partitioned into windows; pairs from different regions get -100."""
+    band = np.where(np.arange(res) < res - ws, 0, np.where(np.arange(res) < res - shift, 1, 2))
+    lab = 3 * band[:, None] + band[None, :]
+    n = res // ws
+    mw = lab.reshape(n, ws, n, ws).transpose(0, 2, 1, 3).reshape(n * n, ws * ws)
+    return np.where(mw[:, None, :] != mw[:, :, None], f32(-100.0), f32(0.0)).astype(f32)
+
+
 def mask_always_clamps(s2, qmin2: int, qmax2: int) -> bool:
     """float32 restatement of the kernel's masked score: x = fl(fl(c s) - 100) / s against the smallest
     possible row maximum fl(fl(qmin s) / s); int_exp_shift (ivit_modules.py:150-162) clamps at 15 x0."""

@@ -9,6 +9,7 @@ import pytest
 import torch
 
 import ivit_b200.quantization_utils as qu
+from ivit_b200 import _cabi
 from ivit_b200._cabi import IvitKernelError
 from ivit_b200.synthetic import load_case, synth_images
 
@@ -145,6 +146,70 @@ def test_reference_swin_quant_runs_unchanged_and_calibrates_identically():
     want = FrozenSwinPlan(cfg, state, host_only=True)
     assert plan.pool_mult == want.pool_mult and plan.stages[1]["blocks"][1]["proj"].mult2 == \
         want.stages[1]["blocks"][1]["proj"].mult2
+
+
+def _expect_swin_toy_launches(calls, B):
+    """swin_toy: 14x14 tokens, 2 + 2 blocks, 7x7 windows (block 1 of stage 0 shifted and masked), one PatchMerging."""
+    from collections import Counter
+    n = Counter(c.split(":")[0] for c in calls)
+    assert n["window_attention"] == 4 and n["gelu"] == 4 and n["avgpool"] == 1 and n["quantize_patches"] == 1
+    assert n["ln_strided"] == 5 and n["ln"] == 6          # stage 0 (and the stem) channel-strided in the reference: H11
+    wa = [c for c in calls if c.startswith("window_attention")]
+    assert wa[0] == f"window_attention:B={4 * B}:res=7:ws=7:shift=0:nH=3:windowed=1"      # every window on its own
+    assert wa[1] == f"window_attention:B={B}:res=14:ws=7:shift=3:nH=3:windowed=1"         # mask checked, geometry kept
+    assert wa[2] == wa[3] == f"window_attention:B={B}:res=7:ws=7:shift=0:nH=6:windowed=1"
+    assert f"gemm:{_cabi.EPI_LOGITS}" == calls[-1]
+
+
+def test_frozen_swin_forward_walks_the_carrier(monkeypatch):
+    """Row a16, host logic (no GPU, nothing computed: tests/kernel_stubs.py): a frozen swin_quant-style forward stays
+    on integer carriers through torch.roll, window_partition / window_reverse, the bias gather, the mask add,
+    PatchMerging and the average pool, and maps to the expected launches."""
+    import kernel_stubs
+    from ivit_b200 import lifecycle
+    from ivit_b200.synthetic import load_swin_case
+    from swin_caller import SwinTransformer
+    cfg, state, _ = load_swin_case("swin_toy")
+    model = SwinTransformer(cfg)
+    lifecycle.load_checkpoint(model, {"model": {k: torch.as_tensor(v) for k, v in state.items()}})
+    lifecycle.freeze_model(model, fused_plan=False)
+    calls = kernel_stubs.install(monkeypatch)
+    with torch.no_grad():
+        out = model(synth_images(2, cfg, seed=0))
+        assert isinstance(out, qu.QTensor) and tuple(out.shape) == (2, cfg.num_classes)
+        assert out.dequantize().shape == (2, cfg.num_classes)
+    _expect_swin_toy_launches(calls, 2)
+    # a mask that is not the shifted-window mask is refused, not silently replaced
+    model.layers[0].blocks[1].attn_mask = model.layers[0].blocks[1].attn_mask * 0.5
+    with torch.no_grad(), pytest.raises(NotImplementedError):
+        model(synth_images(2, cfg, seed=0))
+
+
+@pytest.mark.reference
+def test_reference_swin_quant_frozen_forward_walks_the_carrier(monkeypatch):
+    """The same walk under the reference's UNMODIFIED swin_quant.py, frozen by the reference's own freeze_model."""
+    import kernel_stubs
+    from functools import partial
+    from ivit_b200 import lifecycle
+    from ivit_b200.synthetic import load_swin_case
+    from oracle.ref_shim import load_reference_swin_on
+    sw = load_reference_swin_on(qu)
+    cfg, state, _ = load_swin_case("swin_toy")
+    model = sw.SwinTransformer(img_size=cfg.img_size, patch_size=cfg.patch_size, in_chans=cfg.in_chans,
+                               num_classes=cfg.num_classes, embed_dim=cfg.embed_dim, depths=cfg.depths,
+                               num_heads=cfg.num_heads, window_size=cfg.window_size, mlp_ratio=float(cfg.mlp_ratio),
+                               norm_layer=partial(qu.IntLayerNorm, eps=1e-6))
+    lifecycle.load_checkpoint(model, {"model": {k: torch.as_tensor(v) for k, v in state.items()}})
+    model.eval()
+    for m in model.modules():                   # model_utils.py:13-15
+        if hasattr(m, "fix") and callable(m.fix):
+            m.fix()
+    calls = kernel_stubs.install(monkeypatch)
+    with torch.no_grad():
+        out = model(synth_images(3, cfg, seed=0))
+    assert isinstance(out, qu.QTensor) and tuple(out.shape) == (3, cfg.num_classes)
+    out.dequantize()
+    _expect_swin_toy_launches(calls, 3)
 
 
 def test_swin_caller_calibrates_to_the_reference_ranges():

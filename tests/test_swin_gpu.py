@@ -296,3 +296,52 @@ def test_layernorm_strided_order(C, tokens, bits):
                                         dev(p["sf"], torch.float32), dev(mult, torch.float64), -128, 127).cpu().numpy()
     assert np.array_equal(got.astype(np.int64), codes.reshape(B * tokens, C).astype(np.int64))
     assert not np.array_equal(y, y_in) or bits == 8     # the two orders really differ on this input
+
+
+@pytest.mark.parametrize("case,batch", [("swin_toy", 2), ("swin_toy_w4", 3), ("swin_toy_b", 2), ("swin_tiny", 1)])
+def test_frozen_module_path_runs_swin_glue_on_the_carrier(case, batch):
+    """Row a16: with only fix() called (the reference's own freeze_model), the caller's forward runs module by module on
+    integer carriers -- torch.roll, window_partition / window_reverse, the bias gather, the mask add, PatchMerging's
+    slices + cat and the token average pool included (swin_quant.py:18-50, :140-153, :258-289, :339-345, :554).  Every
+    QuantAct output against the oracle's tap of the same name, logits against the oracle and the fused plan."""
+    from ivit_b200 import lifecycle
+    from ivit_b200.quantization_utils import QTensor
+    from swin_caller import SwinTransformer
+    cfg, state, fix = load_swin_case(case)
+    model = SwinTransformer(cfg)
+    lifecycle.load_checkpoint(model, {"model": {k: torch.as_tensor(v) for k, v in state.items()}})
+    model.cuda().eval()
+    lifecycle.freeze_model(model, fused_plan=False)
+    assert "forward" not in model.__dict__
+    taps = {}
+
+    def hook(name):
+        def f(mod, inp, out):
+            if isinstance(out, tuple) and isinstance(out[0], QTensor) and out[0].codes is not None:
+                taps[name] = out[0].materialize().cpu().numpy().astype(np.int64)
+        return f
+    for name, mod in model.named_modules():
+        if type(mod).__name__ == "QuantAct":
+            mod.register_forward_hook(hook(name))
+    x = synth_images(batch, cfg, seed=0)
+    with torch.no_grad():
+        out = model(x.cuda())
+        assert isinstance(out, QTensor)
+        logits = out.dequantize().cpu().numpy()
+        again = model(x.cuda()).float().cpu().numpy()          # cached constants
+    o = SO.SwinOracle(cfg, state)
+    exp = o.forward(x.numpy(), record=True)
+    bad, seen = [], 0
+    for name, got in taps.items():
+        if name not in o.taps:
+            continue
+        want = SO.codes_of(o.taps[name]).astype(np.int64)
+        if want.size != got.size:
+            continue                                            # qact_table: the oracle taps the gathered bias
+        seen += 1
+        if not np.array_equal(got.reshape(-1), want.reshape(-1)):
+            bad.append(f"{name}: {(got.reshape(-1) != want.reshape(-1)).sum()}/{got.size}")
+    assert seen >= 30 and not bad, (seen, bad[:12])
+    assert np.array_equal(logits, exp) and np.array_equal(again, exp)
+    plan = FrozenSwinPlan(cfg, state, "cuda")
+    assert np.array_equal(plan.forward(x.cuda()).cpu().numpy(), logits)
