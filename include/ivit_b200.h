@@ -60,8 +60,15 @@ int ivit_layernorm_requant_i8(int kind, const int8_t* x, int64_t ldx, int8_t* ou
                               const float* bias_int, const float* sf, const double* mult, int qmin, int qmax,
                               float shift, int use_int_sqrt, void* stream);
 /* Two kernels for kind 0: packed lanes (C % 128 == 0, default) and strided lanes (any supported C).
- * variant 0 = choose per call, 1 = always the second.  Returns the previous setting.  Process-wide. */
+ * variant 0 = choose per call, 1 = always the second.  Returns the previous setting.  Process-wide.
+ * The 16-bit entry points below follow the same switch: 0 = the restructured kernels (x/s as two fused operations on
+ * 1/s, taken only for scales the library has checked against the IEEE quotient over every code), 1 = always the
+ * division kernels.  For A/B timing and tests. */
 int ivit_layernorm_set_variant(int variant);
+/* The check behind that choice, host arithmetic only (no GPU needed): 1 if, for scale s and EVERY code of the given
+ * width (8 or 16 bits), c + fma(-c, s, r) * (1/s) with r = fl(q s), c = fl(r (1/s)) equals the IEEE quotient r / s --
+ * the reference's `x / scaling_factor` on the float carrier (ivit_modules.py:36).  Cached per (s, bits). */
+int ivit_xeff_fma_ok(float s, int bits);
 
 /* ---- GELU (+ mlp.qact1) as a per-layer table --------------------------------------------
  * kind 0: ivit_modules.py:89-126 (ShiftGELU, n = 23, output_bit), kind 1:
@@ -284,8 +291,10 @@ typedef struct {
 } ivit_window_attention_params_t;
 int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int res, int ws, int shift, int nH,
                              int hd, const ivit_window_attention_params_t* p, void* stream);
-/* Two kernels: the products on tcgen05 (head_dim 32, default) or on dp4a (any head_dim % 4 == 0).  variant 0 =
- * choose per call, 1 = always dp4a.  Returns the previous setting.  Process-wide; for A/B timing and tests. */
+/* Three kernels: thread-per-row with two (window, head) units per CTA (7x7 windows, head_dim 32, tabulated exp term:
+ * the default where it applies), CTA per unit with the products on tcgen05 (head_dim 32), CTA per unit on dp4a (any
+ * head_dim % 4 == 0).  variant 0 = choose per call, 1 = always dp4a, 2 = never the thread-per-row kernel.  Returns the
+ * previous setting.  Process-wide; for A/B timing and tests. */
 int ivit_window_attention_set_variant(int variant);
 /* PatchMerging.forward's strided slices + cat (:339-344): [B, res, res, C] -> [B, (res/2)^2, 4C]. */
 int ivit_patch_merge_gather(const void* x, void* out, int elem_bits, int B, int res, int C, void* stream);

@@ -79,6 +79,7 @@ _SIGS = {
     "ivit_set_pdl": (C.c_int, [C.c_int]),
     "ivit_device_sm": (C.c_int, [C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "ivit_last_error": (C.c_char_p, []),
+    "ivit_xeff_fma_ok": (C.c_int, [C.c_float, C.c_int]),
     "ivit_quantize_f32_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_int64, C.c_void_p]),
     "ivit_quantize_patches_f32_i8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_int,
                                                C.c_int, C.c_int, C.c_void_p]),

@@ -787,6 +787,9 @@ extern "C" int ivit_set_pdl(int on) {
 }
 
 static int g_ln_variant = 0;
+namespace ivit {
+int ln_variant() { return g_ln_variant; }
+}
 extern "C" int ivit_layernorm_set_variant(int variant) {
   const int prev = g_ln_variant;
   g_ln_variant = variant;

@@ -10,12 +10,18 @@
 // EVERY row (not just exact ties), and |y| exceeds 46340, so the int32 square wraps (hazard H9)
 // exactly as `y_int ** 2` does in the reference.  One warp per row; lane t owns elements 32 i + t
 // (torch's accumulator layout, intmath.cuh TorchSum32).
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <unordered_map>
+
 #include "intmath.cuh"
 #include "ivit_b200.h"
 
 namespace ivit {
 int fail(int code, const char* msg);
 int check_launch(const char* what);
+int ln_variant();          // ivit_layernorm_set_variant (rowwise.cu)
 
 // exact replay of the QuantAct behind the LayerNorm for one element (quant_utils.py:220-251)
 __device__ __noinline__ int ln16_requant(float v, float sc, double mult, int qmin, int qmax) {
@@ -295,6 +301,376 @@ layernorm96_strided_kernel(const XT* __restrict__ x, long long ldx, int8_t* __re
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Round 2: the I-ViT kind again, restructured like rowwise.cu's int8 kernel.  Same arithmetic, fewer
+// instructions per element:
+//   * x/s as c = fl(r inv_s), c' = fma(fma(-c, s, r), inv_s, c) with r = fl(q s), inv_s = fl(1/s): three FMA-pipe
+//     operations instead of the IEEE division sequence.  It is used only when the HOST has checked, for this s and
+//     EVERY code of the input width, that c' equals the IEEE quotient (xeff_fma_ok below: same IEEE arithmetic on
+//     the host cores, cached per scale); otherwise the kernels above run.
+//   * R rows in flight per warp; the per-row scalar work (mean division, the ten Newton steps of :45-49, the
+//     2^31 / std division) runs once with row r on lane r, and the Newton loop stops as soon as every lane has
+//     reached a fixed point (further steps would return the same value).
+//   * the QuantAct tail of rowwise.cu: fl(y factor) / 2 == fl(y (factor / 2)); clamp before rounding; the near-tie
+//     test as two FMAs whose roundings must agree; the code is the low byte of the magic-number sum.
+__device__ __forceinline__ float x_eff_fma(float q, float s, float inv_s) {
+  const float r = __fmul_rn(q, s);
+  const float c = __fmul_rn(r, inv_s);
+  return __fmaf_rn(__fmaf_rn(-c, s, r), inv_s, c);
+}
+
+// ten steps of k <- floor((k + floor(v / k)) / 2) from 2^16 (ivit_modules.py:45-49), then floor(2^31 / k) (:51)
+__device__ __forceinline__ float ivit_std_factor(float var_f) {
+  float k = 65536.f;
+#pragma unroll 1
+  for (int it = 0; it < 10; ++it) {
+    const float kn = floorf(__fmul_rn(__fadd_rn(k, floorf(__fdiv_rn(var_f, k))), 0.5f));
+    const bool same = kn == k;                  // fixed point: every later step returns k again (NaN never matches)
+    k = kn;
+    if (__all_sync(0xffffffffu, same)) break;
+  }
+  return floorf(__fdiv_rn(2147483648.f, k));
+}
+
+template <int NPL, int R, typename XT, int MINB>
+__global__ void __launch_bounds__(256, MINB)
+layernorm16_ivit_kernel(const XT* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows, float s_in,
+                        float inv_s, const float* __restrict__ bias_int, const float* __restrict__ sf,
+                        const double* __restrict__ mult, int qmin, int qmax) {
+  constexpr int C = NPL * 32;
+  constexpr int VPR = C / 16;
+  __shared__ __align__(16) int8_t stage[8][R][C];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float bia[NPL], mf[NPL];
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) {
+    bia[i] = __ldg(bias_int + 32 * i + lane);
+    mf[i] = static_cast<float>(__ldg(mult + 32 * i + lane));
+  }
+  const bool fast_ok = qmin == -128 && qmax == 127;
+  const int ngroups = (rows + R - 1) / R;
+  for (int g = blockIdx.x * 8 + warp; g < ngroups; g += gridDim.x * 8) {
+    const int row0 = g * R;
+    const int nr = min(R, rows - row0);
+    int y[R][NPL];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const XT* xr = x + static_cast<long long>(row0 + min(r, nr - 1)) * ldx + lane;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) y[r][i] = static_cast<int>(__ldg(xr + 32 * i));
+    }
+    float sum_l = 0.f;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      TorchSum32 acc;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        const float xe = x_eff_fma(static_cast<float>(y[r][i]), s_in, inv_s);     // ivit_modules.py:36
+        acc.add(xe);
+        y[r][i] = static_cast<int>(xe);                                          // :38 trunc
+      }
+      const float sr = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+      sum_l = (lane == r) ? sr : sum_l;
+    }
+    const int mean_l = static_cast<int>(rintf(__fdiv_rn(sum_l, static_cast<float>(C))));   // :37, row r on lane r
+    long long var_l = 1ll << 32;              // lanes without a row: 2^16 is a fixed point at once (early exit)
+    int mean_r[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int mean = mean_r[r] = __shfl_sync(0xffffffffu, mean_l, r);
+      long long var = 0;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        y[r][i] -= mean;                                                          // :40
+        const int sq = static_cast<int>(static_cast<uint32_t>(y[r][i]) * static_cast<uint32_t>(y[r][i]));   // :41 wraps (H9)
+        var += static_cast<long long>(sq);                                        // :42
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) var += __shfl_xor_sync(0xffffffffu, var, o);
+      var_l = (lane == r) ? var : var_l;
+    }
+    const float fct_l = ivit_std_factor(static_cast<float>(var_l));
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float fh = __fmul_rn(__shfl_sync(0xffffffffu, fct_l, r), 0.5f);
+      uint32_t slow = 0;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        const float yf = __fsub_rn(__int_as_float(0x4B400000 + y[r][i]), 12582912.f);     // |y| < 2^17: exact
+        float v = floorf(__fmul_rn(yf, fh));                                      // :52
+        v = __fadd_rn(v, bia[i]);                                                 // :61
+        const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -128.4f), 127.4f);
+        const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);        // 1 - 2^-18
+        const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);        // 1 + 2^-18
+        slow |= __float_as_uint(lo) ^ __float_as_uint(hi);
+        stage[warp][r][32 * i + lane] = static_cast<int8_t>(__float_as_uint(lo));
+      }
+      if (!fast_ok) slow = 1u;
+      if (slow & 1u) {                        // some element within 2^-18 of a rounding tie: exact replay of those
+        // (rolled loop over re-read codes: indexing y[][] dynamically would push it to local memory)
+        const XT* xr = x + static_cast<long long>(row0 + min(r, nr - 1)) * ldx + lane;
+        const int mean = mean_r[r];
+#pragma unroll 1
+        for (int i = 0; i < NPL; ++i) {
+          const int c = 32 * i + lane;
+          const float xe = x_eff_fma(static_cast<float>(static_cast<int>(__ldg(xr + 32 * i))), s_in, inv_s);
+          const float yf = static_cast<float>(static_cast<int>(xe) - mean);
+          float v = floorf(__fmul_rn(yf, fh));
+          v = __fadd_rn(v, __ldg(bias_int + c));
+          const float ra = fminf(fmaxf(__fmul_rn(v, static_cast<float>(__ldg(mult + c))), -128.4f), 127.4f);
+          const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);
+          const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);
+          if (!fast_ok || ((__float_as_uint(lo) ^ __float_as_uint(hi)) & 1u))
+            stage[warp][r][c] = static_cast<int8_t>(ln16_requant(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax));
+        }
+      }
+    }
+    __syncwarp();
+    for (int v = lane; v < R * VPR; v += 32) {
+      const int r = v / VPR, vv = v - r * VPR;
+      if (r < nr)
+        *reinterpret_cast<int4*>(out + static_cast<long long>(row0 + r) * C + vv * 16) =
+            *reinterpret_cast<const int4*>(&stage[warp][r][vv * 16]);
+    }
+    __syncwarp();
+  }
+}
+
+// The I-BERT kind (ibert_modules.py:112-158) in the same shape: y stays a float (x/s - mean, :131), the variance is a
+// second float32 row sum in torch's order over floor(y / 2^shift)^2 (:132-134), the standard deviation one square
+// root (or the four integer Newton steps of :85-109) -- evaluated with row r on lane r.
+template <int NPL, int R, typename XT, int MINB>
+__global__ void __launch_bounds__(256, MINB)
+layernorm16_ibert_kernel(const XT* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows, float s_in,
+                         float inv_s, const float* __restrict__ bias_int, const float* __restrict__ sf,
+                         const double* __restrict__ mult, int qmin, int qmax, float shift_pow, float inv_shift_pow,
+                         int use_int_sqrt) {
+  constexpr int C = NPL * 32;
+  constexpr int VPR = C / 16;
+  __shared__ __align__(16) int8_t stage[8][R][C];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float bia[NPL], mf[NPL];
+#pragma unroll
+  for (int i = 0; i < NPL; ++i) {
+    bia[i] = __ldg(bias_int + 32 * i + lane);
+    mf[i] = static_cast<float>(__ldg(mult + 32 * i + lane));
+  }
+  const bool fast_ok = qmin == -128 && qmax == 127;
+  const int ngroups = (rows + R - 1) / R;
+  for (int g = blockIdx.x * 8 + warp; g < ngroups; g += gridDim.x * 8) {
+    const int row0 = g * R;
+    const int nr = min(R, rows - row0);
+    float y[R][NPL];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const XT* xr = x + static_cast<long long>(row0 + min(r, nr - 1)) * ldx + lane;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) y[r][i] = static_cast<float>(static_cast<int>(__ldg(xr + 32 * i)));
+    }
+    float sum_l = 0.f;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      TorchSum32 acc;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        y[r][i] = x_eff_fma(y[r][i], s_in, inv_s);                               // ibert_modules.py:129
+        acc.add(y[r][i]);
+      }
+      const float sr = torch_sum_finish(acc.level_sum(), 0.f, nullptr, 0, lane);
+      sum_l = (lane == r) ? sr : sum_l;
+    }
+    const float mean_l = rintf(__fdiv_rn(sum_l, static_cast<float>(C)));          // :130, row r on lane r
+    float var_l = 0.f;
+    float mean_r[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float mean = mean_r[r] = __shfl_sync(0xffffffffu, mean_l, r);
+      TorchSum32 vacc;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        y[r][i] = __fsub_rn(y[r][i], mean);                                       // :131
+        const float ys = floorf(__fmul_rn(y[r][i], inv_shift_pow));               // :132
+        vacc.add(__fmul_rn(ys, ys));                                              // :133
+      }
+      const float vr = torch_sum_finish(vacc.level_sum(), 0.f, nullptr, 0, lane); // :134
+      var_l = (lane == r) ? vr : var_l;
+    }
+    float std_l;
+    if (use_int_sqrt) {                                                           // :85-109
+      const float n = fmaxf(var_l, 0.f);
+      const float bits = floorf(log2f(fmaxf(n, 1.f))) + 1.f;
+      float xk = pow2i(static_cast<int>(ceilf(__fmul_rn(bits, 0.5f))));
+      for (int it = 0; it < 4; ++it) {
+        const float inv = floorf(__fdiv_rn(n, fmaxf(xk, 1.f)));
+        xk = floorf(__fmul_rn(__fadd_rn(xk, inv), 0.5f));
+      }
+      std_l = (var_l > 0.f) ? xk : 0.f;
+    } else {
+      std_l = floorf(__fsqrt_rn(var_l));                                          // :145
+    }
+    std_l = __fmul_rn(std_l, shift_pow);
+    const float fct_l = floorf(__fdiv_rn(2147483648.f, std_l));                   // :146 (2^31)
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float fh = __fmul_rn(__shfl_sync(0xffffffffu, fct_l, r), 0.5f);
+      uint32_t slow = 0;
+#pragma unroll
+      for (int i = 0; i < NPL; ++i) {
+        float v = floorf(__fmul_rn(y[r][i], fh));                                 // :147
+        v = __fadd_rn(v, bia[i]);                                                 // :154
+        const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -128.4f), 127.4f);
+        const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);        // 1 - 2^-18
+        const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);        // 1 + 2^-18
+        slow |= __float_as_uint(lo) ^ __float_as_uint(hi);
+        stage[warp][r][32 * i + lane] = static_cast<int8_t>(__float_as_uint(lo));
+      }
+      if (!fast_ok) slow = 1u;
+      if (slow & 1u) {                        // near a rounding tie: exact replay (rolled loop over re-read codes)
+        const XT* xr = x + static_cast<long long>(row0 + min(r, nr - 1)) * ldx + lane;
+        const float mean = mean_r[r];
+#pragma unroll 1
+        for (int i = 0; i < NPL; ++i) {
+          const int c = 32 * i + lane;
+          const float xe = x_eff_fma(static_cast<float>(static_cast<int>(__ldg(xr + 32 * i))), s_in, inv_s);
+          float v = floorf(__fmul_rn(__fsub_rn(xe, mean), fh));
+          v = __fadd_rn(v, __ldg(bias_int + c));
+          const float ra = fminf(fmaxf(__fmul_rn(v, static_cast<float>(__ldg(mult + c))), -128.4f), 127.4f);
+          const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);
+          const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);
+          if (!fast_ok || ((__float_as_uint(lo) ^ __float_as_uint(hi)) & 1u))
+            stage[warp][r][c] = static_cast<int8_t>(ln16_requant(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax));
+        }
+      }
+    }
+    __syncwarp();
+    for (int v = lane; v < R * VPR; v += 32) {
+      const int r = v / VPR, vv = v - r * VPR;
+      if (r < nr)
+        *reinterpret_cast<int4*>(out + static_cast<long long>(row0 + r) * C + vv * 16) =
+            *reinterpret_cast<const int4*>(&stage[warp][r][vv * 16]);
+    }
+    __syncwarp();
+  }
+}
+
+// Channel-strided order (Swin stage 0: every token inside a whole block of 32 of its image, so the row sum is ATen's
+// multi_row_sum: groups of 16 channels summed sequentially from zero, the group sums added in order).  Two lanes per
+// row, GPL groups each (C = 32 GPL: 96 for Swin-T/S, 128 for Swin-B), sixteen rows per warp: all lanes carry
+// elements, the scalar work of a row runs on its own two lanes, rows come in and leave as 16-byte vectors.
+template <int GPL, typename XT>
+__global__ void __launch_bounds__(256, 2)
+layernorm16_outer2_kernel(const XT* __restrict__ x, long long ldx, int8_t* __restrict__ out, int rows, float s_in,
+                          float inv_s, const float* __restrict__ bias_int, const float* __restrict__ sf,
+                          const double* __restrict__ mult, int qmin, int qmax) {
+  constexpr int C = 32 * GPL, E = 16 * GPL;
+  __shared__ __align__(16) float sb[C];
+  __shared__ __align__(16) float sm[C];
+  if (threadIdx.x < C) {
+    sb[threadIdx.x] = __ldg(bias_int + threadIdx.x);
+    sm[threadIdx.x] = static_cast<float>(__ldg(mult + threadIdx.x));
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int half = lane & 1, sub = lane >> 1;
+  const int c0 = half * E;
+  const bool fast_ok = qmin == -128 && qmax == 127;
+  const int ngroups = (rows + 15) / 16;
+  for (int g = blockIdx.x * 8 + warp; g < ngroups; g += gridDim.x * 8) {
+    const int row = 16 * g + sub;
+    const bool live = row < rows;
+    const XT* xr = x + static_cast<long long>(live ? row : rows - 1) * ldx + c0;
+    int t[E];
+    if (sizeof(XT) == 2) {
+#pragma unroll
+      for (int h = 0; h < E / 8; ++h) {
+        const int4 w = __ldg(reinterpret_cast<const int4*>(xr) + h);
+        const int ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int u = 0; u < 8; ++u) t[8 * h + u] = static_cast<int16_t>(ww[u >> 1] >> (16 * (u & 1)));
+      }
+    } else {
+#pragma unroll
+      for (int h = 0; h < E / 16; ++h) {
+        const int4 w = __ldg(reinterpret_cast<const int4*>(xr) + h);
+        const int ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int u = 0; u < 16; ++u) t[16 * h + u] = static_cast<int8_t>(ww[u >> 2] >> (8 * (u & 3)));
+      }
+    }
+    float gs[GPL];
+#pragma unroll
+    for (int k = 0; k < GPL; ++k) {
+      float sg = 0.f;
+#pragma unroll
+      for (int u = 0; u < 16; ++u) {
+        const float xe = x_eff_fma(static_cast<float>(t[16 * k + u]), s_in, inv_s);   // ivit_modules.py:36
+        sg = __fadd_rn(sg, xe);                                                      // one 16-element cascade group
+        t[16 * k + u] = static_cast<int>(xe);                                        // :38 trunc
+      }
+      gs[k] = sg;
+    }
+    // group sums in order: ((((0 + g0) + g1) + ...) + g_{2 GPL - 1}); the even lane holds the first GPL groups
+    float pre = 0.f;
+#pragma unroll
+    for (int k = 0; k < GPL; ++k) pre = __fadd_rn(pre, gs[k]);
+    float tot = __shfl_sync(0xffffffffu, pre, lane & ~1);
+#pragma unroll
+    for (int k = 0; k < GPL; ++k) tot = __fadd_rn(tot, gs[k]);
+    tot = __shfl_sync(0xffffffffu, tot, lane | 1);
+    const int mean = static_cast<int>(rintf(__fdiv_rn(tot, static_cast<float>(C))));  // :37
+    long long var = 0;
+#pragma unroll
+    for (int u = 0; u < E; ++u) {
+      t[u] -= mean;                                                                  // :40
+      const int sq = static_cast<int>(static_cast<uint32_t>(t[u]) * static_cast<uint32_t>(t[u]));   // :41 wraps (H9)
+      var += static_cast<long long>(sq);                                             // :42
+    }
+    var += __shfl_xor_sync(0xffffffffu, var, 1);
+    const float fh = __fmul_rn(ivit_std_factor(static_cast<float>(var)), 0.5f);       // :45-51
+    int8_t* orow = out + static_cast<long long>(row) * C + c0;
+    uint32_t slow = 0;
+#pragma unroll
+    for (int h = 0; h < E / 16; ++h) {
+      uint32_t w[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float4 b4 = *reinterpret_cast<const float4*>(&sb[c0 + 16 * h + 4 * j]);
+        const float4 m4 = *reinterpret_cast<const float4*>(&sm[c0 + 16 * h + 4 * j]);
+        const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, mm[4] = {m4.x, m4.y, m4.z, m4.w};
+        uint32_t lob[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float yf = __fsub_rn(__int_as_float(0x4B400000 + t[16 * h + 4 * j + e]), 12582912.f);
+          float v = floorf(__fmul_rn(yf, fh));                                       // :52
+          v = __fadd_rn(v, bb[e]);                                                   // :61
+          const float ra = fminf(fmaxf(__fmul_rn(v, mm[e]), -128.4f), 127.4f);
+          const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);
+          const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);
+          slow |= __float_as_uint(lo) ^ __float_as_uint(hi);
+          lob[e] = __float_as_uint(lo);
+        }
+        w[j] = __byte_perm(__byte_perm(lob[0], lob[1], 0x0040), __byte_perm(lob[2], lob[3], 0x0040), 0x5410);
+      }
+      if (live) *(reinterpret_cast<int4*>(orow) + h) = make_int4(w[0], w[1], w[2], w[3]);
+    }
+    if (!fast_ok) slow = 1u;
+    if ((slow & 1u) && live) {                 // rare: exact replay of the elements near a rounding tie
+#pragma unroll 1
+      for (int u = 0; u < E; ++u) {            // re-read codes: indexing t[] dynamically would push it to local memory
+        const float xe = x_eff_fma(static_cast<float>(static_cast<int>(__ldg(xr + u))), s_in, inv_s);
+        const float yf = static_cast<float>(static_cast<int>(xe) - mean);
+        float v = floorf(__fmul_rn(yf, fh));
+        v = __fadd_rn(v, sb[c0 + u]);
+        const float ra = fminf(fmaxf(__fmul_rn(v, sm[c0 + u]), -128.4f), 127.4f);
+        const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);
+        const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);
+        if (!fast_ok || ((__float_as_uint(lo) ^ __float_as_uint(hi)) & 1u))
+          orow[u] = static_cast<int8_t>(ln16_requant(v, __ldg(sf + c0 + u), __ldg(mult + c0 + u), qmin, qmax));
+      }
+    }
+  }
+}
+
 __global__ void fill_cls_rows16_kernel(int16_t* __restrict__ out, const int16_t* __restrict__ cls_row, int B, int N,
                                        int C) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -362,6 +738,94 @@ static int dispatch_requant(int id_bits, int out_bits, const void* z, const floa
 
 using namespace ivit;
 
+// Host check behind x_eff_fma: for this scale and every code of the input width, c + fma(-c, s, r) * inv_s (two
+// fused operations) must equal the IEEE quotient r / s.  The host cores do the same IEEE single-precision arithmetic
+// as the device (divss, mulss, a correctly rounded fmaf), 65536 codes take ~0.2 ms, and the verdict is cached per
+// (scale, width).  A scale that fails keeps the division kernels.
+static bool xeff_fma_ok(float s, int bits) {
+  static std::mutex mu;
+  static std::unordered_map<uint64_t, bool> cache;
+  uint32_t sb;
+  std::memcpy(&sb, &s, 4);
+  const uint64_t key = (static_cast<uint64_t>(bits) << 32) | sb;
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) return it->second;
+  bool ok = std::isfinite(s) && s > 0.f;
+  if (ok) {
+    const volatile float inv = 1.0f / s;
+    const int lim = bits == 8 ? 128 : 32768;
+    for (int q = -lim; q < lim && ok; ++q) {
+      const volatile float r = static_cast<float>(q) * s;
+      const volatile float ref = r / s;
+      const volatile float c = r * inv;
+      const volatile float e = std::fmaf(-c, s, r);
+      const volatile float c2 = std::fmaf(e, inv, c);
+      ok = c2 == ref;
+    }
+  }
+  if (cache.size() > 4096) cache.clear();
+  cache[key] = ok;
+  return ok;
+}
+
+template <typename K>
+static int resident_ctas(K kernel, int fallback) {
+  int nb = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, 256, 0) != cudaSuccess || nb < 1) nb = fallback;
+  return nb;
+}
+
+
+template <int NPL, int R, typename XT, int MINB>
+static int launch_ln16_rows(const XT* x, int64_t ldx, int8_t* out, int rows, float s_in, const float* bias_int,
+                            const float* sf, const double* mult, int qmin, int qmax, cudaStream_t st) {
+  static int resident[16] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev = dev < 0 || dev >= 16 ? 0 : dev;
+  if (resident[dev] == 0) resident[dev] = resident_ctas(layernorm16_ivit_kernel<NPL, R, XT, MINB>, MINB);
+  const int ngroups = (rows + R - 1) / R;
+  int g = (ngroups + 7) / 8;
+  if (g > 148 * resident[dev]) g = 148 * resident[dev];
+  layernorm16_ivit_kernel<NPL, R, XT, MINB><<<g, 256, 0, st>>>(x, ldx, out, rows, s_in, 1.0f / s_in, bias_int, sf, mult,
+                                                               qmin, qmax);
+  return check_launch("layernorm16_ivit_kernel");
+}
+
+template <int NPL, int R, typename XT, int MINB>
+static int launch_ln16_rows_ibert(const XT* x, int64_t ldx, int8_t* out, int rows, float s_in, const float* bias_int,
+                                  const float* sf, const double* mult, int qmin, int qmax, float sp, int use_int_sqrt,
+                                  cudaStream_t st) {
+  static int resident[16] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev = dev < 0 || dev >= 16 ? 0 : dev;
+  if (resident[dev] == 0) resident[dev] = resident_ctas(layernorm16_ibert_kernel<NPL, R, XT, MINB>, MINB);
+  const int ngroups = (rows + R - 1) / R;
+  int g = (ngroups + 7) / 8;
+  if (g > 148 * resident[dev]) g = 148 * resident[dev];
+  layernorm16_ibert_kernel<NPL, R, XT, MINB><<<g, 256, 0, st>>>(x, ldx, out, rows, s_in, 1.0f / s_in, bias_int, sf, mult,
+                                                                qmin, qmax, sp, 1.f / sp, use_int_sqrt);
+  return check_launch("layernorm16_ibert_kernel");
+}
+
+template <int GPL, typename XT>
+static int launch_ln16_outer2(const XT* x, int64_t ldx, int8_t* out, int rows, float s_in, const float* bias_int,
+                              const float* sf, const double* mult, int qmin, int qmax, cudaStream_t st) {
+  static int resident[16] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev = dev < 0 || dev >= 16 ? 0 : dev;
+  if (resident[dev] == 0) resident[dev] = resident_ctas(layernorm16_outer2_kernel<GPL, XT>, 2);
+  const int ngroups = (rows + 15) / 16;
+  int g = (ngroups + 7) / 8;
+  if (g > 148 * resident[dev]) g = 148 * resident[dev];
+  layernorm16_outer2_kernel<GPL, XT><<<g, 256, 0, st>>>(x, ldx, out, rows, s_in, 1.0f / s_in, bias_int, sf, mult, qmin,
+                                                        qmax);
+  return check_launch("layernorm16_outer2_kernel");
+}
+
 template <typename XT>
 static int launch_ln16(int kind, const XT* x, int64_t ldx, int8_t* out, int rows, int C, float s_in,
                        const float* bias_int, const float* sf, const double* mult, int qmin, int qmax, float shift,
@@ -373,6 +837,34 @@ static int launch_ln16(int kind, const XT* x, int64_t ldx, int8_t* out, int rows
   const float sp = ldexpf(1.f, static_cast<int>(shift));
   const int grid = (rows + 7) / 8;
   const bool outer = strided_tokens > 0;
+  // I-ViT kind, scale validated for the two-FMA quotient: the restructured kernels
+  if (kind == 0 && ln_variant() == 0 && xeff_fma_ok(s_in, static_cast<int>(8 * sizeof(XT)))) {
+    const bool vec_ok = (ldx * sizeof(XT)) % 16 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 &&
+                        (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    if (outer && strided_tokens % 32 == 0 && vec_ok) {
+      if (C == 96) return launch_ln16_outer2<3, XT>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, st);
+      if (C == 128) return launch_ln16_outer2<4, XT>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, st);
+    }
+    if (!outer && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+      switch (C) {
+        case 192: return launch_ln16_rows<6, 8, XT, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, st);
+        case 256: return launch_ln16_rows<8, 4, XT, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, st);
+        case 384: return launch_ln16_rows<12, 4, XT, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, st);
+        case 512: return launch_ln16_rows<16, 2, XT, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, st);
+        case 768: return launch_ln16_rows<24, 2, XT, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, st);
+        default: break;
+      }
+    }
+  }
+  if (kind == 1 && ln_variant() == 0 && !outer && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+      xeff_fma_ok(s_in, static_cast<int>(8 * sizeof(XT)))) {
+    switch (C) {
+      case 192: return launch_ln16_rows_ibert<6, 8, XT, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp, use_int_sqrt, st);
+      case 384: return launch_ln16_rows_ibert<12, 4, XT, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp, use_int_sqrt, st);
+      case 768: return launch_ln16_rows_ibert<24, 2, XT, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp, use_int_sqrt, st);
+      default: break;
+    }
+  }
   // Swin stage 0: C = 96, no tail tokens (L % 32 == 0), aligned rows -> the eight-lanes-per-row kernel
   if (outer && kind == 0 && C == 96 && strided_tokens % 32 == 0 && (ldx * sizeof(XT)) % 16 == 0 &&
       (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
@@ -417,6 +909,8 @@ static int launch_ln16(int kind, const XT* x, int64_t ldx, int8_t* out, int rows
 #undef IVIT_LN16_CASE
   return check_launch("layernorm_x16_requant_kernel");
 }
+
+extern "C" int ivit_xeff_fma_ok(float s, int bits) { return (bits == 8 || bits == 16) && xeff_fma_ok(s, bits) ? 1 : 0; }
 
 extern "C" int ivit_layernorm_requant_i16_i8(int kind, const int16_t* x, int64_t ldx, int8_t* out, int rows, int C,
                                              float s_in, const float* bias_int, const float* sf, const double* mult,

@@ -418,6 +418,249 @@ window_attention_tc_kernel(const WinAttnArgs a) {
   if (warp == 0) tmem_dealloc(tmem_base, 64);
 }
 
+// ------------------------------------------------------------------ thread-per-row variant (7x7 windows, hd = 32)
+// Round 2.  Two (image, window, head) units per 128-thread CTA, persistent over the unit pairs:
+//   S = Q K^T   the A tile holds unit 0's 49 query rows in rows 0..48 and unit 1's in rows 64..112; one 128 x 64 x 64
+//               MMA per unit (its own K tile) writes TMEM columns 64 u .. 64 u + 63 -- each thread then owns ONE
+//               score row in its own TMEM lane (lanes 0..63 read unit 0's columns, lanes 64..127 unit 1's),
+//   the per-score chain runs out of registers: qact_attn1 (FP64 dyadic), qact2 as a 256-entry shared table of
+//               rint(c1 m2) plus the layer's precomputed bias term, mask as a per-row 49-bit set, row maximum,
+//               exp term gathered from the layer's (row max, code) table, row sum in torch's order, probabilities
+//               written as one swizzled 64-byte row of the P tile -- no score tile in shared memory, no barrier
+//               between the softmax phases;
+//   O = P V     one 128 x 32 x 64 MMA per unit into columns 32 u .. 32 u + 31 (over the dead scores), read back by
+//               the row's thread, requantised (qact3) and stored as the token's 32 output bytes.
+// Table path only (exp_table present and, under a shift mask, mask_clamps), int8 code ranges.
+constexpr int RN = 49, RWS = 7;
+
+template <bool MASKED, bool BTERMS>
+__device__ __forceinline__ void rows_softmax(const WinAttnArgs& a, uint32_t t_row, const int32_t* __restrict__ bt_row,
+                                             const int8_t* __restrict__ bias_row, const int* rq2, const int* btab,
+                                             unsigned long long mbits, float (&e)[RN]) {
+  int c2[RN];
+  int mx = -0x7fffffff;
+#pragma unroll
+  for (int q4 = 0; q4 < 4; ++q4) {
+    uint32_t v[16];
+    tmem_ld16(t_row + 16 * q4, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int jj = 0; jj < 16; ++jj) {
+      const int j = 16 * q4 + jj;
+      if (j < RN) {
+        const int c1 = clampi(requant_i32_fast(static_cast<int>(v[jj]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
+        const int bterm = BTERMS ? __ldg(bt_row + j) : btab[static_cast<int>(__ldg(bias_row + j)) + 128];
+        c2[j] = clampi(rq2[c1 + 128] + bterm, a.p.qmin2, a.p.qmax2);
+        if (MASKED) mx = ((mbits >> j) & 1ull) ? mx : max(mx, c2[j]);
+        else mx = max(mx, c2[j]);
+      }
+    }
+  }
+  mx = max(mx, a.p.qmin2);                       // (a real row always keeps its diagonal: no effect there)
+  const float* trow = a.p.exp_table + (mx + 128) * 256 + 128;
+  const float e_mask = -a.x0;
+#pragma unroll
+  for (int j = 0; j < RN; ++j) {
+    const float t = __ldg(trow + c2[j]);
+    e[j] = (MASKED && ((mbits >> j) & 1ull)) ? e_mask : t;
+  }
+}
+
+template <bool BTERMS>
+__global__ void __launch_bounds__(128, 4)
+window_attention_rows_kernel(const WinAttnArgs a, long long units) {
+  __shared__ __align__(1024) uint8_t tiles[8192 + 2 * 4096 + 8192 + 2 * 2048];
+  __shared__ int rq2[256];
+  __shared__ int btab[256];
+  __shared__ __align__(8) uint64_t bars[2];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* const sQ = tiles;                 // [128][64 B]: unit 0 rows 0..48, unit 1 rows 64..112
+  uint8_t* const sK = tiles + 8192;          // two [64][64 B]
+  uint8_t* const sP = tiles + 16384;         // [128][64 B]
+  uint8_t* const sVt = tiles + 24576;        // two [32][64 B]: v transposed, [d][token]
+  constexpr int hd = 32;
+  const int res = a.res, nWx = res / RWS, nW = nWx * nWx;
+  const int C = a.nH * hd, L = res * res;
+  const int warp = threadIdx.x >> 5;
+  const int u = threadIdx.x >> 6, i = threadIdx.x & 63;
+  if (threadIdx.x == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(&tmem_slot, 128);
+    tmem_relinquish();
+  }
+  for (int t = threadIdx.x; t < static_cast<int>(sizeof(tiles) / 16); t += blockDim.x)
+    reinterpret_cast<int4*>(tiles)[t] = make_int4(0, 0, 0, 0);       // the K padding (bytes 32..63) stays zero
+  for (int t = threadIdx.x; t < 256; t += blockDim.x) {
+    rq2[t] = requant_i32_fast(t - 128, a.p.mult2);                   // qact2's own branch per qact_attn1 code
+    btab[t] = requant_i32_fast(t - 128, a.p.mult_bias);              // identity branch per bias code
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(32 * warp) << 16);
+  const int iy = i / RWS, ix = i - iy * RWS;
+  uint32_t phase = 0;
+  const long long pairs = (units + 1) >> 1;
+  for (long long pair = blockIdx.x; pair < pairs; pair += gridDim.x, phase ^= 1u) {
+    const long long U = 2 * pair + u;
+    const bool active = U < units && i < RN;
+    const int Uc = static_cast<int>(U < units ? U : units - 1);       // units < 2^31 (checked by the launcher)
+    const int h = Uc % a.nH;
+    const int wb = Uc / a.nH;
+    const int w = wb % nW;
+    const long long b = wb / nW;
+    const int wy = w / nWx, wx = w - wy * nWx;
+    const int ry = wy * RWS + iy, rx = wx * RWS + ix;                 // rolled coordinates
+    const int tok = a.p.windowed ? w * RN + i : ((ry + a.shift) % res) * res + (rx + a.shift) % res;
+    // shifted-window mask of this row as a 49-bit set (swin_quant.py:226-247): only the last window row / column
+    // straddles two regions
+    unsigned long long mbits = 0;
+    const bool masked = a.shift > 0 && (wy == nWx - 1 || wx == nWx - 1);
+    if (masked) {
+      const int by = mask_region(ry, res, RWS, a.shift), bx = mask_region(rx, res, RWS, a.shift);
+      uint32_t my = 0, mxb = 0;
+#pragma unroll
+      for (int t = 0; t < RWS; ++t) {
+        my |= (mask_region(wy * RWS + t, res, RWS, a.shift) != by ? 1u : 0u) << t;
+        mxb |= (mask_region(wx * RWS + t, res, RWS, a.shift) != bx ? 1u : 0u) << t;
+      }
+#pragma unroll
+      for (int t = 0; t < RWS; ++t)
+        mbits |= static_cast<unsigned long long>(((my >> t) & 1u) ? 0x7fu : mxb) << (RWS * t);
+      if (i >= RN) mbits = 0;                    // padding lanes: no row of their own
+    }
+    if (active) {
+      const int8_t* src = a.qkv + (b * L + tok) * 3 * C + h * hd;
+      const int4 q0 = __ldg(reinterpret_cast<const int4*>(src)), q1 = __ldg(reinterpret_cast<const int4*>(src) + 1);
+      const int4 k0 = __ldg(reinterpret_cast<const int4*>(src + C)), k1 = __ldg(reinterpret_cast<const int4*>(src + C) + 1);
+      const int4 v0 = __ldg(reinterpret_cast<const int4*>(src + 2 * C));
+      const int4 v1 = __ldg(reinterpret_cast<const int4*>(src + 2 * C) + 1);
+      const int row = 64 * u + i;
+      *reinterpret_cast<int4*>(sQ + sw64_off(row, 0)) = q0;
+      *reinterpret_cast<int4*>(sQ + sw64_off(row, 16)) = q1;
+      *reinterpret_cast<int4*>(sK + 4096 * u + sw64_off(i, 0)) = k0;
+      *reinterpret_cast<int4*>(sK + 4096 * u + sw64_off(i, 16)) = k1;
+      const int vw[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+      uint8_t* vt = sVt + 2048 * u;
+#pragma unroll
+      for (int d = 0; d < hd; ++d) vt[sw64_off(d, i)] = static_cast<uint8_t>(vw[d >> 2] >> (8 * (d & 3)));
+    }
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      tc_fence_after();
+      constexpr uint32_t idesc1 = make_idesc_i8(128, 64, true, true, false, false);
+#pragma unroll
+      for (int uu = 0; uu < 2; ++uu)
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const uint64_t da = make_smem_desc(smem_u32(sQ) + k * 32, 16, 512, kLayoutSW64);
+          const uint64_t db = make_smem_desc(smem_u32(sK) + 4096 * uu + k * 32, 16, 512, kLayoutSW64);
+          mma_i8_ss(tmem_base + 64 * uu, da, db, idesc1, k != 0 ? 1u : 0u);
+        }
+      tc_commit(&bars[0]);
+    }
+    __syncwarp();
+    mbar_wait(&bars[0], phase);
+    tc_fence_after();
+    {
+      float e[RN];
+      const int32_t* bt_row = BTERMS ? a.p.bias_terms + (static_cast<long long>(h) * RN + (i < RN ? i : 0)) * RN : nullptr;
+      const int8_t* bias_row = a.p.bias_codes + (static_cast<long long>(h) * RN + (i < RN ? i : 0)) * RN;
+      if (masked) rows_softmax<true, BTERMS>(a, t_lane + 64 * u, bt_row, bias_row, rq2, btab, mbits, e);
+      else rows_softmax<false, BTERMS>(a, t_lane + 64 * u, bt_row, bias_row, rq2, btab, 0ull, e);
+      // torch.sum over the 49 terms (ATen vectorized_inner_sum: 32 accumulators take e[0..31], the two left-over
+      // vectors go to accumulator row 0, rows merge in order, lanes add in order after the scalar tail e[48])
+      float acc[8];
+#pragma unroll
+      for (int l = 0; l < 8; ++l) {
+        acc[l] = __fadd_rn(__fadd_rn(e[l], e[32 + l]), e[40 + l]);
+        acc[l] = __fadd_rn(acc[l], e[8 + l]);
+        acc[l] = __fadd_rn(acc[l], e[16 + l]);
+        acc[l] = __fadd_rn(acc[l], e[24 + l]);
+      }
+      float sum = e[48];
+#pragma unroll
+      for (int l = 0; l < 8; ++l) sum = __fadd_rn(sum, acc[l]);
+      sum = fminf(sum, 2147483648.f);                                             // ivit_modules.py:171-173
+      const float fs = __fmul_rn(floorf(__fdiv_rn(2147483648.f, sum)), a.out_shift);   // :174-175
+      uint32_t pw[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        uint32_t lob[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const int j = 4 * k + t;
+          // floor of a value in [0, 2^22) through the 2^23 magic constant (round toward zero): the code is the low byte
+          lob[t] = j < RN ? __float_as_uint(__fadd_rz(__fmul_rn(e[j], fs), 8388608.f)) : 0u;
+        }
+        pw[k] = __byte_perm(__byte_perm(lob[0], lob[1], 0x0040), __byte_perm(lob[2], lob[3], 0x0040), 0x5410);
+      }
+      if (i < RN) {
+        const int row = 64 * u + i;
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          *reinterpret_cast<int4*>(sP + sw64_off(row, 16 * c)) = make_int4(pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
+        if (a.probs != nullptr && active) {
+          uint8_t* pr = a.probs + ((b * nW + w) * a.nH + h) * RN * RN + i * RN;
+#pragma unroll
+          for (int j = 0; j < RN; ++j) pr[j] = static_cast<uint8_t>(pw[j >> 2] >> (8 * (j & 3)));
+        }
+      }
+    }
+    tc_fence_before();
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      tc_fence_after();
+      constexpr uint32_t idesc2 = make_idesc_i8(128, 32, false, true, false, false);   // P u8, v^T s8, both K-major
+#pragma unroll
+      for (int uu = 0; uu < 2; ++uu)
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const uint64_t da = make_smem_desc(smem_u32(sP) + k * 32, 16, 512, kLayoutSW64);
+          const uint64_t db = make_smem_desc(smem_u32(sVt) + 2048 * uu + k * 32, 16, 512, kLayoutSW64);
+          mma_i8_ss(tmem_base + 32 * uu, da, db, idesc2, k != 0 ? 1u : 0u);
+        }
+      tc_commit(&bars[1]);
+    }
+    __syncwarp();
+    mbar_wait(&bars[1], phase);
+    tc_fence_after();
+    {
+      uint32_t o[32];
+      tmem_ld16(t_lane + 32 * u, *reinterpret_cast<uint32_t(*)[16]>(&o[0]));
+      tmem_ld16(t_lane + 32 * u + 16, *reinterpret_cast<uint32_t(*)[16]>(&o[16]));
+      tmem_ld_wait();
+      if (active && a.out != nullptr) {
+        uint32_t wds[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          int c[4];
+#pragma unroll
+          for (int t = 0; t < 4; ++t)
+            c[t] = clampi(requant_i32_fast(static_cast<int>(o[4 * k + t]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
+          wds[k] = __byte_perm(__byte_perm(c[0], c[1], 0x0040), __byte_perm(c[2], c[3], 0x0040), 0x5410);
+        }
+        int4* op = reinterpret_cast<int4*>(a.out + (b * L + tok) * C + h * hd);
+        op[0] = make_int4(wds[0], wds[1], wds[2], wds[3]);
+        op[1] = make_int4(wds[4], wds[5], wds[6], wds[7]);
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+  }
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
+  }
+}
+
 // PatchMerging gather (swin_quant.py:339-344): [B, res, res, C] -> [B, (res/2)^2, 4C], channel block k
 // of output token (i, j) = input token (2 i + k % 2, 2 j + k / 2).
 // One 16-byte vector per thread (VEC elements); C % VEC == 0.
@@ -501,8 +744,29 @@ extern "C" int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t*
   const bool table = p->exp_table != nullptr && (shift == 0 || p->mask_clamps != 0) && p->qmin2 >= -128 && p->qmax2 <= 127;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int grid = static_cast<int>(ctas);
+  // 7x7 windows, hd = 32, table path, int8 code ranges: the thread-per-row kernel (variant 0)
+  if (g_win_variant == 0 && table && ws == RWS && hd == 32 && p->qmin_attn >= -128 && p->qmax_attn <= 127 &&
+      (reinterpret_cast<uintptr_t>(out) & 15) == 0 && (reinterpret_cast<uintptr_t>(qkv) & 15) == 0) {
+    static int resident[16] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = dev < 0 || dev >= 16 ? 0 : dev;
+    const bool bterms = p->bias_terms != nullptr;
+    if (resident[dev] == 0) {
+      int nb = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, window_attention_rows_kernel<true>, 128, 0) != cudaSuccess || nb < 1)
+        nb = 2;
+      resident[dev] = nb > 4 ? 4 : nb;           // 128 TMEM columns per CTA: at most four per SM
+    }
+    const long long pairs = (ctas + 1) / 2;
+    const long long cap = 148LL * resident[dev];
+    const int g = static_cast<int>(pairs < cap ? pairs : cap);
+    if (bterms) window_attention_rows_kernel<true><<<g, 128, 0, st>>>(a, ctas);
+    else window_attention_rows_kernel<false><<<g, 128, 0, st>>>(a, ctas);
+    return check_launch("window_attention_rows_kernel");
+  }
   // hd = 32 (every Swin size): the two products on tcgen05; otherwise (or variant 1) the dp4a kernel
-  const bool tc = g_win_variant == 0 && hd == 32 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+  const bool tc = g_win_variant != 1 && hd == 32 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
                   (reinterpret_cast<uintptr_t>(qkv) & 3) == 0;
   if (tc) {
     if (table) window_attention_tc_kernel<true><<<grid, 256, 0, st>>>(a);

@@ -67,11 +67,30 @@ def test_layernorm16_ivit(C):
     _ln16_case(0, C, 64, seed=C + 1, s_in=3.1e-5, spread=20000.0, neg=True)
 
 
+@pytest.mark.parametrize("C", [192, 256, 384, 512, 768])
+def test_layernorm16_ivit_both_kernel_families(C):
+    """The restructured kernels (x/s as two fused operations, taken for scales ivit_xeff_fma_ok accepts) and the division
+    kernels (ivit_layernorm_set_variant(1)) against the same oracle rows."""
+    assert _cabi.load().ivit_xeff_fma_ok(float(f32(1.37e-4)), 16) == 1
+    try:
+        for variant in (0, 1):
+            ops.set_layernorm_variant(variant)
+            _ln16_case(0, C, 203, seed=C + 7, s_in=1.37e-4, spread=9000.0)
+            _ln16_case(0, C, 37, seed=C + 8, s_in=2.9e-5, spread=25000.0, neg=True)
+    finally:
+        ops.set_layernorm_variant(0)
+
+
 @pytest.mark.parametrize("C", [192, 384, 768])
 def test_layernorm16_ibert(C):
-    assert _ln16_case(1, C, 203, seed=C, s_in=1.37e-4, spread=9000.0, shift=5.0) >= 200
-    _ln16_case(1, C, 64, seed=C + 1, s_in=3.1e-5, spread=3000.0, neg=True, shift=3.0)
-    _ln16_case(1, C, 64, seed=C + 2, s_in=3.1e-5, spread=3000.0, use_int_sqrt=True, shift=3.0)
+    try:
+        for variant in (0, 1):              # restructured kernel / division kernel
+            ops.set_layernorm_variant(variant)
+            assert _ln16_case(1, C, 203, seed=C, s_in=1.37e-4, spread=9000.0, shift=5.0) >= 200
+            _ln16_case(1, C, 64, seed=C + 1, s_in=3.1e-5, spread=3000.0, neg=True, shift=3.0)
+            _ln16_case(1, C, 64, seed=C + 2, s_in=3.1e-5, spread=3000.0, use_int_sqrt=True, shift=3.0)
+    finally:
+        ops.set_layernorm_variant(0)
 
 
 def test_layernorm16_strided_class_rows():

@@ -138,12 +138,12 @@ def test_compile_frozen_from_a_module_api_swin_model():
     assert np.array_equal(sess2.infer(x.pin_memory()).numpy(), exp)
 
 
-def _window_attention_case(res, ws, shift, nH, hd, seed, s2_target, use_table):
+def _window_attention_case(res, ws, shift, nH, hd, seed, s2_target, use_table, B=2, bias_terms=False):
     """ivit_window_attention_i8 alone against the oracle's statement of WindowAttention.forward (swin_quant.py:131-160)
     on random int8 qkv codes, for a chosen softmax-input scale s2 (decides whether a masked score can be proven to clamp)."""
     from ivit_b200.swin_plan import mask_always_clamps, relative_position_index
     rng = np.random.default_rng(seed)
-    B, C, L, N = 2, nH * hd, res * res, ws * ws
+    C, L, N = nH * hd, res * res, ws * ws
     qkv = np.clip(np.rint(rng.standard_normal((B, L, 3 * C)) * 40), -128, 127).astype(np.int8)
     s1 = np.array([0.05], dtype=f32)
     x = (qkv.astype(f32) * s1).astype(f32).reshape(B, res, res, 3 * C)
@@ -186,6 +186,10 @@ def _window_attention_case(res, ws, shift, nH, hd, seed, s2_target, use_table):
     bias_codes = torch.from_numpy(np.ascontiguousarray(
         tab_codes[idx].reshape(N, N, nH).transpose(2, 0, 1)).astype(np.int8)).cuda()
     p.bias_codes = bias_codes.data_ptr()
+    terms = None
+    if bias_terms:              # the identity branch of qact2 evaluated once per layer (what FrozenSwinPlan passes)
+        terms = torch.from_numpy(np.rint(bias_codes.cpu().numpy().astype(np.float64) * p.mult_bias).astype(np.int32)).cuda()
+        p.bias_terms = terms.data_ptr()
     clamps = mask_always_clamps(s2[0], -128, 127)
     keep = None
     if use_table:
@@ -196,11 +200,11 @@ def _window_attention_case(res, ws, shift, nH, hd, seed, s2_target, use_table):
     out, probs = ops.window_attention(torch.from_numpy(qkv).cuda(), B, res, ws, shift, nH, hd, p, want_probs=True)
     assert np.array_equal(probs.cpu().numpy().astype(np.int64), pr_codes.astype(np.int64)), "softmax codes"
     assert np.array_equal(out.cpu().numpy().reshape(exp.shape).astype(np.int64), exp.astype(np.int64)), "output codes"
-    del keep
+    del keep, terms
     return clamps
 
 
-@pytest.fixture(params=[0, 1], ids=["tcgen05", "dp4a"])
+@pytest.fixture(params=[0, 1, 2], ids=["rows", "dp4a", "tcgen05"])
 def window_variant(request):
     prev = ops.set_window_attention_variant(request.param)
     yield request.param
@@ -227,6 +231,10 @@ def test_window_attention_kernel(s2_target, use_table, window_variant):
     _window_attention_case(8, 4, 2, 2, 32, seed=3, s2_target=s2_target, use_table=use_table)      # 4x4 windows
     _window_attention_case(7, 7, 0, 6, 32, seed=4, s2_target=s2_target, use_table=use_table)      # one window, 6 heads
     _window_attention_case(16, 8, 4, 2, 32, seed=5, s2_target=s2_target, use_table=use_table)     # 8x8 windows: 64 tokens
+    # odd number of (window, head) units, 16 windows (masks on the last window row AND column), precomputed bias terms
+    _window_attention_case(7, 7, 0, 3, 32, seed=7, s2_target=s2_target, use_table=use_table, B=3)
+    _window_attention_case(28, 7, 3, 3, 32, seed=8, s2_target=s2_target, use_table=use_table, B=1, bias_terms=True)
+    _window_attention_case(14, 7, 3, 6, 32, seed=9, s2_target=s2_target, use_table=use_table, B=5, bias_terms=True)
     if window_variant == 1:
         _window_attention_case(14, 7, 3, 2, 64, seed=6, s2_target=s2_target, use_table=use_table)  # head_dim 64: dp4a only
 
@@ -267,9 +275,19 @@ def test_patch_merge_gather_and_avgpool():
         assert np.array_equal(got.astype(np.int64), codes[:, :, 0].astype(np.int64)), (L, Cc)
 
 
+@pytest.mark.parametrize("variant", [0, 1])
 @pytest.mark.parametrize("C,tokens,bits", [(96, 196, 16), (96, 64, 16), (128, 49, 16), (96, 196, 8), (192, 100, 16),
-                                           (96, 64, 8), (96, 160, 16), (96, 3136, 16), (384, 64, 16)])
-def test_layernorm_strided_order(C, tokens, bits):
+                                           (96, 64, 8), (96, 160, 16), (96, 3136, 16), (384, 64, 16), (128, 64, 16),
+                                           (128, 96, 8)])
+def test_layernorm_strided_order(C, tokens, bits, variant):
+    ops.set_layernorm_variant(variant)          # 0: two-lanes-per-row kernels where they apply; 1: division kernels
+    try:
+        _layernorm_strided_order(C, tokens, bits)
+    finally:
+        ops.set_layernorm_variant(0)
+
+
+def _layernorm_strided_order(C, tokens, bits):
     """LayerNorm whose reference input is channel-strided: torch's outer-reduction order of the mean, both
     forms (whole 32-token blocks / tail tokens).  16-bit codes make the order matter on ordinary rows."""
     rng = np.random.default_rng(C + tokens)
