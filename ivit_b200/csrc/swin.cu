@@ -9,6 +9,9 @@
 // kernel reads q / k / v of window token (iy, ix) of window (wy, wx) at image token
 // ((wy ws + iy + shift) % res, (wx ws + ix + shift) % res) of the un-permuted [B, L, 3C] qkv
 // buffer and writes its output row to the same token, so no permuted copy ever exists in HBM.
+#include <cstdio>
+#include <cstdlib>
+
 #include "intmath.cuh"
 #include "ivit_b200.h"
 #include "ptx.cuh"
@@ -433,9 +436,8 @@ window_attention_tc_kernel(const WinAttnArgs a) {
 // Table path only (exp_table present and, under a shift mask, mask_clamps), int8 code ranges.
 constexpr int RN = 49, RWS = 7;
 
-template <bool MASKED, bool BTERMS>
-__device__ __forceinline__ void rows_softmax(const WinAttnArgs& a, uint32_t t_row, const int32_t* __restrict__ bt_row,
-                                             const int8_t* __restrict__ bias_row, const int* rq2, const int* btab,
+template <bool MASKED>
+__device__ __forceinline__ void rows_softmax(const WinAttnArgs& a, uint32_t t_row, const int* bt_row, const int* rq2,
                                              unsigned long long mbits, float (&e)[RN]) {
   int c2[RN];
   int mx = -0x7fffffff;
@@ -448,9 +450,9 @@ __device__ __forceinline__ void rows_softmax(const WinAttnArgs& a, uint32_t t_ro
     for (int jj = 0; jj < 16; ++jj) {
       const int j = 16 * q4 + jj;
       if (j < RN) {
-        const int c1 = clampi(requant_i32_fast(static_cast<int>(v[jj]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
-        const int bterm = BTERMS ? __ldg(bt_row + j) : btab[static_cast<int>(__ldg(bias_row + j)) + 128];
-        c2[j] = clampi(rq2[c1 + 128] + bterm, a.p.qmin2, a.p.qmax2);
+        // int32 -> fp64 on the conversion pipe (idle here): two issue slots per requantisation instead of four
+        const int c1 = clampi(requant_i32_cvt(static_cast<int>(v[jj]), a.p.mult_attn), a.p.qmin_attn, a.p.qmax_attn);
+        c2[j] = clampi(rq2[c1 + 128] + bt_row[j], a.p.qmin2, a.p.qmax2);
         if (MASKED) mx = ((mbits >> j) & 1ull) ? mx : max(mx, c2[j]);
         else mx = max(mx, c2[j]);
       }
@@ -466,12 +468,14 @@ __device__ __forceinline__ void rows_softmax(const WinAttnArgs& a, uint32_t t_ro
   }
 }
 
-template <bool BTERMS>
+// grid: a multiple of nH CTAs, so that CTA c keeps head c % nH for all of its pairs: the head's bias terms
+// (rint(bias code x m_bias), [49][49] int32) live in shared memory.  A pair = the same head of two consecutive
+// (image, window) positions bw = 2 m, 2 m + 1 of the B * nW windows.
 __global__ void __launch_bounds__(128, 4)
-window_attention_rows_kernel(const WinAttnArgs a, long long units) {
+window_attention_rows_kernel(const WinAttnArgs a, int BW) {
   __shared__ __align__(1024) uint8_t tiles[8192 + 2 * 4096 + 8192 + 2 * 2048];
+  __shared__ int sbt[RN * RN];
   __shared__ int rq2[256];
-  __shared__ int btab[256];
   __shared__ __align__(8) uint64_t bars[2];
   __shared__ uint32_t tmem_slot;
   uint8_t* const sQ = tiles;                 // [128][64 B]: unit 0 rows 0..48, unit 1 rows 64..112
@@ -483,6 +487,7 @@ window_attention_rows_kernel(const WinAttnArgs a, long long units) {
   const int C = a.nH * hd, L = res * res;
   const int warp = threadIdx.x >> 5;
   const int u = threadIdx.x >> 6, i = threadIdx.x & 63;
+  const int h = blockIdx.x % a.nH;
   if (threadIdx.x == 0) {
     mbar_init(&bars[0], 1);
     mbar_init(&bars[1], 1);
@@ -494,29 +499,32 @@ window_attention_rows_kernel(const WinAttnArgs a, long long units) {
   }
   for (int t = threadIdx.x; t < static_cast<int>(sizeof(tiles) / 16); t += blockDim.x)
     reinterpret_cast<int4*>(tiles)[t] = make_int4(0, 0, 0, 0);       // the K padding (bytes 32..63) stays zero
-  for (int t = threadIdx.x; t < 256; t += blockDim.x) {
+  for (int t = threadIdx.x; t < 256; t += blockDim.x)
     rq2[t] = requant_i32_fast(t - 128, a.p.mult2);                   // qact2's own branch per qact_attn1 code
-    btab[t] = requant_i32_fast(t - 128, a.p.mult_bias);              // identity branch per bias code
-  }
+  for (int t = threadIdx.x; t < RN * RN; t += blockDim.x)            // its identity branch (quant_utils.py:232-245)
+    sbt[t] = a.p.bias_terms != nullptr ? __ldg(a.p.bias_terms + h * RN * RN + t)
+                                       : requant_i32_fast(__ldg(a.p.bias_codes + h * RN * RN + t), a.p.mult_bias);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
   const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(32 * warp) << 16);
   const int iy = i / RWS, ix = i - iy * RWS;
+  const int* bt_row = sbt + (i < RN ? i : 0) * RN;
   uint32_t phase = 0;
-  const long long pairs = (units + 1) >> 1;
-  for (long long pair = blockIdx.x; pair < pairs; pair += gridDim.x, phase ^= 1u) {
-    const long long U = 2 * pair + u;
-    const bool active = U < units && i < RN;
-    const int Uc = static_cast<int>(U < units ? U : units - 1);       // units < 2^31 (checked by the launcher)
-    const int h = Uc % a.nH;
-    const int wb = Uc / a.nH;
-    const int w = wb % nW;
-    const long long b = wb / nW;
+  const int step = gridDim.x / a.nH;                                  // window pairs between two iterations
+  const int npairs = (BW + 1) >> 1;
+  for (int m = blockIdx.x / a.nH; m < npairs; m += step, phase ^= 1u) {
+    const int bw = 2 * m + u;
+    const bool active = bw < BW && i < RN;
+    const int bwc = min(bw, BW - 1);
+    const int b = bwc / nW, w = bwc - b * nW;
     const int wy = w / nWx, wx = w - wy * nWx;
     const int ry = wy * RWS + iy, rx = wx * RWS + ix;                 // rolled coordinates
-    const int tok = a.p.windowed ? w * RN + i : ((ry + a.shift) % res) * res + (rx + a.shift) % res;
+    int ty = ry + a.shift, tx = rx + a.shift;                         // < 2 res: one conditional subtract each
+    ty -= ty >= res ? res : 0;
+    tx -= tx >= res ? res : 0;
+    const int tok = a.p.windowed ? w * RN + i : ty * res + tx;
     // shifted-window mask of this row as a 49-bit set (swin_quant.py:226-247): only the last window row / column
     // straddles two regions
     unsigned long long mbits = 0;
@@ -534,8 +542,9 @@ window_attention_rows_kernel(const WinAttnArgs a, long long units) {
         mbits |= static_cast<unsigned long long>(((my >> t) & 1u) ? 0x7fu : mxb) << (RWS * t);
       if (i >= RN) mbits = 0;                    // padding lanes: no row of their own
     }
+    const long long row_off = static_cast<long long>(b) * L + tok;
     if (active) {
-      const int8_t* src = a.qkv + (b * L + tok) * 3 * C + h * hd;
+      const int8_t* src = a.qkv + row_off * 3 * C + h * hd;
       const int4 q0 = __ldg(reinterpret_cast<const int4*>(src)), q1 = __ldg(reinterpret_cast<const int4*>(src) + 1);
       const int4 k0 = __ldg(reinterpret_cast<const int4*>(src + C)), k1 = __ldg(reinterpret_cast<const int4*>(src + C) + 1);
       const int4 v0 = __ldg(reinterpret_cast<const int4*>(src + 2 * C));
@@ -566,14 +575,28 @@ window_attention_rows_kernel(const WinAttnArgs a, long long units) {
       tc_commit(&bars[0]);
     }
     __syncwarp();
+    {
+      // the next pair's q / k / v rows of this thread: pull them into L2 while this pair is worked on
+      const int bwn = 2 * (m + step) + u;
+      if (bwn < BW && i < RN) {
+        const int bn = bwn / nW, wn = bwn - bn * nW;
+        const int wyn = wn / nWx, wxn = wn - wyn * nWx;
+        int tyn = wyn * RWS + iy + a.shift, txn = wxn * RWS + ix + a.shift;
+        tyn -= tyn >= res ? res : 0;
+        txn -= txn >= res ? res : 0;
+        const int tokn = a.p.windowed ? wn * RN + i : tyn * res + txn;
+        const int8_t* nsrc = a.qkv + (static_cast<long long>(bn) * L + tokn) * 3 * C + h * hd;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(nsrc));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(nsrc + C));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(nsrc + 2 * C));
+      }
+    }
     mbar_wait(&bars[0], phase);
     tc_fence_after();
     {
       float e[RN];
-      const int32_t* bt_row = BTERMS ? a.p.bias_terms + (static_cast<long long>(h) * RN + (i < RN ? i : 0)) * RN : nullptr;
-      const int8_t* bias_row = a.p.bias_codes + (static_cast<long long>(h) * RN + (i < RN ? i : 0)) * RN;
-      if (masked) rows_softmax<true, BTERMS>(a, t_lane + 64 * u, bt_row, bias_row, rq2, btab, mbits, e);
-      else rows_softmax<false, BTERMS>(a, t_lane + 64 * u, bt_row, bias_row, rq2, btab, 0ull, e);
+      if (masked) rows_softmax<true>(a, t_lane + 64 * u, bt_row, rq2, mbits, e);
+      else rows_softmax<false>(a, t_lane + 64 * u, bt_row, rq2, 0ull, e);
       // torch.sum over the 49 terms (ATen vectorized_inner_sum: 32 accumulators take e[0..31], the two left-over
       // vectors go to accumulator row 0, rows merge in order, lanes add in order after the scalar tail e[48])
       float acc[8];
@@ -607,9 +630,9 @@ window_attention_rows_kernel(const WinAttnArgs a, long long units) {
         for (int c = 0; c < 4; ++c)
           *reinterpret_cast<int4*>(sP + sw64_off(row, 16 * c)) = make_int4(pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
         if (a.probs != nullptr && active) {
-          uint8_t* pr = a.probs + ((b * nW + w) * a.nH + h) * RN * RN + i * RN;
-#pragma unroll
-          for (int j = 0; j < RN; ++j) pr[j] = static_cast<uint8_t>(pw[j >> 2] >> (8 * (j & 3)));
+          uint8_t* pr = a.probs + ((static_cast<long long>(b) * nW + w) * a.nH + h) * RN * RN + i * RN;
+#pragma unroll 1
+          for (int j = 0; j < RN; ++j) pr[j] = sP[sw64_off(row, j)];
         }
       }
     }
@@ -644,10 +667,10 @@ window_attention_rows_kernel(const WinAttnArgs a, long long units) {
           int c[4];
 #pragma unroll
           for (int t = 0; t < 4; ++t)
-            c[t] = clampi(requant_i32_fast(static_cast<int>(o[4 * k + t]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
+            c[t] = clampi(requant_i32_cvt(static_cast<int>(o[4 * k + t]), a.p.mult_out), a.p.qmin_out, a.p.qmax_out);
           wds[k] = __byte_perm(__byte_perm(c[0], c[1], 0x0040), __byte_perm(c[2], c[3], 0x0040), 0x5410);
         }
-        int4* op = reinterpret_cast<int4*>(a.out + (b * L + tok) * C + h * hd);
+        int4* op = reinterpret_cast<int4*>(a.out + row_off * C + h * hd);
         op[0] = make_int4(wds[0], wds[1], wds[2], wds[3]);
         op[1] = make_int4(wds[4], wds[5], wds[6], wds[7]);
       }
@@ -747,22 +770,23 @@ extern "C" int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t*
   // 7x7 windows, hd = 32, table path, int8 code ranges: the thread-per-row kernel (variant 0)
   if (g_win_variant == 0 && table && ws == RWS && hd == 32 && p->qmin_attn >= -128 && p->qmax_attn <= 127 &&
       (reinterpret_cast<uintptr_t>(out) & 15) == 0 && (reinterpret_cast<uintptr_t>(qkv) & 15) == 0) {
-    static int resident[16] = {0};
+    static int attr_set[16] = {0};
     int dev = 0;
     cudaGetDevice(&dev);
     dev = dev < 0 || dev >= 16 ? 0 : dev;
-    const bool bterms = p->bias_terms != nullptr;
-    if (resident[dev] == 0) {
-      int nb = 0;
-      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, window_attention_rows_kernel<true>, 128, 0) != cudaSuccess || nb < 1)
-        nb = 2;
-      resident[dev] = nb > 4 ? 4 : nb;           // 128 TMEM columns per CTA: at most four per SM
+    if (attr_set[dev] == 0) {
+      // four CTAs per SM: 128 of the 512 TMEM columns each (the occupancy API does not know about TMEM), 4 x 41 KB of
+      // shared memory -- ask for the large carve-out so that they fit
+      cudaFuncSetAttribute(window_attention_rows_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                           cudaSharedmemCarveoutMaxShared);
+      attr_set[dev] = 1;
     }
-    const long long pairs = (ctas + 1) / 2;
-    const long long cap = 148LL * resident[dev];
-    const int g = static_cast<int>(pairs < cap ? pairs : cap);
-    if (bterms) window_attention_rows_kernel<true><<<g, 128, 0, st>>>(a, ctas);
-    else window_attention_rows_kernel<false><<<g, 128, 0, st>>>(a, ctas);
+    const long long BW = static_cast<long long>(B) * (res / ws) * (res / ws);
+    const long long pairs = ((BW + 1) / 2) * nH;
+    long long g = pairs < 148LL * 4 ? pairs : 148LL * 4;
+    g -= g % nH;                                   // CTA c keeps head c % nH
+    if (g < nH) g = nH;
+    window_attention_rows_kernel<<<static_cast<int>(g), 128, 0, st>>>(a, static_cast<int>(BW));
     return check_launch("window_attention_rows_kernel");
   }
   // hd = 32 (every Swin size): the two products on tcgen05; otherwise (or variant 1) the dp4a kernel
