@@ -35,6 +35,8 @@ class _FusedPlanForward:
     def __init__(self, model: nn.Module):
         self._model = model
         self._plans = {}
+        # the plans hold constants derived from the state_dict: a later load_state_dict starts over
+        self._hook = model.register_load_state_dict_post_hook(lambda module, incompatible: self._plans.clear())
 
     def __call__(self, x: torch.Tensor) -> torch.Tensor:
         from . import _cabi
@@ -76,6 +78,7 @@ def unfreeze_model(model: nn.Module) -> nn.Module:
         if isinstance(mod, _FREEZABLE) and hasattr(mod, "unfix"):
             mod.unfix()
     if isinstance(model.__dict__.get("forward"), _FusedPlanForward):
+        model.__dict__["forward"]._hook.remove()
         del model.__dict__["forward"]
     return model
 

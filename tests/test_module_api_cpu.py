@@ -337,3 +337,23 @@ def test_float_registry_entries_equal_reference():
     assert torch.equal(la, lb)
     for k, v in m_ref.state_dict().items():
         assert torch.equal(v, m_our.state_dict()[k]), k
+
+
+def test_fused_swin_forward_drops_its_plans_on_load_state_dict():
+    """lifecycle._FusedPlanForward keeps FrozenSwinPlans built from the state_dict: loading new weights must start over."""
+    from ivit_b200 import lifecycle
+    from ivit_b200.synthetic import load_swin_case
+    from swin_caller import SwinTransformer
+    cfg, state, _ = load_swin_case("swin_toy")
+    model = SwinTransformer(cfg)
+    ck = {"model": {k: torch.as_tensor(v) for k, v in state.items()}}
+    lifecycle.load_checkpoint(model, ck)
+    lifecycle.freeze_model(model)
+    fwd = model.__dict__["forward"]
+    fwd._plans[("cuda", 0)] = object()
+    lifecycle.load_checkpoint(model, ck)
+    assert fwd._plans == {}
+    with pytest.raises(IvitKernelError):
+        model(synth_images(1, cfg, seed=0))            # CPU tensor: the frozen forward refuses, no fallback
+    lifecycle.unfreeze_model(model)
+    assert "forward" not in model.__dict__
