@@ -32,7 +32,7 @@ others)
   # the other BASELINE.json configs on the current build -> one JSON list
   echo "[" > gpurun_out/${T}_bench_other_configs.json
   first=1
-  for cb in "deit_tiny_ivit 8" "deit_tiny_ivit 256" "vit_base_mixed 64" "vit_base_mixed 256" "swin_tiny_ivit 256" "deit_base_ibert_w16 64" "deit_base_ibert_w16 256" "deit_base_ibert 64" "deit_tiny_ppoly 256"; do
+  for cb in "deit_tiny_ivit 8" "deit_tiny_ivit 256" "vit_base_mixed 64" "vit_base_mixed 256" "swin_tiny 256" "deit_base_ibert_w16 64" "deit_base_ibert_w16 256" "deit_base_ibert 64" "deit_tiny_ppoly 256"; do
     set -- $cb
     timeout 400 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --case $1 --batch $2 > gpurun_out/_o.json 2> gpurun_out/_o.err || { echo "bench $1 $2 failed"; tail -n 3 gpurun_out/_o.err; continue; }
     [ $first = 1 ] || echo "," >> gpurun_out/${T}_bench_other_configs.json
