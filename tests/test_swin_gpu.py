@@ -200,6 +200,17 @@ def _window_attention_case(res, ws, shift, nH, hd, seed, s2_target, use_table, B
     out, probs = ops.window_attention(torch.from_numpy(qkv).cuda(), B, res, ws, shift, nH, hd, p, want_probs=True)
     assert np.array_equal(probs.cpu().numpy().astype(np.int64), pr_codes.astype(np.int64)), "softmax codes"
     assert np.array_equal(out.cpu().numpy().reshape(exp.shape).astype(np.int64), exp.astype(np.int64)), "output codes"
+    # window-order form (params.windowed = 1, the module path's caller): qkv already rolled and partitioned, output in
+    # WindowAttention.forward's own [B * nW, N, C] order
+    qw = qkv.reshape(B, res, res, 3 * C)
+    if shift:
+        qw = np.roll(qw, (-shift, -shift), axis=(1, 2))
+    qw = np.ascontiguousarray(SO.window_partition(qw, ws).reshape(B, L, 3 * C))
+    p.windowed = 1
+    out_w, probs_w = ops.window_attention(torch.from_numpy(qw).cuda(), B, res, ws, shift, nH, hd, p, want_probs=True)
+    assert np.array_equal(probs_w.cpu().numpy().astype(np.int64), pr_codes.astype(np.int64)), "softmax codes (windowed)"
+    assert np.array_equal(out_w.cpu().numpy().reshape(-1, N, C).astype(np.int64), out_codes.reshape(-1, N, C).astype(np.int64)), \
+        "output codes (windowed)"
     del keep, terms
     return clamps
 
