@@ -451,34 +451,32 @@ layernorm_ivit_requant4_kernel(const int8_t* __restrict__ x, long long ldx, int8
     }
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      uint32_t slow = 0;
       uint32_t lob[NPL];                  // 1.5 * 2^23 + code as float bits: the code is the low byte
       const float fh = __fmul_rn(factor[r], 0.5f);                  // fl(y * factor) / 2 == fl(y * (factor / 2)): exact scaling
 #pragma unroll
-      for (int i = 0; i < NPL; ++i) {
-        const float yf = __fsub_rn(__int_as_float(0x4B400000 + y[r][i]), 12582912.f);
-        float v = floorf(__fmul_rn(yf, fh));                                                     // :52
-        v = __fadd_rn(v, bia[i]);                                                               // :61
-        // clamp(rint(ra), -128, 127) == rint(clamp(ra, -128.4, 127.4)): the code then fits the low byte
-        const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -128.4f), 127.4f);
-        const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);   // 1 - 2^-18
-        const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);   // 1 + 2^-18
-        slow |= __float_as_uint(lo) ^ __float_as_uint(hi);                   // consecutive integers differ in bit 0
-        lob[i] = __float_as_uint(lo);
-      }
-      if (!fast_ok) slow = 1u;
-      if (slow & 1u) {                      // some element sits within 2^-18 of a rounding tie (~1e-3 of them): exact replay
+      for (int j = 0; j < NJ; ++j) {       // the four channels of one output word; a near-tie is replayed inside its group
+        float v[4];
+        uint32_t x[4], any = 0;
 #pragma unroll
-        for (int i = 0; i < NPL; ++i) {
-          const int c = 128 * (i >> 2) + 4 * lane + (i & 3);
-          const float yf = static_cast<float>(y[r][i]);
-          float v = floorf(__fmul_rn(__fmul_rn(yf, factor[r]), 0.5f));                          // :52
-          v = __fadd_rn(v, bia[i]);                                                             // :61
-          const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -128.4f), 127.4f);
-          const uint32_t l2 = __float_as_uint(__fmaf_rn(ra, 0.999996185302734375f, 12582912.f));
-          const uint32_t h2 = __float_as_uint(__fmaf_rn(ra, 1.000003814697265625f, 12582912.f));
-          if (((l2 ^ h2) & 1u) || !fast_ok)
-            lob[i] = static_cast<uint32_t>(ln_requant_exact(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax)) & 0xffu;
+        for (int e = 0; e < 4; ++e) {
+          const int i = 4 * j + e;
+          const float yf = __fsub_rn(__int_as_float(0x4B400000 + y[r][i]), 12582912.f);
+          v[e] = __fadd_rn(floorf(__fmul_rn(yf, fh)), bia[i]);                                  // :52, :61
+          // clamp(rint(ra), -128, 127) == rint(clamp(ra, -128.4, 127.4)): the code then fits the low byte
+          const float ra = fminf(fmaxf(__fmul_rn(v[e], mf[i]), -128.4f), 127.4f);
+          const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);   // 1 - 2^-18
+          const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);   // 1 + 2^-18
+          x[e] = __float_as_uint(lo) ^ __float_as_uint(hi);                    // consecutive integers differ in bit 0
+          any |= x[e];
+          lob[i] = __float_as_uint(lo);
+        }
+        if ((any & 1u) || !fast_ok) {      // within 2^-18 of a rounding tie (~1e-3 of the elements): exact replay
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (!fast_ok || (x[e] & 1u)) {
+              const int c = 128 * j + 4 * lane + e;
+              lob[4 * j + e] = static_cast<uint32_t>(ln_requant_exact(v[e], __ldg(sf + c), __ldg(mult + c), qmin, qmax)) & 0xffu;
+            }
         }
       }
       if (r < nr) {

@@ -319,6 +319,33 @@ __device__ __forceinline__ float x_eff_fma(float q, float s, float inv_s) {
   return __fmaf_rn(__fmaf_rn(-c, s, r), inv_s, c);
 }
 
+// The QuantAct behind the LayerNorm for G values of one lane (channels ch[0..G)): float32 product clamped before
+// rounding; rint(ra (1 -+ 2^-18) + 1.5 * 2^23) must agree (the exact value lies between them: float32(mult), z vs v and
+// the product rounding are each < 2^-21.5 relative), the code is then the low byte of the sum.  Where they differ
+// (~7e-4 of the elements) the exact replay runs for that element, inline and on its own group only -- a second pass
+// over the whole row would run for most warps.
+template <int G>
+__device__ __forceinline__ void ln_tail_group(const float (&v)[G], const float (&mf)[G], const int (&ch)[G],
+                                              const float* __restrict__ sf, const double* __restrict__ mult, bool fast_ok,
+                                              int qmin, int qmax, uint32_t (&lob)[G]) {
+  uint32_t x[G], any = 0;
+#pragma unroll
+  for (int e = 0; e < G; ++e) {
+    const float ra = fminf(fmaxf(__fmul_rn(v[e], mf[e]), -128.4f), 127.4f);
+    const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);        // 1 - 2^-18
+    const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);        // 1 + 2^-18
+    x[e] = __float_as_uint(lo) ^ __float_as_uint(hi);
+    any |= x[e];
+    lob[e] = __float_as_uint(lo);
+  }
+  if ((any & 1u) || !fast_ok) {
+#pragma unroll
+    for (int e = 0; e < G; ++e)
+      if (!fast_ok || (x[e] & 1u))
+        lob[e] = static_cast<uint32_t>(ln16_requant(v[e], __ldg(sf + ch[e]), __ldg(mult + ch[e]), qmin, qmax)) & 0xffu;
+  }
+}
+
 // ten steps of k <- floor((k + floor(v / k)) / 2) from 2^16 (ivit_modules.py:45-49), then floor(2^31 / k) (:51)
 __device__ __forceinline__ float ivit_std_factor(float var_f) {
   float k = 65536.f;
@@ -393,36 +420,22 @@ layernorm16_ivit_kernel(const XT* __restrict__ x, long long ldx, int8_t* __restr
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       const float fh = __fmul_rn(__shfl_sync(0xffffffffu, fct_l, r), 0.5f);
-      uint32_t slow = 0;
+      constexpr int G = NPL % 4 == 0 ? 4 : 2;
 #pragma unroll
-      for (int i = 0; i < NPL; ++i) {
-        const float yf = __fsub_rn(__int_as_float(0x4B400000 + y[r][i]), 12582912.f);     // |y| < 2^17: exact
-        float v = floorf(__fmul_rn(yf, fh));                                      // :52
-        v = __fadd_rn(v, bia[i]);                                                 // :61
-        const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -128.4f), 127.4f);
-        const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);        // 1 - 2^-18
-        const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);        // 1 + 2^-18
-        slow |= __float_as_uint(lo) ^ __float_as_uint(hi);
-        stage[warp][r][32 * i + lane] = static_cast<int8_t>(__float_as_uint(lo));
-      }
-      if (!fast_ok) slow = 1u;
-      if (slow & 1u) {                        // some element within 2^-18 of a rounding tie: exact replay of those
-        // (rolled loop over re-read codes: indexing y[][] dynamically would push it to local memory)
-        const XT* xr = x + static_cast<long long>(row0 + min(r, nr - 1)) * ldx + lane;
-        const int mean = mean_r[r];
-#pragma unroll 1
-        for (int i = 0; i < NPL; ++i) {
-          const int c = 32 * i + lane;
-          const float xe = x_eff_fma(static_cast<float>(static_cast<int>(__ldg(xr + 32 * i))), s_in, inv_s);
-          const float yf = static_cast<float>(static_cast<int>(xe) - mean);
-          float v = floorf(__fmul_rn(yf, fh));
-          v = __fadd_rn(v, __ldg(bias_int + c));
-          const float ra = fminf(fmaxf(__fmul_rn(v, static_cast<float>(__ldg(mult + c))), -128.4f), 127.4f);
-          const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);
-          const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);
-          if (!fast_ok || ((__float_as_uint(lo) ^ __float_as_uint(hi)) & 1u))
-            stage[warp][r][c] = static_cast<int8_t>(ln16_requant(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax));
+      for (int i0 = 0; i0 < NPL; i0 += G) {
+        float v[G], mg[G];
+        int ch[G];
+        uint32_t lob[G];
+#pragma unroll
+        for (int e = 0; e < G; ++e) {
+          const float yf = __fsub_rn(__int_as_float(0x4B400000 + y[r][i0 + e]), 12582912.f);   // |y| < 2^17: exact
+          v[e] = __fadd_rn(floorf(__fmul_rn(yf, fh)), bia[i0 + e]);               // :52, :61
+          mg[e] = mf[i0 + e];
+          ch[e] = 32 * (i0 + e) + lane;
         }
+        ln_tail_group<G>(v, mg, ch, sf, mult, fast_ok, qmin, qmax, lob);
+#pragma unroll
+        for (int e = 0; e < G; ++e) stage[warp][r][ch[e]] = static_cast<int8_t>(lob[e]);
       }
     }
     __syncwarp();
@@ -513,33 +526,21 @@ layernorm16_ibert_kernel(const XT* __restrict__ x, long long ldx, int8_t* __rest
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       const float fh = __fmul_rn(__shfl_sync(0xffffffffu, fct_l, r), 0.5f);
-      uint32_t slow = 0;
+      constexpr int G = NPL % 4 == 0 ? 4 : 2;
 #pragma unroll
-      for (int i = 0; i < NPL; ++i) {
-        float v = floorf(__fmul_rn(y[r][i], fh));                                 // :147
-        v = __fadd_rn(v, bia[i]);                                                 // :154
-        const float ra = fminf(fmaxf(__fmul_rn(v, mf[i]), -128.4f), 127.4f);
-        const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);        // 1 - 2^-18
-        const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);        // 1 + 2^-18
-        slow |= __float_as_uint(lo) ^ __float_as_uint(hi);
-        stage[warp][r][32 * i + lane] = static_cast<int8_t>(__float_as_uint(lo));
-      }
-      if (!fast_ok) slow = 1u;
-      if (slow & 1u) {                        // near a rounding tie: exact replay (rolled loop over re-read codes)
-        const XT* xr = x + static_cast<long long>(row0 + min(r, nr - 1)) * ldx + lane;
-        const float mean = mean_r[r];
-#pragma unroll 1
-        for (int i = 0; i < NPL; ++i) {
-          const int c = 32 * i + lane;
-          const float xe = x_eff_fma(static_cast<float>(static_cast<int>(__ldg(xr + 32 * i))), s_in, inv_s);
-          float v = floorf(__fmul_rn(__fsub_rn(xe, mean), fh));
-          v = __fadd_rn(v, __ldg(bias_int + c));
-          const float ra = fminf(fmaxf(__fmul_rn(v, static_cast<float>(__ldg(mult + c))), -128.4f), 127.4f);
-          const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);
-          const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);
-          if (!fast_ok || ((__float_as_uint(lo) ^ __float_as_uint(hi)) & 1u))
-            stage[warp][r][c] = static_cast<int8_t>(ln16_requant(v, __ldg(sf + c), __ldg(mult + c), qmin, qmax));
+      for (int i0 = 0; i0 < NPL; i0 += G) {
+        float v[G], mg[G];
+        int ch[G];
+        uint32_t lob[G];
+#pragma unroll
+        for (int e = 0; e < G; ++e) {
+          v[e] = __fadd_rn(floorf(__fmul_rn(y[r][i0 + e], fh)), bia[i0 + e]);     // :147, :154
+          mg[e] = mf[i0 + e];
+          ch[e] = 32 * (i0 + e) + lane;
         }
+        ln_tail_group<G>(v, mg, ch, sf, mult, fast_ok, qmin, qmax, lob);
+#pragma unroll
+        for (int e = 0; e < G; ++e) stage[warp][r][ch[e]] = static_cast<int8_t>(lob[e]);
       }
     }
     __syncwarp();
@@ -628,7 +629,6 @@ layernorm16_outer2_kernel(const XT* __restrict__ x, long long ldx, int8_t* __res
     var += __shfl_xor_sync(0xffffffffu, var, 1);
     const float fh = __fmul_rn(ivit_std_factor(static_cast<float>(var)), 0.5f);       // :45-51
     int8_t* orow = out + static_cast<long long>(row) * C + c0;
-    uint32_t slow = 0;
 #pragma unroll
     for (int h = 0; h < E / 16; ++h) {
       uint32_t w[4];
@@ -637,36 +637,19 @@ layernorm16_outer2_kernel(const XT* __restrict__ x, long long ldx, int8_t* __res
         const float4 b4 = *reinterpret_cast<const float4*>(&sb[c0 + 16 * h + 4 * j]);
         const float4 m4 = *reinterpret_cast<const float4*>(&sm[c0 + 16 * h + 4 * j]);
         const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, mm[4] = {m4.x, m4.y, m4.z, m4.w};
+        float v[4];
+        int ch[4];
         uint32_t lob[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const float yf = __fsub_rn(__int_as_float(0x4B400000 + t[16 * h + 4 * j + e]), 12582912.f);
-          float v = floorf(__fmul_rn(yf, fh));                                       // :52
-          v = __fadd_rn(v, bb[e]);                                                   // :61
-          const float ra = fminf(fmaxf(__fmul_rn(v, mm[e]), -128.4f), 127.4f);
-          const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);
-          const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);
-          slow |= __float_as_uint(lo) ^ __float_as_uint(hi);
-          lob[e] = __float_as_uint(lo);
+          v[e] = __fadd_rn(floorf(__fmul_rn(yf, fh)), bb[e]);                        // :52, :61
+          ch[e] = c0 + 16 * h + 4 * j + e;
         }
+        ln_tail_group<4>(v, mm, ch, sf, mult, fast_ok, qmin, qmax, lob);
         w[j] = __byte_perm(__byte_perm(lob[0], lob[1], 0x0040), __byte_perm(lob[2], lob[3], 0x0040), 0x5410);
       }
       if (live) *(reinterpret_cast<int4*>(orow) + h) = make_int4(w[0], w[1], w[2], w[3]);
-    }
-    if (!fast_ok) slow = 1u;
-    if ((slow & 1u) && live) {                 // rare: exact replay of the elements near a rounding tie
-#pragma unroll 1
-      for (int u = 0; u < E; ++u) {            // re-read codes: indexing t[] dynamically would push it to local memory
-        const float xe = x_eff_fma(static_cast<float>(static_cast<int>(__ldg(xr + u))), s_in, inv_s);
-        const float yf = static_cast<float>(static_cast<int>(xe) - mean);
-        float v = floorf(__fmul_rn(yf, fh));
-        v = __fadd_rn(v, sb[c0 + u]);
-        const float ra = fminf(fmaxf(__fmul_rn(v, sm[c0 + u]), -128.4f), 127.4f);
-        const float lo = __fmaf_rn(ra, 0.999996185302734375f, 12582912.f);
-        const float hi = __fmaf_rn(ra, 1.000003814697265625f, 12582912.f);
-        if (!fast_ok || ((__float_as_uint(lo) ^ __float_as_uint(hi)) & 1u))
-          orow[u] = static_cast<int8_t>(ln16_requant(v, __ldg(sf + c0 + u), __ldg(mult + c0 + u), qmin, qmax));
-      }
     }
   }
 }
