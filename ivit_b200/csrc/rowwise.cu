@@ -787,6 +787,9 @@ extern "C" int ivit_set_pdl(int on) {
 static int g_ln_variant = 0;
 namespace ivit {
 int ln_variant() { return g_ln_variant; }
+int try_ln_ibert_rows_i8(const int8_t* x, int64_t ldx, int8_t* out, int rows, int C, float s_in, const float* bias_int,
+                         const float* sf, const double* mult, int qmin, int qmax, float shift, int use_int_sqrt,
+                         cudaStream_t st);        // rowwise16.cu
 }
 extern "C" int ivit_layernorm_set_variant(int variant) {
   const int prev = g_ln_variant;
@@ -846,6 +849,10 @@ extern "C" int ivit_layernorm_requant_i8(int kind, const int8_t* x, int64_t ldx,
   if (rows <= 0) return 0;
   if (ldx % 16 != 0 || ldx < C) return fail(IVIT_ERR_BAD_ARG, "layernorm: row stride must be >= C and a multiple of 16");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (kind == 1) {     // I-BERT kind: several rows per warp, x/s as two fused operations (rowwise16.cu) where that applies
+    const int rc = try_ln_ibert_rows_i8(x, ldx, out, rows, C, s_in, bias_int, sf, mult, qmin, qmax, shift, use_int_sqrt, st);
+    if (rc != -1) return rc;
+  }
 #define IVIT_LN_CASE(c)                                                                                          \
   case c:                                                                                                        \
     return launch_ln<c / 32>(kind, x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, shift, use_int_sqrt, st);

@@ -893,6 +893,25 @@ static int launch_ln16(int kind, const XT* x, int64_t ldx, int8_t* out, int rows
   return check_launch("layernorm_x16_requant_kernel");
 }
 
+// int8 rows of the I-BERT kind through the restructured kernel (rowwise.cu's entry point asks here first);
+// returns -1 when it does not apply (width, alignment, scale not accepted by the host check, variant 1)
+namespace ivit {
+int try_ln_ibert_rows_i8(const int8_t* x, int64_t ldx, int8_t* out, int rows, int C, float s_in, const float* bias_int,
+                         const float* sf, const double* mult, int qmin, int qmax, float shift, int use_int_sqrt,
+                         cudaStream_t st) {
+  if (ln_variant() != 0 || qmin < -128 || qmax > 127 || (reinterpret_cast<uintptr_t>(out) & 15) != 0 ||
+      !xeff_fma_ok(s_in, 8))
+    return -1;
+  const float sp = ldexpf(1.f, static_cast<int>(shift));
+  switch (C) {
+    case 192: return launch_ln16_rows_ibert<6, 8, int8_t, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp, use_int_sqrt, st);
+    case 384: return launch_ln16_rows_ibert<12, 4, int8_t, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp, use_int_sqrt, st);
+    case 768: return launch_ln16_rows_ibert<24, 2, int8_t, 2>(x, ldx, out, rows, s_in, bias_int, sf, mult, qmin, qmax, sp, use_int_sqrt, st);
+    default: return -1;
+  }
+}
+}  // namespace ivit
+
 extern "C" int ivit_xeff_fma_ok(float s, int bits) { return (bits == 8 || bits == 16) && xeff_fma_ok(s, bits) ? 1 : 0; }
 
 extern "C" int ivit_layernorm_requant_i16_i8(int kind, const int16_t* x, int64_t ldx, int8_t* out, int rows, int C,

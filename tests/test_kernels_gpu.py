@@ -100,8 +100,13 @@ def test_layernorm_ivit(C):
 
 @pytest.mark.parametrize("C", [192, 384, 768])
 def test_layernorm_ibert(C):
-    _ln_case(1, C, 301, seed=C)
-    _ln_case(1, C, 64, seed=C + 1, s_in=0.113, neg=True)
+    try:
+        for variant in (0, 1):          # several rows per warp with the two-FMA quotient / one warp per row with divisions
+            ops.set_layernorm_variant(variant)
+            _ln_case(1, C, 301, seed=C)
+            _ln_case(1, C, 64, seed=C + 1, s_in=0.113, neg=True)
+    finally:
+        ops.set_layernorm_variant(0)
 
 
 @pytest.mark.parametrize("s_in", [0.0371, 0.0123, 0.113, 0.0052])
