@@ -312,7 +312,8 @@ layernorm96_strided_kernel(const XT* __restrict__ x, long long ldx, int8_t* __re
 //     2^31 / std division) runs once with row r on lane r, and the Newton loop stops as soon as every lane has
 //     reached a fixed point (further steps would return the same value).
 //   * the QuantAct tail of rowwise.cu: fl(y factor) / 2 == fl(y (factor / 2)); clamp before rounding; the near-tie
-//     test as two FMAs whose roundings must agree; the code is the low byte of the magic-number sum.
+//     test as two FMAs whose roundings must agree; the code is the low byte of the magic-number sum; an element
+//     that fails the test is replayed exactly inside its own group of four (ln_tail_group).
 __device__ __forceinline__ float x_eff_fma(float q, float s, float inv_s) {
   const float r = __fmul_rn(q, s);
   const float c = __fmul_rn(r, inv_s);
@@ -401,10 +402,9 @@ layernorm16_ivit_kernel(const XT* __restrict__ x, long long ldx, int8_t* __restr
     }
     const int mean_l = static_cast<int>(rintf(__fdiv_rn(sum_l, static_cast<float>(C))));   // :37, row r on lane r
     long long var_l = 1ll << 32;              // lanes without a row: 2^16 is a fixed point at once (early exit)
-    int mean_r[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      const int mean = mean_r[r] = __shfl_sync(0xffffffffu, mean_l, r);
+      const int mean = __shfl_sync(0xffffffffu, mean_l, r);
       long long var = 0;
 #pragma unroll
       for (int i = 0; i < NPL; ++i) {
@@ -494,10 +494,9 @@ layernorm16_ibert_kernel(const XT* __restrict__ x, long long ldx, int8_t* __rest
     }
     const float mean_l = rintf(__fdiv_rn(sum_l, static_cast<float>(C)));          // :130, row r on lane r
     float var_l = 0.f;
-    float mean_r[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      const float mean = mean_r[r] = __shfl_sync(0xffffffffu, mean_l, r);
+      const float mean = __shfl_sync(0xffffffffu, mean_l, r);
       TorchSum32 vacc;
 #pragma unroll
       for (int i = 0; i < NPL; ++i) {
