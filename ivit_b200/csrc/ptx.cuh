@@ -167,7 +167,7 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_
   d |= static_cast<uint64_t>(layout) << 61;
   return d;
 }
-constexpr uint32_t kLayoutSW128 = 2, kLayoutSW64 = 4;
+constexpr uint32_t kLayoutSW128 = 2, kLayoutSW64 = 4, kLayoutSW32 = 6;
 
 // TMEM -> registers: 32 lanes x 32-bit, N consecutive columns per thread (thread = TMEM lane = tile row).
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {

@@ -481,7 +481,7 @@ window_attention_rows_kernel(const WinAttnArgs a, int BW) {
   uint8_t* const sQ = tiles;                 // [128][64 B]: unit 0 rows 0..48, unit 1 rows 64..112
   uint8_t* const sK = tiles + 8192;          // two [64][64 B]
   uint8_t* const sP = tiles + 16384;         // [128][64 B]
-  uint8_t* const sVt = tiles + 24576;        // two [32][64 B]: v transposed, [d][token]
+  uint8_t* const sVt = tiles + 24576;        // two [64 tokens][32 B]: v as it lies in qkv (MN-major B operand)
   constexpr int hd = 32;
   const int res = a.res, nWx = res / RWS, nW = nWx * nWx;
   const int C = a.nH * hd, L = res * res;
@@ -554,10 +554,12 @@ window_attention_rows_kernel(const WinAttnArgs a, int BW) {
       *reinterpret_cast<int4*>(sQ + sw64_off(row, 16)) = q1;
       *reinterpret_cast<int4*>(sK + 4096 * u + sw64_off(i, 0)) = k0;
       *reinterpret_cast<int4*>(sK + 4096 * u + sw64_off(i, 16)) = k1;
-      const int vw[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-      uint8_t* vt = sVt + 2048 * u;
-#pragma unroll
-      for (int d = 0; d < hd; ++d) vt[sw64_off(d, i)] = static_cast<uint8_t>(vw[d >> 2] >> (8 * (d & 3)));
+      // v stays in its natural [token][32 B] order: the B operand of O = P V is read MN-major (head-dim contiguous,
+      // SWIZZLE_32B: inside each 8-token group of 256 bytes, tokens 4..7 have their two 16-byte halves exchanged)
+      uint8_t* vt = sVt + 2048 * u + 32 * i;
+      const int sw = ((i >> 2) & 1) << 4;
+      *reinterpret_cast<int4*>(vt + sw) = v0;
+      *reinterpret_cast<int4*>(vt + (sw ^ 16)) = v1;
     }
     fence_proxy_async_smem();
     __syncthreads();
@@ -641,13 +643,13 @@ window_attention_rows_kernel(const WinAttnArgs a, int BW) {
     __syncthreads();
     if (threadIdx.x == 0) {
       tc_fence_after();
-      constexpr uint32_t idesc2 = make_idesc_i8(128, 32, false, true, false, false);   // P u8, v^T s8, both K-major
+      constexpr uint32_t idesc2 = make_idesc_i8(128, 32, false, true, false, true);    // P u8 K-major, v s8 MN-major
 #pragma unroll
       for (int uu = 0; uu < 2; ++uu)
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < 2; ++k) {              // 32 tokens per MMA: four 8-token groups of 256 bytes
           const uint64_t da = make_smem_desc(smem_u32(sP) + k * 32, 16, 512, kLayoutSW64);
-          const uint64_t db = make_smem_desc(smem_u32(sVt) + 2048 * uu + k * 32, 16, 512, kLayoutSW64);
+          const uint64_t db = make_smem_desc(smem_u32(sVt) + 2048 * uu + k * 1024, 16, 256, kLayoutSW32);
           mma_i8_ss(tmem_base + 32 * uu, da, db, idesc2, k != 0 ? 1u : 0u);
         }
       tc_commit(&bars[1]);
