@@ -376,6 +376,7 @@ def run_ours(args):
                 a0.record()
                 for _ in range(args.steps):
                     s2.infer_async(host)
+                s2.join()              # the logits read-backs run on their own stream: the timed region ends after the last one
                 a1.record()
             s2.synchronize()
             barrier()
@@ -404,6 +405,7 @@ def run_ours(args):
             a0.record()
             for _ in range(args.steps):
                 s8.infer_async(host8)
+            s8.join()
             a1.record()
         s8.synchronize()
         barrier()

@@ -33,6 +33,7 @@ class InferenceSession:
         self.batch, self.chunks, self.cb = batch, chunks, batch // chunks
         self.compute = torch.cuda.Stream(device=self.device)
         self.copy = torch.cuda.Stream(device=self.device)
+        self.readback = torch.cuda.Stream(device=self.device)      # logits device->host, off the compute stream
         self.in_dtype = torch.float32
         if uint8_input is not None:
             if not isinstance(self.plan, FrozenVitPlan):
@@ -43,6 +44,7 @@ class InferenceSession:
             self.slots = [self.plan.capture(self.cb, slot=s, dtype=self.in_dtype) for s in range(slots)]
             self.ready = [torch.cuda.Event() for _ in self.slots]
             self.consumed = [torch.cuda.Event() for _ in self.slots]
+            self.read = [torch.cuda.Event() for _ in self.slots]     # the slot's logits have been copied out
         # two result buffers: the logits of call k stay valid while call k+1 is in flight
         self.out_hosts = [torch.empty((batch, cfg.num_classes), dtype=torch.float32).pin_memory() for _ in range(2)]
         self.h2d_bytes = batch * cfg.in_chans * cfg.img_size * cfg.img_size * (4 if uint8_input is None else 1)
@@ -75,13 +77,23 @@ class InferenceSession:
                 self.ready[s].record(self.copy)
             with torch.cuda.stream(self.compute):
                 self.compute.wait_event(self.ready[s])
+                self.compute.wait_event(self.read[s])           # the slot's previous logits are out (no-op at first)
                 g.replay()
                 self.consumed[s].record(self.compute)
+            with torch.cuda.stream(self.readback):               # the next forward does not queue behind this copy
+                self.readback.wait_event(self.consumed[s])
                 out_host[lo:hi].copy_(g.static_out, non_blocking=True)
+                self.read[s].record(self.readback)
         return out_host
+
+    def join(self):
+        """Make the compute stream wait for every readback enqueued so far (an event recorded on the compute stream
+        afterwards then covers the device->host copies too: bench.py's end-to-end timing)."""
+        self.compute.wait_stream(self.readback)
 
     def synchronize(self):
         self.compute.synchronize()
+        self.readback.synchronize()
 
     def infer(self, images: torch.Tensor) -> torch.Tensor:
         out = self.infer_async(images)
