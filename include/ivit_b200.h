@@ -63,7 +63,7 @@ int ivit_layernorm_requant_i8(int kind, const int8_t* x, int64_t ldx, int8_t* ou
  * variant 0 = choose per call, 1 = always the second.  Returns the previous setting.  Process-wide.
  * The 16-bit entry points below follow the same switch: 0 = the restructured kernels (x/s as two fused operations on
  * 1/s, taken only for scales the library has checked against the IEEE quotient over every code), 1 = always the
- * division kernels.  For A/B timing and tests. */
+ * division kernels (and ivit_gelu_lut_apply_i8 one row per warp at every width).  For A/B timing and tests. */
 int ivit_layernorm_set_variant(int variant);
 /* The check behind that choice, host arithmetic only (no GPU needed): 1 if, for scale s and EVERY code of the given
  * width (8 or 16 bits), c + fma(-c, s, r) * (1/s) with r = fl(q s), c = fl(r (1/s)) equals the IEEE quotient r / s --

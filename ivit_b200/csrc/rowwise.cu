@@ -912,10 +912,84 @@ extern "C" int ivit_gelu_ivit_raw_table(float* out65536, float s_in, int output_
   return check_launch("gelu_ivit_raw_kernel");
 }
 
+// Narrow rows (Swin stage 0 / 1: C = 384 / 768): R = 1536 / C rows per warp.  The R rows are one contiguous run of
+// 1536 bytes -- three 16-byte vectors per lane, every lane busy, 1.5 KB in flight per warp (a 384-byte row per warp
+// left the pass latency-bound at 3.2 TB/s) -- and the R row maxima travel through ONE shuffle reduction as the four
+// bytes of a word (__vmaxs4).
+template <int R>
+__global__ void __launch_bounds__(256)
+gelu_lut_apply_rows_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ out, const int8_t* __restrict__ lut,
+                           int rows) {
+  constexpr int NVR = 96 / R;                          // 16-byte vectors per row
+  __shared__ __align__(256) uint8_t srow[8][R][256];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long row0 = (static_cast<long long>(blockIdx.x) * 8 + warp) * R;
+  pdl_wait();                   // programmatic dependent launch: x is the predecessor's output
+  if (row0 >= rows) return;
+  const int nr = static_cast<int>(min(static_cast<long long>(R), rows - row0));
+  const int4* xr = reinterpret_cast<const int4*>(x + row0 * (NVR * 16));
+  int4* orow = reinterpret_cast<int4*>(out + row0 * (NVR * 16));
+  int4 v[3];
+  int rid[3];
+  uint32_t m = 0x80808080u;                            // byte r = running maximum of row r
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const int t = i * 32 + lane;
+    rid[i] = t / NVR;
+    if (rid[i] < nr) {
+      v[i] = __ldg(xr + t);
+      uint32_t q = __vmaxs4(__vmaxs4(v[i].x, v[i].y), __vmaxs4(v[i].z, v[i].w));
+      q = __vmaxs4(q, __byte_perm(q, 0, 0x1032));      // every byte = the maximum of the vector's 16 codes
+      q = __vmaxs4(q, __byte_perm(q, 0, 0x2301));
+      const uint32_t sel = 0xffu << (8 * rid[i]);
+      m = __vmaxs4(m, (q & sel) | (0x80808080u & ~sel));
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = __vmaxs4(m, __shfl_xor_sync(0xffffffffu, m, o));
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int mx = static_cast<int8_t>(m >> (8 * r));
+    // entry of code c at byte (c & 0xff): the line rotated by 128
+    *reinterpret_cast<uint2*>(&srow[warp][r][(8 * lane + 128) & 255]) =
+        __ldg(reinterpret_cast<const uint2*>(lut + (mx + 128) * 256) + lane);
+  }
+  __syncwarp();
+  const uint32_t tb0 = smem_u32(&srow[warp][0][0]);    // low byte zero
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    if (rid[i] < nr) {
+      const uint32_t tb = tb0 + 256u * static_cast<uint32_t>(rid[i]);
+      auto look4 = [&](uint32_t w) -> uint32_t {
+        uint32_t r0, r1, r2, r3;
+        asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r0) : "r"(__byte_perm(w, tb, 0x7650)));
+        asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r1) : "r"(__byte_perm(w, tb, 0x7651)));
+        asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r2) : "r"(__byte_perm(w, tb, 0x7652)));
+        asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r3) : "r"(__byte_perm(w, tb, 0x7653)));
+        return __byte_perm(__byte_perm(r0, r1, 0x0040), __byte_perm(r2, r3, 0x0040), 0x5410);
+      };
+      int4 o;
+      o.x = look4(v[i].x); o.y = look4(v[i].y); o.z = look4(v[i].z); o.w = look4(v[i].w);
+      orow[i * 32 + lane] = o;
+    }
+  }
+}
+
 extern "C" int ivit_gelu_lut_apply_i8(const int8_t* x, int8_t* out, const int8_t* lut, int rows, int C,
                                       void* stream) {
   if (rows <= 0) return 0;
   if (C % 16 != 0 || C > 6144) return fail(IVIT_ERR_UNSUPPORTED, "gelu: C % 16 == 0 and C <= 6144 required");
+  if ((C == 384 || C == 768) && g_ln_variant != 1 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 &&
+      (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+    const int R = 1536 / C;
+    const int grid = (rows + 8 * R - 1) / (8 * R);
+    cudaError_t le = R == 4 ? launch_kernel(gelu_lut_apply_rows_kernel<4>, dim3(grid), dim3(256), 0,
+                                            static_cast<cudaStream_t>(stream), x, out, lut, rows)
+                            : launch_kernel(gelu_lut_apply_rows_kernel<2>, dim3(grid), dim3(256), 0,
+                                            static_cast<cudaStream_t>(stream), x, out, lut, rows);
+    if (le != cudaSuccess) return fail(static_cast<int>(le), cudaGetErrorString(le));
+    return check_launch("gelu_lut_apply_rows_kernel");
+  }
   if (C <= 3072)
   {
     cudaError_t le = launch_kernel(gelu_lut_apply_kernel<6>, dim3((rows + 7) / 8), dim3(256), 0,

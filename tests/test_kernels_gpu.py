@@ -138,11 +138,13 @@ def test_gelu_ivit_table_exhaustive(s_in):
 
 
 def test_gelu_apply_wide_rows():
-    """Hidden widths beyond 3072 (ViT-L / Swin-B: 4096, Swin-L: 6144) take the wider instantiation."""
+    """Hidden widths beyond 3072 (ViT-L / Swin-B: 4096, Swin-L: 6144) take the wider instantiation; 384 and 768 (Swin
+    stages 0 / 1, DeiT-T) the several-rows-per-warp one (row counts that are not multiples of its row group)."""
     s_in = f32(0.0371)
     rng = np.random.default_rng(2)
-    for Cw in (4096, 6144, 3072):
-        xr = np.clip(np.rint(rng.standard_normal((21, Cw)) * 30), -128, 100).astype(np.int8)
+    for Cw, nrows in ((4096, 21), (6144, 21), (3072, 21), (384, 203), (768, 77), (384, 1), (768, 1), (384, 32)):
+        xr = np.clip(np.rint(rng.standard_normal((nrows, Cw)) * 30 + rng.integers(-60, 20, size=(nrows, 1))), -128,
+                     100).astype(np.int8)
         yr, sgr, _ = O.ivit_gelu((xr.astype(f32) * s_in).astype(f32), np.array([s_in]))
         x_max = np.array([np.abs(yr).max() * 0.8], dtype=f32)
         _, s_out, expr = O.quant_act(yr, 8, -x_max, x_max, pre_scale=sgr)
