@@ -753,8 +753,8 @@ gemm_i8_cl_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               for (int b = 0; b < 2; ++b) {
                 const int c1 = clampi(c[2 * g + b], e.qmin, e.qmax);
                 const int id = static_cast<int16_t>(iw >> (16 * b));
-                const double cd = __hiloint2double(0x43300000, c1 ^ 0x80000000) - kMagicInt;
-                const double dd = __hiloint2double(0x43300000, id ^ 0x80000000) - kMagicInt;
+                // codes -> fp64 through I2F.F64 (conversion pipe) instead of XOR + MOV + DADD each, as in MODE 2
+                const double cd = __int2double_rn(c1), dd = __int2double_rn(id);
                 r2[b] = clampi(__double2loint(__fma_rn(cd, m2, kMagicRnd)) + __double2loint(__fma_rn(dd, mi, kMagicRnd)),
                                e.qmin2, e.qmax2);
               }
