@@ -288,6 +288,11 @@ typedef struct {
    *    returns (swin_quant.py:121-169) after the caller's torch.roll + window_partition (:258-272); the shift mask is
    *    still generated from (res, ws, shift).  The module-by-module frozen path uses this form. */
   int windowed;
+  /* optional, with exp_table: every table entry whose code lies at least sat_k below its row-max code equals sat_e bit
+   * for bit (int_exp_shift clamps its argument, ivit_modules.py:155), so the kernel need not gather it.  sat_k = 0:
+   * gather every entry. */
+  int sat_k;
+  float sat_e;
 } ivit_window_attention_params_t;
 int ivit_window_attention_i8(const int8_t* qkv, int8_t* out, uint8_t* probs, int B, int res, int ws, int shift, int nH,
                              int hd, const ivit_window_attention_params_t* p, void* stream);

@@ -71,6 +71,7 @@ class WindowAttentionParams(C.Structure):
         ("mask_clamps", C.c_int),
         ("bias_terms", C.c_void_p),
         ("windowed", C.c_int),
+        ("sat_k", C.c_int), ("sat_e", C.c_float),
     ]
 
 

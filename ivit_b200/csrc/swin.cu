@@ -461,9 +461,11 @@ __device__ __forceinline__ void rows_softmax(const WinAttnArgs& a, uint32_t t_ro
   mx = max(mx, a.p.qmin2);                       // (a real row always keeps its diagonal: no effect there)
   const float* trow = a.p.exp_table + (mx + 128) * 256 + 128;
   const float e_mask = -a.x0;
+  // codes at least sat_k below the row maximum all hold the table's saturated value: no gather for them
+  const int csat = a.p.sat_k > 0 ? mx - a.p.sat_k : -1000;
 #pragma unroll
   for (int j = 0; j < RN; ++j) {
-    const float t = __ldg(trow + c2[j]);
+    const float t = c2[j] > csat ? __ldg(trow + c2[j]) : a.p.sat_e;
     e[j] = (MASKED && ((mbits >> j) & 1ull)) ? e_mask : t;
   }
 }

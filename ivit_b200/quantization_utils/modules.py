@@ -923,6 +923,7 @@ def _frozen_window_attention(p, view: QTensor, qact3: QuantAct, device):
             tp.kind, tp.output_bit, tp.s_attn = 0, int(sm.mod.output_bit), float(s2_h[0])
             keep.append(ops.softmax_table_build(tp, device, collapse=False))
             a.exp_table = tp.exp_table
+            a.sat_k, a.sat_e = tp.sat_k, tp.sat_e
         _, s3_h, (lo3, hi3) = qact3._out_scale(device)
         a.mult_out = float(hm.dyadic_mult(p.s_h, s3_h).reshape(-1)[0])
         a.qmin_out, a.qmax_out = lo3, hi3

@@ -167,6 +167,7 @@ class FrozenSwinPlan(GraphCaptureMixin):
             tp.kind, tp.output_bit, tp.s_attn = 0, 8, float(s2[0])
             self._keep.append(ops.softmax_table_build(tp, self.device, collapse=False))
             a.exp_table = tp.exp_table
+            a.sat_k, a.sat_e = tp.sat_k, tp.sat_e
         s_sm = np.array([1 / 2 ** 7], dtype=f32)                           # ivit_modules.py:177
         s_mm2 = (s_sm * s_qkv).astype(f32)
         s3 = self._act_scale(p + "qact3")

@@ -79,6 +79,8 @@ def win_case(it):
     tp.kind, tp.output_bit, tp.s_attn = 0, 8, float(s2)
     keep = ops.softmax_table_build(tp, "cuda", collapse=False)
     p.exp_table, p.mask_clamps = tp.exp_table, int(mask_always_clamps(s2, -128, 127))
+    if rng.random() < 0.7:
+        p.sat_k, p.sat_e = tp.sat_k, tp.sat_e
     p.windowed = int(rng.integers(0, 2))
     x = torch.from_numpy(qkv).cuda()
     outs = []
