@@ -357,3 +357,29 @@ def test_fused_swin_forward_drops_its_plans_on_load_state_dict():
         model(synth_images(1, cfg, seed=0))            # CPU tensor: the frozen forward refuses, no fallback
     lifecycle.unfreeze_model(model)
     assert "forward" not in model.__dict__
+
+
+@pytest.mark.reference
+@pytest.mark.parametrize("momentum", [0.95, -1])
+def test_percentile_and_minmax_calibration_modes_equal_reference(momentum):
+    """QuantAct's other running-stat modes (quant_modules.py:319-355): percentile ranges (torch.quantile) and the
+    running min / max (act_range_momentum = -1) -- every calibrated buffer equals the reference's."""
+    from ivit_b200 import lifecycle
+    cfg, ref_model, our_model = _build_pair("toy_ivit")
+    for model in (ref_model, our_model):
+        n = 0
+        for m in model.modules():
+            if type(m).__name__ == "QuantAct":
+                m.percentile = 99.9 if n % 2 == 0 else None          # half of the locations on percentiles
+                m.act_range_momentum = momentum
+                n += 1
+        assert n >= 20
+    batches = [synth_images(3, cfg, seed=2), synth_images(2, cfg, seed=6), synth_images(2, cfg, seed=7)]
+    with torch.no_grad():
+        for x in batches:
+            ref_model(x)
+    assert lifecycle.calibrate_model(our_model, batches) == 3
+    ref_sd, our_sd = ref_model.state_dict(), our_model.state_dict()
+    for k in ref_sd:
+        if k.endswith((".x_min", ".x_max", "act_scaling_factor")):
+            assert torch.equal(ref_sd[k], our_sd[k]), k
