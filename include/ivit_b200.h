@@ -25,7 +25,9 @@ extern "C" {
 #define IVIT_ERR_UNSUPPORTED (-2)
 #define IVIT_ERR_DRIVER (-3)
 
-/* Library / device probe.  ivit_abi_version() needs no GPU. */
+/* Library / device probe.  ivit_abi_version() needs no GPU.  2 = this header (round 2: fields appended to
+ * ivit_attention_params_t, ivit_window_attention_params_t and ivit_gemm_epilogue_t; zero-initialised structs of version 1
+ * callers keep their meaning). */
 int ivit_abi_version(void);
 /* Programmatic dependent launch of the hot kernels (GEMM, attention, LayerNorm, GELU table): their prologues
  * overlap the predecessor's tail inside a stream / CUDA graph.  Returns the previous setting.  Process-wide. */

@@ -715,7 +715,7 @@ static int ew_grid(long long n, int block) {
 
 using namespace ivit;
 
-extern "C" int ivit_abi_version(void) { return 1; }
+extern "C" int ivit_abi_version(void) { return 2; }   // 2: round-2 fields appended to the attention / window-attention / GEMM epilogue structs
 extern "C" const char* ivit_last_error(void) { return g_err; }
 extern "C" int ivit_device_sm(int* major, int* minor) {
   int dev = 0;
